@@ -1,0 +1,236 @@
+// fgdm_b200 — small fused kernels around the UNet: CFG combine + DDIM update, timestep embedding,
+// skinny Linear layers on the [R, 1280] embedding, NHWC resampling helpers.
+#include "common.cuh"
+
+namespace fgdm {
+
+// ---------------------------------------------------------------------------------------------
+// Fused classifier-free guidance + DDIM x_{t-1} update. Replaces ~15 ATen launches of
+// DDIMSampler.p_sample_ddim (ldm/models/diffusion/ddim.py:243 and :249-268; controlnet/cldm/
+// ddim_hacked.py:192,207-230):
+//   e      = e_u + s * (e_c - e_u)
+//   x0     = (x - sqrt(1 - a_t) * e) / sqrt(a_t)
+//   x_prev = sqrt(a_prev) * x0 + sqrt(1 - a_prev - sigma^2) * e + sigma * temperature * noise
+// coef row layout (fp32[5]): {sqrt(1-a_t), sqrt(a_t), sqrt(a_prev), sqrt(1-a_prev-sigma^2), sigma}.
+// The row index is read from device memory when index_ptr != null so a captured CUDA graph can be
+// replayed for every step. At 131 k elements this kernel is launch-latency bound, not HBM bound.
+// ---------------------------------------------------------------------------------------------
+__global__ void cfg_ddim_kernel(const float* __restrict__ e_u, const float* __restrict__ e_c,
+                                const float* __restrict__ x, const float* __restrict__ noise,
+                                const float* __restrict__ coef_table, const int* __restrict__ index_ptr, int index,
+                                float scale, float temperature, float* __restrict__ x_prev,
+                                float* __restrict__ pred_x0, int n) {
+  const int row = index_ptr ? *index_ptr : index;
+  const float* cf = coef_table + 5 * row;
+  const float s1m = cf[0], sa = cf[1], sap = cf[2], dir = cf[3], sigma = cf[4];
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  const float4 eu = *reinterpret_cast<const float4*>(e_u + i);
+  const float4 ec = e_c ? *reinterpret_cast<const float4*>(e_c + i) : eu;
+  const float4 xv = *reinterpret_cast<const float4*>(x + i);
+  float4 nz = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (noise) nz = *reinterpret_cast<const float4*>(noise + i);
+  const float eua[4] = {eu.x, eu.y, eu.z, eu.w}, eca[4] = {ec.x, ec.y, ec.z, ec.w};
+  const float xa[4] = {xv.x, xv.y, xv.z, xv.w}, na[4] = {nz.x, nz.y, nz.z, nz.w};
+  float xp[4], p0[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float e = eua[k] + scale * (eca[k] - eua[k]);
+    const float x0 = (xa[k] - s1m * e) / sa;
+    p0[k] = x0;
+    xp[k] = sap * x0 + dir * e + sigma * temperature * na[k];
+  }
+  *reinterpret_cast<float4*>(x_prev + i) = make_float4(xp[0], xp[1], xp[2], xp[3]);
+  if (pred_x0) *reinterpret_cast<float4*>(pred_x0 + i) = make_float4(p0[0], p0[1], p0[2], p0[3]);
+}
+
+int launch_cfg_ddim(const float* e_u, const float* e_c, const float* x, const float* noise, const float* coef_table,
+                    const int* index_ptr, int index, float scale, float temperature, float* x_prev, float* pred_x0,
+                    int n, cudaStream_t stream) {
+  if (n % 4 != 0) { set_error("cfg_ddim: n=%d must be a multiple of 4", n); return -1; }
+  const int threads = 256;
+  const int blocks = (n / 4 + threads - 1) / threads;
+  cfg_ddim_kernel<<<blocks, threads, 0, stream>>>(e_u, e_c, x, noise, coef_table, index_ptr, index, scale,
+                                                  temperature, x_prev, pred_x0, n);
+  return check_launch("cfg_ddim_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
+// timestep_embedding (ldm/modules/diffusionmodules/util.py:160-180): out[r] = [cos(t f), sin(t f)]
+// with the frequency table computed on the host exactly as the reference does.
+// ---------------------------------------------------------------------------------------------
+__global__ void timestep_embedding_kernel(const long long* __restrict__ t, const float* __restrict__ freqs,
+                                          float* __restrict__ out, int rows, int half) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * half) return;
+  const int r = i / half, k = i - r * half;
+  const float arg = static_cast<float>(t[r]) * freqs[k];
+  out[static_cast<size_t>(r) * 2 * half + k] = cosf(arg);
+  out[static_cast<size_t>(r) * 2 * half + half + k] = sinf(arg);
+}
+
+int launch_timestep_embedding(const long long* t, const float* freqs, float* out, int rows, int dim,
+                              cudaStream_t stream) {
+  if (dim % 2) { set_error("timestep_embedding: odd dim %d", dim); return -1; }
+  const int n = rows * (dim / 2);
+  timestep_embedding_kernel<<<(n + 255) / 256, 256, 0, stream>>>(t, freqs, out, rows, dim / 2);
+  return check_launch("timestep_embedding_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Skinny Linear: y[r, n] = out_act( in_act(x[r, :]) . W[n, :] + b[n] ), fp32, R small (<= a few
+// dozen rows). One warp per output column, 8 rows per pass. Used for time_embed
+// (openaimodel.py:538-542) and all ResBlock emb_layers (openaimodel.py:238-244) batched into one
+// weight matrix. Weight-read bound (each W row is read once per 8 rows).
+// ---------------------------------------------------------------------------------------------
+__global__ void skinny_linear_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                     const float* __restrict__ b, float* __restrict__ y, int R, int K, int N,
+                                     int in_act, int out_act) {
+  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const int r0 = blockIdx.y * 8;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+  const float* wr = w + static_cast<size_t>(n) * K;
+  for (int k = lane; k < K; k += 32) {
+    const float wv = __ldg(wr + k);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (r0 + i < R) {
+        float xv = __ldg(x + static_cast<size_t>(r0 + i) * K + k);
+        if (in_act) xv = silu_f(xv);
+        acc[i] += xv * wv;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = warp_sum(acc[i]);
+  if (lane == 0) {
+    const float bias = b ? b[n] : 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (r0 + i < R) {
+        float v = acc[i] + bias;
+        if (out_act) v = silu_f(v);
+        y[static_cast<size_t>(r0 + i) * N + n] = v;
+      }
+    }
+  }
+}
+
+int launch_skinny_linear(const float* x, const float* w, const float* b, float* y, int R, int K, int N, int in_act,
+                         int out_act, cudaStream_t stream) {
+  const int threads = 256;
+  dim3 grid((N * 32 + threads - 1) / threads, (R + 7) / 8);
+  skinny_linear_kernel<<<grid, threads, 0, stream>>>(x, w, b, y, R, K, N, in_act, out_act);
+  return check_launch("skinny_linear_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
+// NHWC bf16 resampling helpers (vectors of 8 channels).
+//  mode 0: nearest 2x upsample (F.interpolate(scale_factor=2, mode="nearest"), openaimodel.py:123,
+//          model.py:53)                                   in [NB,H,W,C] -> out [NB,2H,2W,C]
+//  mode 1: 2x2 average pool (adapter.py Downsample with use_conv=False, :270-277)
+//                                                         in [NB,H,W,C] -> out [NB,H/2,W/2,C]
+//  mode 2: phase split for stride-2 convs                 in [NB,H,W,C] -> out [4,NB,H/2,W/2,C],
+//          phase = (h&1)*2 + (w&1); a 3x3/s2/p1 conv becomes 9 unit-stride shifted loads.
+// ---------------------------------------------------------------------------------------------
+__global__ void resample_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int NB, int H,
+                                int W, int C, int mode) {
+  const int V = C / 8;
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (mode == 0) {
+    const size_t total = static_cast<size_t>(NB) * 4 * H * W * V;
+    if (i >= total) return;
+    const int v = i % V;
+    size_t p = i / V;
+    const int ow = p % (2 * W); p /= (2 * W);
+    const int oh = p % (2 * H);
+    const int n = p / (2 * H);
+    const uint4 u = *reinterpret_cast<const uint4*>(in + ((static_cast<size_t>(n) * H + oh / 2) * W + ow / 2) * C + v * 8);
+    *reinterpret_cast<uint4*>(out + i * 8) = u;
+  } else if (mode == 1) {
+    const int OH = H / 2, OW = W / 2;
+    const size_t total = static_cast<size_t>(NB) * OH * OW * V;
+    if (i >= total) return;
+    const int v = i % V;
+    size_t p = i / V;
+    const int ow = p % OW; p /= OW;
+    const int oh = p % OH;
+    const int n = p / OH;
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.0f;
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const uint4 u = *reinterpret_cast<const uint4*>(
+            in + ((static_cast<size_t>(n) * H + 2 * oh + dy) * W + 2 * ow + dx) * C + v * 8);
+        const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = unpack_bf16x2(w4[e]);
+          acc[2 * e] += f.x; acc[2 * e + 1] += f.y;
+        }
+      }
+    *reinterpret_cast<uint4*>(out + i * 8) =
+        make_uint4(pack_bf16x2(acc[0] * 0.25f, acc[1] * 0.25f), pack_bf16x2(acc[2] * 0.25f, acc[3] * 0.25f),
+                   pack_bf16x2(acc[4] * 0.25f, acc[5] * 0.25f), pack_bf16x2(acc[6] * 0.25f, acc[7] * 0.25f));
+  } else {
+    const size_t total = static_cast<size_t>(NB) * H * W * V;
+    if (i >= total) return;
+    const int v = i % V;
+    size_t p = i / V;
+    const int w = p % W; p /= W;
+    const int h = p % H;
+    const int n = p / H;
+    const int phase = (h & 1) * 2 + (w & 1);
+    const uint4 u = *reinterpret_cast<const uint4*>(in + i * 8);
+    const size_t o = (((static_cast<size_t>(phase) * NB + n) * (H / 2) + h / 2) * (W / 2) + w / 2) * C + v * 8;
+    *reinterpret_cast<uint4*>(out + o) = u;
+  }
+}
+
+int launch_resample(const void* in, void* out, int NB, int H, int W, int C, int mode, cudaStream_t stream) {
+  if (C % 8) { set_error("resample: C=%d must be a multiple of 8", C); return -1; }
+  if (mode != 0 && ((H | W) & 1)) { set_error("resample: odd H/W (%d,%d)", H, W); return -1; }
+  size_t total = static_cast<size_t>(NB) * H * W * (C / 8);
+  if (mode == 0) total *= 4;
+  if (mode == 1) total /= 4;
+  const int threads = 256;
+  const size_t blocks = (total + threads - 1) / threads;
+  resample_kernel<<<static_cast<unsigned>(blocks), threads, 0, stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(in), reinterpret_cast<__nv_bfloat16*>(out), NB, H, W, C, mode);
+  return check_launch("resample_kernel");
+}
+
+// out = a + b (bf16, n multiple of 8) — only used where an add cannot ride a GEMM epilogue.
+__global__ void add_bf16_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                                __nv_bfloat16* __restrict__ out, size_t nvec) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= nvec) return;
+  const uint4 ua = *reinterpret_cast<const uint4*>(a + i * 8);
+  const uint4 ub = *reinterpret_cast<const uint4*>(b + i * 8);
+  const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 fa = unpack_bf16x2(wa[e]), fb = unpack_bf16x2(wb[e]);
+    o[e] = pack_bf16x2(fa.x + fb.x, fa.y + fb.y);
+  }
+  *reinterpret_cast<uint4*>(out + i * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+int launch_add_bf16(const void* a, const void* b, void* out, size_t n, cudaStream_t stream) {
+  if (n % 8) { set_error("add_bf16: n must be a multiple of 8"); return -1; }
+  const size_t nvec = n / 8;
+  add_bf16_kernel<<<static_cast<unsigned>((nvec + 255) / 256), 256, 0, stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(b),
+      reinterpret_cast<__nv_bfloat16*>(out), nvec);
+  return check_launch("add_bf16_kernel");
+}
+
+}  // namespace fgdm

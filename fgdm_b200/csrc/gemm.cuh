@@ -1,0 +1,53 @@
+// fgdm_b200 — parameter block shared by the implicit-GEMM conv / linear kernel and its host launcher.
+#pragma once
+#include "common.cuh"
+
+namespace fgdm {
+
+enum GemmOutMode : int {
+  kOutBf16 = 0,    // out[m, col_off + n] bf16 row-major (NHWC activation)
+  kOutGeglu = 1,   // tile holds BN/2 value columns then BN/2 gate columns: out = x * gelu(gate)
+  kOutQkv = 2,     // head-split Q/K [img, head, tok, d] and transposed V [img, head, d, tok_pad]
+  kOutF32 = 3,     // out[m, n] fp32 row-major
+};
+
+enum GemmAct : int { kActNone = 0, kActSilu = 1, kActRelu = 2 };
+
+struct GemmParams {
+  // A operand: up to two NHWC bf16 sources that are concatenated along channels (virtual concat)
+  int NB, H, W;        // image view of the A rows; M = NB*H*W, row index is the linear pixel index
+  int M;
+  int C0, C1;          // channels of source 0 / 1 (C1 == 0: single source); both multiples of 64
+  int taps;            // filter taps (1 for linear / 1x1, 9 for 3x3)
+  int tap_dn[9];       // per-tap coordinate offsets (image, row, column) applied to the TMA box
+  int tap_dh[9];
+  int tap_dw[9];
+  // B operand: weights [N, taps*(C0+C1)] bf16, K index = tap*(C0+C1) + c
+  int N;
+  int num_m_tiles, num_n_tiles;
+  // epilogue: v = alpha * (acc + bias[n] + rowvec[img, n]); v = act(v); v += res0[m, n] + res1[m, n]
+  const float* bias;
+  const float* rowvec;  // [NB_rowvec, ld_rowvec], row = m / rows_per_img
+  int ld_rowvec;
+  int rows_per_img;     // H*W of the OUTPUT view (tokens per image)
+  const __nv_bfloat16* res0;
+  int ld_res0;
+  const __nv_bfloat16* res1;
+  int ld_res1;
+  float alpha;
+  int act;
+  int out_mode;
+  void* out;
+  int ldo;
+  int col_off;
+  // kOutQkv
+  __nv_bfloat16* q_out;
+  __nv_bfloat16* k_out;
+  __nv_bfloat16* vt_out;
+  int qkv_first;        // 0: columns are [q | k | v]; 1: columns are [k | v]
+  int inner;            // heads * dhead
+  int heads, dhead;
+  int tok_pad;          // row stride of the transposed V (>= tokens per image, multiple of 8)
+};
+
+}  // namespace fgdm

@@ -1,0 +1,252 @@
+"""Tensor-level wrappers over the C ABI. torch is used only for device memory and the current stream.
+
+Activations are NHWC bf16 tensors `[nb, h, w, c]` (tokens: `[nb, n, c]`); see include/fgdm_b200.h.
+Every function launches on torch's current CUDA stream and never synchronises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import _lib
+from ._lib import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU,
+                   OUT_QKV, GemmArgs)
+
+bf16 = torch.bfloat16
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None, bias=None, rowvec=None,
+              rows_per_img=0, res0=None, res1=None, alpha=1.0, act=ACT_NONE, out_mode=OUT_BF16, out=None,
+              ldo=None, col_off=0, qkv=None, bn_hint=0):
+    """Implicit-GEMM conv / Linear. a0 (and a1) are NHWC bf16 `[nb, h, w, c]` or token `[rows, c]` tensors.
+
+    For CONV_3X3_S2, a0 is the phase-split tensor `[4, nb, h, w, c]` (see resample(mode=2)) and
+    (nb, h, w) describe the OUTPUT. Returns the output tensor (or None in QKV mode).
+    """
+    lib = _lib.load()
+    c0 = a0.shape[-1]
+    c1 = a1.shape[-1] if a1 is not None else 0
+    if nb is None:
+        if a0.dim() == 4:
+            nb, h, w = a0.shape[0], a0.shape[1], a0.shape[2]
+        else:  # [rows, c] or [b, n, c] tokens: one flat "image row"
+            nb, h, w = 1, 1, a0.numel() // c0
+    m = nb * h * w
+    args = GemmArgs()
+    args.a0, args.a1, args.c0, args.c1 = _p(a0), _p(a1), c0, c1
+    args.nb, args.h, args.w, args.conv = nb, h, w, conv
+    args.weight, args.n = _p(weight), n
+    args.bias, args.rowvec = _p(bias), _p(rowvec)
+    args.ld_rowvec = rowvec.shape[-1] if rowvec is not None else 0
+    args.rows_per_img = rows_per_img
+    args.res0, args.ld_res0 = _p(res0), (res0.shape[-1] if res0 is not None else 0)
+    args.res1, args.ld_res1 = _p(res1), (res1.shape[-1] if res1 is not None else 0)
+    args.alpha, args.act, args.out_mode = alpha, act, out_mode
+    args.bn_hint = bn_hint
+    if out_mode == OUT_QKV:
+        q, k, vt, first, heads, dhead, tok_pad = qkv
+        args.q_out, args.k_out, args.vt_out = _p(q), _p(k), _p(vt)
+        args.qkv_first, args.heads, args.dhead, args.tok_pad = first, heads, dhead, tok_pad
+    else:
+        n_out = n // 2 if out_mode == OUT_GEGLU else n
+        if out is None:
+            out = torch.empty((m, n_out), device=a0.device, dtype=torch.float32 if out_mode == OUT_F32 else bf16)
+            ldo = n_out
+        elif ldo is None:
+            ldo = out.shape[-1]
+        args.out, args.ldo, args.col_off = _p(out), ldo, col_off
+    _lib.check(lib.fgdm_conv_gemm(C.byref(args), _stream()), "fgdm_conv_gemm")
+    return out
+
+
+def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):
+    scale = d ** -0.5 if scale is None else scale
+    _lib.check(_lib.load().fgdm_attention(_p(q), _p(k), _p(vt), _p(out), images, heads, nq, nk, d, tok_pad,
+                                         scale, _stream()), "fgdm_attention")
+    return out
+
+
+_GN_WS = {}
+
+
+def _gn_workspace(device, nb, groups):
+    need = nb * 64 * groups * 2
+    ws = _GN_WS.get(device)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty(max(need, 1 << 16), device=device, dtype=torch.float32)
+        _GN_WS[device] = ws
+    return ws
+
+
+def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=None):
+    """x0 (and x1): NHWC bf16 [nb, h, w, c]; returns [nb, h, w, c0+c1] bf16."""
+    nb = x0.shape[0]
+    c0 = x0.shape[-1]
+    c1 = x1.shape[-1] if x1 is not None else 0
+    hw = x0.numel() // (nb * c0)
+    if out is None:
+        out = torch.empty(tuple(x0.shape[:-1]) + (c0 + c1,), device=x0.device, dtype=bf16)
+    ws = _gn_workspace(x0.device, nb, groups)
+    _lib.check(_lib.load().fgdm_groupnorm(_p(x0), _p(x1), _p(out), _p(gamma), _p(beta), _p(ws), nb, hw, c0, c1,
+                                         groups, eps, 1 if silu else 0, _stream()), "fgdm_groupnorm")
+    return out
+
+
+def layernorm(x, gamma, beta, eps=1e-5, out=None):
+    c = x.shape[-1]
+    rows = x.numel() // c
+    if out is None:
+        out = torch.empty_like(x)
+    _lib.check(_lib.load().fgdm_layernorm(_p(x), _p(out), _p(gamma), _p(beta), rows, c, eps, _stream()),
+               "fgdm_layernorm")
+    return out
+
+
+def softmax_rows(s, scale, out=None):
+    rows, cols = s.shape
+    if out is None:
+        out = torch.empty((rows, cols), device=s.device, dtype=bf16)
+    _lib.check(_lib.load().fgdm_softmax_rows(_p(s), _p(out), rows, cols, scale, _stream()), "fgdm_softmax_rows")
+    return out
+
+
+def cfg_ddim_step(e_uncond, e_cond, x, coef_table, index, scale, *, noise=None, temperature=1.0, index_ptr=None,
+                  x_prev=None, pred_x0=None):
+    if x_prev is None:
+        x_prev = torch.empty_like(x)
+    if pred_x0 is None:
+        pred_x0 = torch.empty_like(x)
+    _lib.check(_lib.load().fgdm_cfg_ddim_step(_p(e_uncond), _p(e_cond), _p(x), _p(noise), _p(coef_table),
+                                             _p(index_ptr), index, scale, temperature, _p(x_prev), _p(pred_x0),
+                                             x.numel(), _stream()), "fgdm_cfg_ddim_step")
+    return x_prev, pred_x0
+
+
+def timestep_embedding(t, freqs, dim):
+    out = torch.empty((t.shape[0], dim), device=t.device, dtype=torch.float32)
+    _lib.check(_lib.load().fgdm_timestep_embedding(_p(t), _p(freqs), _p(out), t.shape[0], dim, _stream()),
+               "fgdm_timestep_embedding")
+    return out
+
+
+def skinny_linear(x, w, b, in_act=False, out_act=False):
+    rows, k = x.shape
+    n = w.shape[0]
+    y = torch.empty((rows, n), device=x.device, dtype=torch.float32)
+    _lib.check(_lib.load().fgdm_skinny_linear(_p(x), _p(w), _p(b), _p(y), rows, k, n, int(in_act), int(out_act),
+                                             _stream()), "fgdm_skinny_linear")
+    return y
+
+
+def resample(x, mode):
+    """mode 0: nearest 2x up; 1: 2x2 avg pool; 2: phase split -> [4, nb, h/2, w/2, c]."""
+    nb, h, w, c = x.shape
+    if mode == 0:
+        out = torch.empty((nb, 2 * h, 2 * w, c), device=x.device, dtype=bf16)
+    elif mode == 1:
+        out = torch.empty((nb, h // 2, w // 2, c), device=x.device, dtype=bf16)
+    else:
+        out = torch.empty((4, nb, h // 2, w // 2, c), device=x.device, dtype=bf16)
+    _lib.check(_lib.load().fgdm_resample(_p(x), _p(out), nb, h, w, c, mode, _stream()), "fgdm_resample")
+    return out
+
+
+def add_bf16(a, b, out=None):
+    if out is None:
+        out = torch.empty_like(a)
+    _lib.check(_lib.load().fgdm_add_bf16(_p(a), _p(b), _p(out), a.numel(), _stream()), "fgdm_add_bf16")
+    return out
+
+
+def conv_small_cin(x, w, bias, cout, act=ACT_NONE, in_scale=1.0):
+    """x: NCHW fp32 with 3 or 4 channels -> NHWC bf16 [nb, h, w, cout]."""
+    nb, cin, h, wd = x.shape
+    y = torch.empty((nb, h, wd, cout), device=x.device, dtype=bf16)
+    _lib.check(_lib.load().fgdm_conv_small_cin(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, act, in_scale,
+                                              _stream()), "fgdm_conv_small_cin")
+    return y
+
+
+def conv_direct(x, w, bias, cout, stride=1, act=ACT_NONE):
+    nb, h, wd, cin = x.shape
+    y = torch.empty((nb, h // stride, wd // stride, cout), device=x.device, dtype=bf16)
+    _lib.check(_lib.load().fgdm_conv_direct(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, stride, act,
+                                           _stream()), "fgdm_conv_direct")
+    return y
+
+
+def conv_small_cout(x, w, bias, cout):
+    """x: NHWC bf16 -> NCHW fp32 [nb, cout, h, w] with cout in {3, 4}."""
+    nb, h, wd, cin = x.shape
+    y = torch.empty((nb, cout, h, wd), device=x.device, dtype=torch.float32)
+    _lib.check(_lib.load().fgdm_conv_small_cout(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, _stream()),
+               "fgdm_conv_small_cout")
+    return y
+
+
+def latent_affine(x, w, b, in_scale):
+    nb, c, h, wd = x.shape
+    y = torch.empty_like(x)
+    _lib.check(_lib.load().fgdm_latent_affine(_p(x), _p(w), _p(b), _p(y), nb, c, h * wd, in_scale, _stream()),
+               "fgdm_latent_affine")
+    return y
+
+
+def image_to_u8(x, mode):
+    nb, c, h, wd = x.shape
+    y = torch.empty((nb, h, wd, c), device=x.device, dtype=torch.uint8)
+    _lib.check(_lib.load().fgdm_image_to_u8(_p(x), _p(y), nb, c, h * wd, mode, _stream()), "fgdm_image_to_u8")
+    return y
+
+
+def resize_u8(src, dh, dw):
+    nb, sh, sw, c = src.shape
+    dst = torch.empty((nb, dh, dw, c), device=src.device, dtype=torch.uint8)
+    _lib.check(_lib.load().fgdm_resize_u8(_p(src), _p(dst), nb, sh, sw, dh, dw, c, _stream()), "fgdm_resize_u8")
+    return dst
+
+
+def u8_to_hint(src):
+    nb, h, wd, c = src.shape
+    dst = torch.empty((nb, c, h, wd), device=src.device, dtype=torch.float32)
+    _lib.check(_lib.load().fgdm_u8_to_hint(_p(src), _p(dst), nb, c, h * wd, _stream()), "fgdm_u8_to_hint")
+    return dst
+
+
+# ---------------------------------------------------------------------------------------------
+# weight packing (load time, torch plumbing): reference layouts -> the C ABI's packed layouts
+# ---------------------------------------------------------------------------------------------
+def pack_conv_weight(w: torch.Tensor) -> torch.Tensor:
+    """OIHW fp32 (nn.Conv2d) -> [O][kh*kw][I] bf16; Linear [O, I] passes through."""
+    if w.dim() == 4:
+        o, i, kh, kw = w.shape
+        w = w.permute(0, 2, 3, 1).reshape(o, kh * kw * i)
+    return w.contiguous().to(bf16)
+
+
+def pack_geglu(w: torch.Tensor, b: torch.Tensor):
+    """GEGLU proj [2*inner, dim] (value rows then gate rows, attention.py:40-44) -> rows interleaved
+    per 128-column tile (64 value rows, then the matching 64 gate rows); bias likewise."""
+    inner = w.shape[0] // 2
+    assert inner % 64 == 0, "GEGLU inner dim must be a multiple of 64"
+    wx, wg = w[:inner].reshape(inner // 64, 64, -1), w[inner:].reshape(inner // 64, 64, -1)
+    wi = torch.cat([wx, wg], dim=1).reshape(2 * inner, -1)
+    bx, bg = b[:inner].reshape(inner // 64, 64), b[inner:].reshape(inner // 64, 64)
+    bi = torch.cat([bx, bg], dim=1).reshape(2 * inner)
+    return wi.contiguous().to(bf16), bi.contiguous().float()
+
+
+def timestep_freqs(dim: int, max_period: float = 10000.0) -> torch.Tensor:
+    """Frequency table exactly as util.py:171-173 computes it (fp32 on the host)."""
+    half = dim // 2
+    return torch.exp(-math.log(max_period) * torch.arange(start=0, end=half, dtype=torch.float32) / half)

@@ -1,0 +1,150 @@
+/*
+ * fgdm_b200 — C ABI of the B200-native FG-DM sampling hot path (libfgdm_b200.so).
+ *
+ * The reference (DeepakSridhar/fgdm) is pure Python/PyTorch and has no FFI of its own: its plugin
+ * boundary is `instantiate_from_config` (ldm/util.py:78-93) plus the two method signatures
+ * `LatentDiffusion.apply_model` (ldm/models/diffusion/ddpm.py:1035-1136) and `DDIMSampler.sample`
+ * (ldm/models/diffusion/ddim.py:57-114). The host side of this repo (python package `fgdm_b200`)
+ * mirrors those classes; every device operation they perform goes through the entry points below.
+ * Each entry point names the reference call site whose ATen/cuDNN/cuBLAS work it replaces.
+ *
+ * Conventions
+ *  - all pointers are DEVICE pointers unless stated otherwise; `stream` is a cudaStream_t passed as void*.
+ *  - activations are NHWC bf16 ("nhwc"), latents/images at the model boundary are NCHW fp32 like the
+ *    reference's tensors; weights are packed [Cout][kh*kw][Cin] bf16 (Linear: [out][in]).
+ *  - every function returns 0 on success, a negative value on error; fgdm_last_error() returns a
+ *    thread-local, NUL-terminated description. No C++ exception crosses this boundary.
+ *  - no entry point allocates, synchronises or touches the host: all are CUDA-graph capturable.
+ *  - there is NO CPU fallback: without an sm_100a device every compute entry point fails.
+ */
+#ifndef FGDM_B200_H_
+#define FGDM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FGDM_ABI_VERSION 1
+
+const char* fgdm_last_error(void);
+int fgdm_abi_version(void);
+/* 0 when device 0 is an sm_100 class GPU and the driver exposes cuTensorMapEncodeTiled. */
+int fgdm_device_check(void);
+
+/* Output layout of fgdm_conv_gemm */
+enum {
+  FGDM_OUT_BF16 = 0,   /* out[m, col_off + n] bf16, row stride ldo */
+  FGDM_OUT_GEGLU = 1,  /* weights row-interleaved per 128 (64 value rows, 64 gate rows): out = x * gelu(gate) */
+  FGDM_OUT_QKV = 2,    /* q/k -> [img, head, tok, d]; v -> transposed [img, head, d, tok_pad] */
+  FGDM_OUT_F32 = 3     /* out[m, n] fp32 */
+};
+enum { FGDM_ACT_NONE = 0, FGDM_ACT_SILU = 1, FGDM_ACT_RELU = 2 };
+/* A-operand addressing of fgdm_conv_gemm */
+enum {
+  FGDM_CONV_1X1 = 0,      /* Linear / 1x1 conv */
+  FGDM_CONV_3X3 = 1,      /* 3x3, stride 1, pad 1 */
+  FGDM_CONV_3X3_S2 = 2    /* 3x3, stride 2, pad 1 on a phase-split input (fgdm_resample mode 2) */
+};
+
+typedef struct {
+  /* A: one or two NHWC bf16 sources, concatenated along channels (th.cat, openaimodel.py:869) */
+  const void* a0;
+  const void* a1;          /* NULL when c1 == 0 */
+  int c0, c1;              /* multiples of 64 */
+  int nb, h, w;            /* OUTPUT image view: M = nb*h*w rows (for stride 2: the halved size) */
+  int conv;                /* FGDM_CONV_* */
+  /* B: packed weights [n][taps*(c0+c1)] bf16 */
+  const void* weight;
+  int n;                   /* output channels, multiple of 32 */
+  /* epilogue: v = alpha*(acc + bias[n] + rowvec[img,n]); v = act(v); v += res0[m,n] + res1[m,n] */
+  const float* bias;       /* [n] or NULL */
+  const float* rowvec;     /* [images, ld_rowvec] or NULL: per-image vector (time embedding, openaimodel.py:288-298) */
+  int ld_rowvec;
+  int rows_per_img;        /* rows (tokens/pixels) per image for rowvec / QKV indexing; 0 -> h*w */
+  const void* res0;        /* bf16 [M, ld_res0] or NULL */
+  int ld_res0;
+  const void* res1;        /* bf16 [M, ld_res1] or NULL */
+  int ld_res1;
+  float alpha;
+  int act;                 /* FGDM_ACT_* */
+  int out_mode;            /* FGDM_OUT_* */
+  void* out;
+  int ldo;
+  int col_off;
+  /* FGDM_OUT_QKV only */
+  void* q_out;
+  void* k_out;
+  void* vt_out;
+  int qkv_first;           /* 0: weight rows are [q|k|v]; 1: [k|v] */
+  int heads, dhead;
+  int tok_pad;
+  int bn_hint;             /* N tile (0 = auto; 64/128/160/256) */
+} fgdm_gemm_args;
+
+/* nn.Conv2d / nn.Linear call sites: openaimodel.py:224,250,261,112,164-166; attention.py:40,60,
+ * 161-168,258-273; adapter.py:285-293; cldm.py:789-790; model.py:92-119. tcgen05 implicit GEMM. */
+int fgdm_conv_gemm(const fgdm_gemm_args* args, void* stream);
+
+/* CrossAttention core (attention.py:189-202; controlnet/ldm/modules/attention.py:171-190).
+ * q [images, heads, nq, d], k [images, heads, nk, d], vt [images, heads, d, tok_pad], out [images, nq, heads*d]. */
+int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int nq, int nk,
+                   int d, int tok_pad, float scale, void* stream);
+
+/* GroupNorm32 (+SiLU): util.py:223-225, openaimodel.py:221-224; attention.py:76-77; model.py:33-39.
+ * x0/x1 virtual channel concat; workspace >= nb*64*groups*8 bytes. */
+int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
+                   int nb, int hw, int c0, int c1, int groups, float eps, int silu, void* stream);
+
+/* nn.LayerNorm over channels of [rows, c] tokens: attention.py:226-228. */
+int fgdm_layernorm(const void* x, void* y, const float* gamma, const float* beta, int rows, int c, float eps,
+                   void* stream);
+
+/* fp32 logits [rows, cols] * scale -> bf16 softmax rows (VAE AttnBlock, model.py:186-188). */
+int fgdm_softmax_rows(const float* s, void* p, int rows, int cols, float scale, void* stream);
+
+/* CFG combine + DDIM update: ddim.py:243,249-268; ddim_hacked.py:192,207-230.
+ * coef_table fp32 [steps][5] = {sqrt(1-a_t), sqrt(a_t), sqrt(a_prev), sqrt(1-a_prev-sigma^2), sigma}. */
+int fgdm_cfg_ddim_step(const float* e_uncond, const float* e_cond, const float* x, const float* noise,
+                       const float* coef_table, const int* index_ptr, int index, float scale, float temperature,
+                       float* x_prev, float* pred_x0, int n, void* stream);
+
+/* timestep_embedding: util.py:160-180. t int64 [rows]; freqs fp32 [dim/2]; out fp32 [rows, dim]. */
+int fgdm_timestep_embedding(const int64_t* t, const float* freqs, float* out, int rows, int dim, void* stream);
+
+/* Skinny fp32 Linear y = out_act(in_act(x) W^T + b): time_embed (openaimodel.py:538-542) and the
+ * batched ResBlock emb_layers (openaimodel.py:238-244). act flags: 0 none, 1 SiLU. */
+int fgdm_skinny_linear(const float* x, const float* w, const float* b, float* y, int rows, int k, int n, int in_act,
+                       int out_act, void* stream);
+
+/* NHWC bf16 resampling. mode 0: nearest 2x up (openaimodel.py:123, model.py:53); 1: 2x2 avg pool
+ * (adapter.py:270-277); 2: phase split for stride-2 convs -> [4, nb, h/2, w/2, c]. */
+int fgdm_resample(const void* in, void* out, int nb, int h, int w, int c, int mode, void* stream);
+
+int fgdm_add_bf16(const void* a, const void* b, void* out, size_t n, void* stream);
+
+/* 3x3 conv, NCHW fp32 input with cin in {3,4} (scaled by in_scale) -> NHWC bf16: openaimodel.py:561,
+ * adapter.py:332, cldm.py:645,656; model.py:488. */
+int fgdm_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
+                        int cout, int act, float in_scale, void* stream);
+/* 3x3 direct conv NHWC bf16 -> NHWC bf16, stride 1/2 (ControlNet hint stem, cldm.py:656-666). */
+int fgdm_conv_direct(const void* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
+                     int cout, int stride, int act, void* stream);
+/* 3x3 conv NHWC bf16 -> NCHW fp32 with cout in {3,4}: openaimodel.py:727; model.py:529. */
+int fgdm_conv_small_cout(const void* x, const void* w, const float* bias, float* y, int nb, int h, int w_, int cin,
+                         int cout, void* stream);
+/* y = W (x*in_scale) + b on an NCHW fp32 latent, c <= 8: ddpm.py:839 + autoencoder.py:331. */
+int fgdm_latent_affine(const float* x, const float* w, const float* b, float* y, int nb, int c, int hw,
+                       float in_scale, void* stream);
+
+/* Factor hand-off (txt2img_fgdm_inference.py:245-261; initialize_cn.py:77-80,98-99). */
+int fgdm_image_to_u8(const float* x, void* y, int nb, int c, int hw, int mode, void* stream);
+int fgdm_resize_u8(const void* src, void* dst, int nb, int sh, int sw, int dh, int dw, int c, void* stream);
+int fgdm_u8_to_hint(const void* src, float* dst, int nb, int c, int hw, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FGDM_B200_H_ */

@@ -1,0 +1,275 @@
+"""GPU parity tests of every C-ABI kernel against a plain torch fp32 statement of the same op.
+
+Tolerances: bf16 storage (8 mantissa bits) with fp32 accumulation -> max error relative to the
+output's max magnitude <= 1.5e-2 for GEMM-shaped ops, 1e-2 for norms; exact for integer work.
+"""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from fgdm_b200 import _lib, ops
+
+DEV = "cuda"
+
+
+def relerr(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+
+
+def nhwc(x):  # NCHW fp32 -> NHWC bf16
+    return x.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+
+
+def nchw(x):  # NHWC -> NCHW fp32
+    return x.float().permute(0, 3, 1, 2).contiguous()
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _dev():
+    _lib.require_device()
+    torch.manual_seed(0)
+
+
+@pytest.mark.parametrize("m,k,n,bn", [(128, 64, 64, 0), (256, 128, 128, 0), (1232, 768, 640, 0), (4096, 320, 320, 0),
+                                      (8192, 1280, 1280, 0), (512, 640, 2560, 128), (300, 192, 96, 0)])
+def test_linear(m, k, n, bn):
+    x = torch.randn(m, k, device=DEV)
+    w = torch.randn(n, k, device=DEV) / math.sqrt(k)
+    b = torch.randn(n, device=DEV)
+    xb, wb = x.to(torch.bfloat16), w.to(torch.bfloat16)
+    y = ops.conv_gemm(xb, wb, n, bias=b, bn_hint=bn)
+    ref = xb.float() @ wb.float().t() + b
+    assert y.shape == (m, n)
+    assert relerr(y, ref) < 1e-2
+
+
+def test_linear_epilogues():
+    m, k, n = 512, 256, 320
+    x = torch.randn(m, k, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(n, k, device=DEV) / math.sqrt(k)).to(torch.bfloat16)
+    b = torch.randn(n, device=DEV)
+    r0 = torch.randn(m, n, device=DEV).to(torch.bfloat16)
+    r1 = torch.randn(m, n, device=DEV).to(torch.bfloat16)
+    rv = torch.randn(4, n, device=DEV)
+    y = ops.conv_gemm(x, w, n, bias=b, rowvec=rv, rows_per_img=128, res0=r0, res1=r1, alpha=0.5, act=ops.ACT_RELU)
+    ref = (x.float() @ w.float().t() + b + rv.repeat_interleave(128, 0)) * 0.5
+    ref = ref.relu() + r0.float() + r1.float()
+    assert relerr(y, ref) < 1e-2
+    y32 = ops.conv_gemm(x, w, n, out_mode=ops.OUT_F32)
+    assert y32.dtype == torch.float32
+    assert relerr(y32, x.float() @ w.float().t()) < 1e-4
+
+
+@pytest.mark.parametrize("nb,h,w,cin,cout", [(2, 8, 8, 64, 64), (2, 16, 16, 128, 160), (1, 32, 32, 64, 320),
+                                             (2, 64, 64, 320, 320), (1, 128, 128, 128, 128), (1, 4, 4, 64, 64),
+                                             (3, 8, 8, 64, 96)])
+def test_conv3x3(nb, h, w, cin, cout):
+    x = torch.randn(nb, cin, h, w, device=DEV)
+    wt = torch.randn(cout, cin, 3, 3, device=DEV) / math.sqrt(9 * cin)
+    b = torch.randn(cout, device=DEV)
+    xb = nhwc(x)
+    y = ops.conv_gemm(xb, ops.pack_conv_weight(wt), cout, conv=ops.CONV_3X3, bias=b).view(nb, h, w, cout)
+    ref = F.conv2d(nchw(xb), wt.to(torch.bfloat16).float(), b, padding=1)
+    assert relerr(nchw(y), ref) < 1e-2
+
+
+def test_conv3x3_concat_and_temb():
+    nb, h, w, c0, c1, cout = 2, 16, 16, 128, 64, 128
+    x0 = torch.randn(nb, c0, h, w, device=DEV)
+    x1 = torch.randn(nb, c1, h, w, device=DEV)
+    wt = torch.randn(cout, c0 + c1, 3, 3, device=DEV) / math.sqrt(9 * (c0 + c1))
+    b = torch.randn(cout, device=DEV)
+    temb = torch.randn(nb, cout, device=DEV)
+    a0, a1 = nhwc(x0), nhwc(x1)
+    y = ops.conv_gemm(a0, ops.pack_conv_weight(wt), cout, conv=ops.CONV_3X3, a1=a1, bias=b, rowvec=temb)
+    ref = F.conv2d(torch.cat([nchw(a0), nchw(a1)], 1), wt.to(torch.bfloat16).float(), b, padding=1)
+    ref = ref + temb[:, :, None, None]
+    assert relerr(nchw(y.view(nb, h, w, cout)), ref) < 1e-2
+
+
+@pytest.mark.parametrize("nb,h,w,c", [(2, 16, 16, 64), (2, 64, 64, 320), (1, 8, 8, 128)])
+def test_conv3x3_stride2(nb, h, w, c):
+    x = torch.randn(nb, c, h, w, device=DEV)
+    wt = torch.randn(c, c, 3, 3, device=DEV) / math.sqrt(9 * c)
+    b = torch.randn(c, device=DEV)
+    xb = nhwc(x)
+    ph = ops.resample(xb, 2)
+    y = ops.conv_gemm(ph, ops.pack_conv_weight(wt), c, conv=ops.CONV_3X3_S2, nb=nb, h=h // 2, w=w // 2, bias=b)
+    ref = F.conv2d(nchw(xb), wt.to(torch.bfloat16).float(), b, stride=2, padding=1)
+    assert relerr(nchw(y.view(nb, h // 2, w // 2, c)), ref) < 1e-2
+
+
+def test_geglu():
+    m, k, inner = 512, 320, 1280
+    x = torch.randn(m, k, device=DEV).to(torch.bfloat16)
+    w = torch.randn(2 * inner, k, device=DEV) / math.sqrt(k)
+    b = torch.randn(2 * inner, device=DEV)
+    wi, bi = ops.pack_geglu(w, b)
+    y = ops.conv_gemm(x, wi, 2 * inner, bias=bi, out_mode=ops.OUT_GEGLU)
+    proj = x.float() @ w.to(torch.bfloat16).float().t() + b
+    a, g = proj.chunk(2, dim=-1)
+    assert y.shape == (m, inner)
+    assert relerr(y, a * F.gelu(g)) < 1e-2
+
+
+def _attn_ref(q, k, v, scale):
+    s = torch.einsum("bhid,bhjd->bhij", q.float(), k.float()) * scale
+    return torch.einsum("bhij,bhjd->bhid", s.softmax(-1), v.float())
+
+
+@pytest.mark.parametrize("images,heads,nq,nk,d", [(2, 8, 4096, 4096, 40), (2, 8, 1024, 1024, 80), (2, 8, 256, 256, 160),
+                                                  (2, 8, 64, 64, 160), (2, 8, 4096, 77, 40), (2, 8, 256, 77, 160),
+                                                  (1, 2, 128, 128, 8), (1, 4, 64, 77, 32), (1, 1, 256, 384, 64)])
+def test_attention(images, heads, nq, nk, d):
+    q = torch.randn(images, heads, nq, d, device=DEV).to(torch.bfloat16)
+    k = torch.randn(images, heads, nk, d, device=DEV).to(torch.bfloat16)
+    v = torch.randn(images, heads, nk, d, device=DEV).to(torch.bfloat16)
+    tok_pad = (nk + 7) // 8 * 8
+    vt = torch.zeros(images, heads, d, tok_pad, device=DEV, dtype=torch.bfloat16)
+    vt[..., :nk] = v.transpose(-1, -2)
+    out = torch.empty(images, nq, heads * d, device=DEV, dtype=torch.bfloat16)
+    ops.attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad)
+    ref = _attn_ref(q, k, v, d ** -0.5).permute(0, 2, 1, 3).reshape(images, nq, heads * d)
+    assert relerr(out, ref) < 1.5e-2
+
+
+def test_qkv_projection_layouts():
+    images, n, c, heads = 2, 256, 320, 8
+    d = c // heads
+    x = torch.randn(images * n, c, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(3 * c, c, device=DEV) / math.sqrt(c)).to(torch.bfloat16)
+    q = torch.empty(images, heads, n, d, device=DEV, dtype=torch.bfloat16)
+    k = torch.empty_like(q)
+    vt = torch.empty(images, heads, d, n, device=DEV, dtype=torch.bfloat16)
+    ops.conv_gemm(x, w, 3 * c, rows_per_img=n, out_mode=ops.OUT_QKV, qkv=(q, k, vt, 0, heads, d, n))
+    ref = (x.float() @ w.float().t()).view(images, n, 3, heads, d)
+    assert relerr(q, ref[:, :, 0].permute(0, 2, 1, 3)) < 1e-2
+    assert relerr(k, ref[:, :, 1].permute(0, 2, 1, 3)) < 1e-2
+    assert relerr(vt, ref[:, :, 2].permute(0, 2, 3, 1)) < 1e-2
+
+
+@pytest.mark.parametrize("nb,h,w,c0,c1,silu,eps", [(2, 64, 64, 320, 0, True, 1e-5), (2, 16, 16, 1280, 640, True, 1e-5),
+                                                   (1, 8, 8, 64, 0, False, 1e-6), (1, 128, 128, 128, 0, True, 1e-6),
+                                                   (3, 32, 32, 640, 320, False, 1e-5)])
+def test_groupnorm(nb, h, w, c0, c1, silu, eps):
+    x0 = nhwc(torch.randn(nb, c0, h, w, device=DEV) * 2 + 0.5)
+    x1 = nhwc(torch.randn(nb, c1, h, w, device=DEV)) if c1 else None
+    g = torch.randn(c0 + c1, device=DEV)
+    b = torch.randn(c0 + c1, device=DEV)
+    y = ops.groupnorm(x0, g, b, x1=x1, eps=eps, silu=silu)
+    xin = nchw(x0) if x1 is None else torch.cat([nchw(x0), nchw(x1)], 1)
+    ref = F.group_norm(xin, 32, g, b, eps)
+    if silu:
+        ref = F.silu(ref)
+    assert relerr(nchw(y), ref) < 1e-2
+
+
+@pytest.mark.parametrize("rows,c", [(4096, 320), (1024, 640), (256, 1280), (100, 64)])
+def test_layernorm(rows, c):
+    x = (torch.randn(rows, c, device=DEV) * 3 + 1).to(torch.bfloat16)
+    g = torch.randn(c, device=DEV)
+    b = torch.randn(c, device=DEV)
+    y = ops.layernorm(x, g, b)
+    assert relerr(y, F.layer_norm(x.float(), (c,), g, b, 1e-5)) < 1e-2
+
+
+def test_softmax_rows():
+    s = torch.randn(512, 4096, device=DEV) * 20
+    p = ops.softmax_rows(s, 0.1)
+    assert relerr(p, (s * 0.1).softmax(-1)) < 1e-2
+
+
+def test_cfg_ddim():
+    b = 8
+    eu, ec, x = (torch.randn(b, 4, 64, 64, device=DEV) for _ in range(3))
+    table = torch.rand(50, 5, device=DEV) + 0.1
+    xp, p0 = ops.cfg_ddim_step(eu, ec, x, table, 7, 7.5)
+    s1m, sa, sap, dirc, sig = table[7]
+    e = eu + 7.5 * (ec - eu)
+    x0 = (x - s1m * e) / sa
+    torch.testing.assert_close(p0, x0, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(xp, sap * x0 + dirc * e, rtol=1e-5, atol=1e-5)
+    idx = torch.tensor([7], device=DEV, dtype=torch.int32)
+    xp2, _ = ops.cfg_ddim_step(eu, ec, x, table, 0, 7.5, index_ptr=idx)
+    assert torch.equal(xp, xp2)
+
+
+def test_timestep_embedding_and_skinny_linear():
+    t = torch.tensor([1, 21, 981, 500], device=DEV, dtype=torch.int64)
+    freqs = ops.timestep_freqs(320).to(DEV)
+    emb = ops.timestep_embedding(t, freqs, 320)
+    args = t[:, None].float() * freqs[None]
+    ref = torch.cat([torch.cos(args), torch.sin(args)], -1)
+    torch.testing.assert_close(emb, ref, rtol=1e-4, atol=2e-4)
+    w = torch.randn(1280, 320, device=DEV) / 18
+    b = torch.randn(1280, device=DEV)
+    y = ops.skinny_linear(emb, w, b, in_act=True, out_act=True)
+    torch.testing.assert_close(y, F.silu(F.silu(emb) @ w.t() + b), rtol=1e-3, atol=1e-3)
+    x19 = torch.randn(19, 320, device=DEV)
+    torch.testing.assert_close(ops.skinny_linear(x19, w, None), x19 @ w.t(), rtol=1e-3, atol=1e-3)
+
+
+def test_resample_modes():
+    x = nhwc(torch.randn(2, 64, 8, 8, device=DEV))
+    up = ops.resample(x, 0)
+    assert torch.equal(nchw(up), F.interpolate(nchw(x), scale_factor=2, mode="nearest"))
+    pool = ops.resample(x, 1)
+    assert relerr(nchw(pool), F.avg_pool2d(nchw(x), 2)) < 1e-2
+    ph = ops.resample(x, 2)
+    xr = x.view(2, 4, 2, 4, 2, 64).permute(2, 4, 0, 1, 3, 5).reshape(4, 2, 4, 4, 64)
+    assert torch.equal(ph, xr)
+    assert relerr(ops.add_bf16(x, x), x.float() * 2) < 1e-2
+
+
+def test_small_convs():
+    x = torch.randn(2, 4, 32, 32, device=DEV)
+    w = torch.randn(320, 4, 3, 3, device=DEV) / 6
+    b = torch.randn(320, device=DEV)
+    y = ops.conv_small_cin(x, ops.pack_conv_weight(w), b, 320)
+    assert relerr(nchw(y), F.conv2d(x, w.to(torch.bfloat16).float(), b, padding=1)) < 1e-2
+    h3 = torch.rand(1, 3, 64, 64, device=DEV)
+    w3 = torch.randn(16, 3, 3, 3, device=DEV) / 5
+    y3 = ops.conv_small_cin(h3, ops.pack_conv_weight(w3), None, 16, act=ops.ACT_SILU)
+    assert relerr(nchw(y3), F.silu(F.conv2d(h3, w3.to(torch.bfloat16).float(), None, padding=1))) < 1e-2
+    # direct, stride 2
+    xd = nhwc(torch.randn(2, 16, 32, 32, device=DEV))
+    wd = torch.randn(32, 16, 3, 3, device=DEV) / 12
+    bd = torch.randn(32, device=DEV)
+    yd = ops.conv_direct(xd, ops.pack_conv_weight(wd), bd, 32, stride=2, act=ops.ACT_SILU)
+    assert relerr(nchw(yd), F.silu(F.conv2d(nchw(xd), wd.to(torch.bfloat16).float(), bd, stride=2, padding=1))) < 1e-2
+    # small cout
+    for cin, cout in [(320, 4), (128, 3), (64, 4)]:
+        xc = nhwc(torch.randn(2, cin, 16, 16, device=DEV))
+        wc = torch.randn(cout, cin, 3, 3, device=DEV) / math.sqrt(9 * cin)
+        bc = torch.randn(cout, device=DEV)
+        yc = ops.conv_small_cout(xc, ops.pack_conv_weight(wc), bc, cout)
+        assert relerr(yc, F.conv2d(nchw(xc), wc.to(torch.bfloat16).float(), bc, padding=1)) < 1e-2
+    z = torch.randn(2, 4, 8, 8, device=DEV)
+    wq = torch.randn(4, 4, device=DEV)
+    bq = torch.randn(4, device=DEV)
+    ya = ops.latent_affine(z, wq, bq, 1 / 0.18215)
+    torch.testing.assert_close(ya, F.conv2d(z / 0.18215, wq[:, :, None, None], bq), rtol=1e-4, atol=1e-4)
+
+
+def test_u8_handoff_bit_exact():
+    x = torch.randn(2, 3, 64, 64, device=DEV) * 0.8
+    u0 = ops.image_to_u8(x, 0)
+    ref0 = (255.0 * torch.clamp((x + 1.0) / 2.0, 0.0, 1.0)).permute(0, 2, 3, 1).cpu().numpy().astype("uint8")
+    assert (u0.cpu().numpy() == ref0).all()
+    u1 = ops.image_to_u8(x, 1)
+    ref1 = (x.permute(0, 2, 3, 1) * 127.5 + 127.5).cpu().numpy().clip(0, 255).astype("uint8")
+    assert (u1.cpu().numpy() == ref1).all()
+    hint = ops.u8_to_hint(u0)
+    assert torch.equal(hint, (u0.float() / 255.0).permute(0, 3, 1, 2))
+    cv2 = pytest.importorskip("cv2")
+    up = ops.resize_u8(u0, 128, 128).cpu().numpy()
+    for i in range(2):
+        ref = cv2.resize(u0[i].cpu().numpy(), (128, 128), interpolation=cv2.INTER_LINEAR)
+        assert (up[i] == ref).all()
+    same = ops.resize_u8(u0, 64, 64)
+    assert torch.equal(same, u0)
