@@ -89,8 +89,14 @@ FGDM_DEVINL bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Bounded spin: a protocol bug traps (launch error reported to the host) instead of hanging the GPU.
+#ifndef FGDM_SPIN_LIMIT
+#define FGDM_SPIN_LIMIT (1u << 26)
+#endif
 FGDM_DEVINL void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
+    if (++spins > FGDM_SPIN_LIMIT) __trap();
   }
 }
 

@@ -295,7 +295,7 @@ __global__ void u8_to_hint_kernel(const unsigned char* __restrict__ src, float* 
   const int c = i % C;
   const size_t p = i / C;
   const int px = p % HW, n = p / HW;
-  dst[(static_cast<size_t>(n) * C + c) * HW + px] = static_cast<float>(src[i]) / 255.0f;
+  dst[(static_cast<size_t>(n) * C + c) * HW + px] = static_cast<float>(src[i]) * (1.0f / 255.0f);  // torch's CUDA div-by-scalar multiplies by the reciprocal
 }
 
 int launch_u8_to_hint(const void* src, float* dst, int NB, int C, int HW, cudaStream_t stream) {

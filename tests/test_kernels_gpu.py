@@ -32,6 +32,8 @@ def nchw(x):  # NHWC -> NCHW fp32
 @pytest.fixture(scope="module", autouse=True)
 def _dev():
     _lib.require_device()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     torch.manual_seed(0)
 
 
