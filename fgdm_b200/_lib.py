@@ -49,7 +49,9 @@ SIGNATURES = {
     "fgdm_skinny_linear": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_resample": [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_add_bf16": [vp, vp, vp, C.c_size_t, vp],
-    "fgdm_conv_small_cin": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp],
+    "fgdm_conv_small_cin": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int,
+                            vp],
+    "fgdm_ddim_advance": [vp, vp, vp, vp, C.c_int, vp, vp],
     "fgdm_conv_direct": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_conv_small_cout": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_latent_affine": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp],
@@ -73,6 +75,8 @@ def load() -> C.CDLL:
     lib = C.CDLL(LIB_PATH)
     lib.fgdm_last_error.restype = C.c_char_p
     lib.fgdm_last_error.argtypes = []
+    lib.fgdm_launch_count.restype = C.c_longlong
+    lib.fgdm_launch_count.argtypes = []
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype = C.c_int

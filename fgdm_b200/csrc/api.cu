@@ -9,6 +9,7 @@
 namespace fgdm {
 
 static thread_local char g_err[512] = "";
+static long long g_launches = 0;   // kernels launched through this library (single host thread per process)
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -23,6 +24,7 @@ int check_launch(const char* what) {
     set_error("%s: launch failed: %s", what, cudaGetErrorString(e));
     return -1;
   }
+  ++g_launches;
   return 0;
 }
 
@@ -107,7 +109,9 @@ int launch_skinny_linear(const float* x, const float* w, const float* b, float* 
 int launch_resample(const void* in, void* out, int NB, int H, int W, int C, int mode, cudaStream_t stream);
 int launch_add_bf16(const void* a, const void* b, void* out, size_t n, cudaStream_t stream);
 int launch_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int NB, int H, int W, int Cin,
-                          int Cout, int act, float in_scale, cudaStream_t stream);
+                          int Cout, int act, float in_scale, int nb_in, cudaStream_t stream);
+int launch_ddim_advance(int* counter, const long long* t_table, const int* idx_table, long long* t_out, int rows,
+                        int* index_out, cudaStream_t stream);
 int launch_conv_direct(const void* x, const void* w, const float* bias, void* y, int NB, int H, int W, int Cin,
                        int Cout, int stride, int act, cudaStream_t stream);
 int launch_conv_small_cout(const void* x, const void* w, const float* bias, float* y, int NB, int H, int W, int Cin,
@@ -134,6 +138,7 @@ extern "C" {
 
 const char* fgdm_last_error(void) { return g_err; }
 int fgdm_abi_version(void) { return FGDM_ABI_VERSION; }
+long long fgdm_launch_count(void) { return g_launches; }
 
 int fgdm_device_check(void) {
   int count = 0;
@@ -283,10 +288,19 @@ int fgdm_add_bf16(const void* a, const void* b, void* out, size_t n, void* strea
 }
 
 int fgdm_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
-                        int cout, int act, float in_scale, void* stream) {
+                        int cout, int act, float in_scale, int nb_in, void* stream) {
   FGDM_NONNULL(x, "x"); FGDM_NONNULL(w, "w"); FGDM_NONNULL(y, "y");
-  return launch_conv_small_cin(x, w, bias, y, nb, h, w_, cin, cout, act, in_scale,
+  return launch_conv_small_cin(x, w, bias, y, nb, h, w_, cin, cout, act, in_scale, nb_in,
                                reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_ddim_advance(int* counter, const int64_t* t_table, const int* idx_table, int64_t* t_out, int rows,
+                      int* index_out, void* stream) {
+  FGDM_NONNULL(counter, "counter"); FGDM_NONNULL(t_table, "t_table"); FGDM_NONNULL(idx_table, "idx_table");
+  FGDM_NONNULL(t_out, "t_out"); FGDM_NONNULL(index_out, "index_out");
+  return launch_ddim_advance(counter, reinterpret_cast<const long long*>(t_table), idx_table,
+                             reinterpret_cast<long long*>(t_out), rows, index_out,
+                             reinterpret_cast<cudaStream_t>(stream));
 }
 
 int fgdm_conv_direct(const void* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,

@@ -56,6 +56,28 @@ int launch_cfg_ddim(const float* e_u, const float* e_c, const float* x, const fl
 }
 
 // ---------------------------------------------------------------------------------------------
+// Device-side loop bookkeeping (ddim.py:147-149) so a captured graph can be replayed per step.
+// ---------------------------------------------------------------------------------------------
+__global__ void ddim_advance_kernel(int* counter, const long long* __restrict__ t_table,
+                                    const int* __restrict__ idx_table, long long* __restrict__ t_out, int rows,
+                                    int* __restrict__ index_out) {
+  const int i = *counter;
+  const long long t = t_table[i];
+  for (int r = threadIdx.x; r < rows; r += blockDim.x) t_out[r] = t;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *index_out = idx_table[i];
+    *counter = i + 1;
+  }
+}
+
+int launch_ddim_advance(int* counter, const long long* t_table, const int* idx_table, long long* t_out, int rows,
+                        int* index_out, cudaStream_t stream) {
+  ddim_advance_kernel<<<1, 128, 0, stream>>>(counter, t_table, idx_table, t_out, rows, index_out);
+  return check_launch("ddim_advance_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
 // timestep_embedding (ldm/modules/diffusionmodules/util.py:160-180): out[r] = [cos(t f), sin(t f)]
 // with the frequency table computed on the host exactly as the reference does.
 // ---------------------------------------------------------------------------------------------

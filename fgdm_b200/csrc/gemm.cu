@@ -348,6 +348,10 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
 
 // Box geometry of one 128-row A tile in the [NB, H, W, C] image view.
 static bool tile_box(int NB, int H, int W, int* bn, int* bh, int* bw) {
+  if (NB == 1 && H == 1) {  // flat row matrix (Linear / 1x1): any row count, TMA zero-fills the tail
+    *bw = kBM; *bh = 1; *bn = 1;
+    return true;
+  }
   if (W >= kBM) {
     if ((NB > 1 || H > 1) && (W % kBM) != 0) return false;
     *bw = kBM; *bh = 1; *bn = 1;

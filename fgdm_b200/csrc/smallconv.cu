@@ -13,7 +13,7 @@ namespace fgdm {
 template <int CIN>
 __global__ void conv_small_cin_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                                       const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, int NB, int H,
-                                      int W, int Cout, int act, float in_scale) {
+                                      int W, int Cout, int act, float in_scale, int nb_in) {
   const int V = Cout / 8;
   const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t total = static_cast<size_t>(NB) * H * W * V;
@@ -22,7 +22,7 @@ __global__ void conv_small_cin_kernel(const float* __restrict__ x, const __nv_bf
   size_t p = i / V;
   const int ow = p % W; p /= W;
   const int oh = p % H;
-  const int n = p / H;
+  const int n = (p / H) % nb_in;   // output image r reads input image r % nb_in (shared CFG latent)
   float in[9][CIN];
 #pragma unroll
   for (int t = 0; t < 9; ++t) {
@@ -49,14 +49,15 @@ __global__ void conv_small_cin_kernel(const float* __restrict__ x, const __nv_bf
 }
 
 int launch_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int NB, int H, int W, int Cin,
-                          int Cout, int act, float in_scale, cudaStream_t stream) {
+                          int Cout, int act, float in_scale, int nb_in, cudaStream_t stream) {
   if (Cout % 8) { set_error("conv_small_cin: Cout=%d must be a multiple of 8", Cout); return -1; }
+  if (nb_in <= 0) nb_in = NB;
   const size_t total = static_cast<size_t>(NB) * H * W * (Cout / 8);
   const unsigned blocks = static_cast<unsigned>((total + 127) / 128);
   const __nv_bfloat16* wp = reinterpret_cast<const __nv_bfloat16*>(w);
   __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y);
-  if (Cin == 3) conv_small_cin_kernel<3><<<blocks, 128, 0, stream>>>(x, wp, bias, yp, NB, H, W, Cout, act, in_scale);
-  else if (Cin == 4) conv_small_cin_kernel<4><<<blocks, 128, 0, stream>>>(x, wp, bias, yp, NB, H, W, Cout, act, in_scale);
+  if (Cin == 3) conv_small_cin_kernel<3><<<blocks, 128, 0, stream>>>(x, wp, bias, yp, NB, H, W, Cout, act, in_scale, nb_in);
+  else if (Cin == 4) conv_small_cin_kernel<4><<<blocks, 128, 0, stream>>>(x, wp, bias, yp, NB, H, W, Cout, act, in_scale, nb_in);
   else { set_error("conv_small_cin: Cin=%d unsupported (3 or 4)", Cin); return -1; }
   return check_launch("conv_small_cin_kernel");
 }

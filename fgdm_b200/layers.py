@@ -1,0 +1,340 @@
+"""Host-side layer objects of the B200 path: parameter specs (reference names/shapes), weight packing
+and forward functions that only launch C-ABI kernels (fgdm_b200.ops).
+
+Activations are NHWC bf16 `[nb, h, w, c]`; tokens are the same memory viewed `[nb*h*w, c]`, so the
+reference's `rearrange(b c h w -> b (h w) c)` (ldm/modules/attention.py:283) costs nothing here.
+Parameter NAMES and SHAPES are the reference's (so its state_dicts load unchanged); the packed device
+layouts are ours. No layer falls back to torch arithmetic.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .ops import ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU, OUT_QKV
+
+bf16 = torch.bfloat16
+
+
+class Layer:
+    """A node of the parameter tree. Children are registered in `self.children` (name -> Layer); leaves
+    declare `self.params` (name -> shape)."""
+
+    def __init__(self):
+        self.children: dict[str, "Layer"] = {}
+        self.params: dict[str, tuple] = {}
+
+    def add(self, name: str, layer: "Layer") -> "Layer":
+        self.children[str(name)] = layer
+        return layer
+
+    def specs(self, prefix: str = ""):
+        for n, s in self.params.items():
+            yield prefix + n, tuple(s)
+        for n, c in self.children.items():
+            yield from c.specs(prefix + n + ".")
+
+    def load(self, sd, prefix: str, dev):
+        self._load(sd, prefix, dev)
+        for n, c in self.children.items():
+            c.load(sd, prefix + n + ".", dev)
+
+    def _load(self, sd, prefix, dev):
+        pass
+
+    @staticmethod
+    def _get(sd, key, shape):
+        if key not in sd:
+            raise KeyError(f"missing parameter {key}")
+        t = sd[key]
+        if tuple(t.shape) != tuple(shape):
+            raise ValueError(f"parameter {key}: shape {tuple(t.shape)} != expected {tuple(shape)}")
+        return t
+
+
+class Conv2d(Layer):
+    """nn.Conv2d / conv_nd parameters; packed [Cout][kh*kw][Cin] bf16 for the implicit-GEMM kernels."""
+
+    def __init__(self, cin, cout, k=3, stride=1):
+        super().__init__()
+        self.cin, self.cout, self.k, self.stride = cin, cout, k, stride
+        self.params = {"weight": (cout, cin, k, k), "bias": (cout,)}
+
+    def _load(self, sd, prefix, dev):
+        w = self._get(sd, prefix + "weight", self.params["weight"])
+        b = self._get(sd, prefix + "bias", self.params["bias"])
+        self.w = ops.pack_conv_weight(w.to(dev, torch.float32))
+        self.b = b.to(dev, torch.float32).contiguous()
+        self.w_raw = None
+
+    # tensor-core implicit GEMM; x may be a virtual concat (x, x1)
+    def gemm(self, x, x1=None, **kw):
+        nb, h, w, _ = x.shape
+        if self.k == 1:
+            y = ops.conv_gemm(x, self.w, self.cout, a1=x1, bias=self.b, nb=1, h=1, w=nb * h * w, **kw)
+            return y.view(nb, h, w, -1) if y is not None else None
+        if self.stride == 2:
+            ph = ops.resample(x, 2)
+            y = ops.conv_gemm(ph, self.w, self.cout, conv=CONV_3X3_S2, nb=nb, h=h // 2, w=w // 2, bias=self.b, **kw)
+            return y.view(nb, h // 2, w // 2, -1)
+        y = ops.conv_gemm(x, self.w, self.cout, conv=CONV_3X3, a1=x1, bias=self.b, **kw)
+        return y.view(nb, h, w, -1)
+
+
+class Linear(Layer):
+    def __init__(self, cin, cout, bias=True):
+        super().__init__()
+        self.cin, self.cout, self.has_bias = cin, cout, bias
+        self.params = {"weight": (cout, cin)}
+        if bias:
+            self.params["bias"] = (cout,)
+
+    def _load(self, sd, prefix, dev):
+        self.w32 = self._get(sd, prefix + "weight", self.params["weight"]).to(dev, torch.float32).contiguous()
+        self.b = (self._get(sd, prefix + "bias", self.params["bias"]).to(dev, torch.float32).contiguous()
+                  if self.has_bias else None)
+        self.w = None
+
+    def pack(self):
+        """bf16 copy for the tensor-core path (fp32 copy is dropped)."""
+        self.w = self.w32.to(bf16).contiguous()
+        self.w32 = None
+        return self
+
+
+class Norm(Layer):
+    """GroupNorm / LayerNorm affine parameters (fp32 on device)."""
+
+    def __init__(self, c):
+        super().__init__()
+        self.c = c
+        self.params = {"weight": (c,), "bias": (c,)}
+
+    def _load(self, sd, prefix, dev):
+        self.g = self._get(sd, prefix + "weight", (self.c,)).to(dev, torch.float32).contiguous()
+        self.b = self._get(sd, prefix + "bias", (self.c,)).to(dev, torch.float32).contiguous()
+
+
+class Seq(Layer):
+    """nn.Sequential / nn.ModuleList naming: children keyed by integer position."""
+
+    def __init__(self, items: dict | list):
+        super().__init__()
+        if isinstance(items, list):
+            items = dict(enumerate(items))
+        self.items = {}
+        for i, l in items.items():
+            if l is not None:
+                self.add(i, l)
+            self.items[i] = l
+
+    def __getitem__(self, i):
+        return self.children[str(i)]
+
+
+# ---------------------------------------------------------------------------------------------
+# ResBlock (ldm/modules/diffusionmodules/openaimodel.py:183-301; controlnet fork :162-275)
+# ---------------------------------------------------------------------------------------------
+class ResBlock(Layer):
+    def __init__(self, cin, emb_ch, cout):
+        super().__init__()
+        self.cin, self.cout = cin, cout
+        self.in_layers = self.add("in_layers", Seq({0: Norm(cin), 2: Conv2d(cin, cout, 3)}))
+        self.emb_layers = self.add("emb_layers", Seq({1: Linear(emb_ch, cout)}))
+        self.out_layers = self.add("out_layers", Seq({0: Norm(cout), 3: Conv2d(cout, cout, 3)}))
+        self.skip = self.add("skip_connection", Conv2d(cin, cout, 1)) if cin != cout else None
+        self.emb_off = -1   # column offset into the batched emb_layers output (set by the owning net)
+
+    def forward(self, x, x1, emb_all, res1=None):
+        """x (+ optional concat partner x1): NHWC bf16. emb_all: fp32 [R, total] batched emb_layers output.
+        Returns skip(x) + h (+ res1), openaimodel.py:275-301."""
+        n1, c1 = self.in_layers[0], self.in_layers[2]
+        n2, c2 = self.out_layers[0], self.out_layers[3]
+        h = ops.groupnorm(x, n1.g, n1.b, x1=x1, eps=1e-5, silu=True)
+        rv = emb_all[:, self.emb_off:self.emb_off + self.cout]
+        h = c1.gemm(h, rowvec=rv)                                   # conv + bias + emb[:, :, None, None]
+        h = ops.groupnorm(h, n2.g, n2.b, eps=1e-5, silu=True)
+        s = self.skip.gemm(x, x1) if self.skip is not None else x
+        return c2.gemm(h, res0=s, res1=res1)
+
+
+# ---------------------------------------------------------------------------------------------
+# CrossAttention / BasicTransformerBlock / SpatialTransformer (ldm/modules/attention.py:152-292)
+# ---------------------------------------------------------------------------------------------
+class CrossAttention(Layer):
+    def __init__(self, query_dim, context_dim, heads, dim_head):
+        super().__init__()
+        inner = heads * dim_head
+        self.heads, self.d, self.inner = heads, dim_head, inner
+        self.is_self = context_dim is None
+        cdim = query_dim if context_dim is None else context_dim
+        self.to_q = self.add("to_q", Linear(query_dim, inner, bias=False))
+        self.to_k = self.add("to_k", Linear(cdim, inner, bias=False))
+        self.to_v = self.add("to_v", Linear(cdim, inner, bias=False))
+        self.to_out = self.add("to_out", Seq({0: Linear(inner, query_dim)}))
+
+    def load(self, sd, prefix, dev):
+        super().load(sd, prefix, dev)
+        q, k, v = self.to_q.w32, self.to_k.w32, self.to_v.w32
+        if self.is_self:
+            self.w_qkv = torch.cat([q, k, v], 0).to(bf16).contiguous()
+        else:
+            self.w_q = q.to(bf16).contiguous()
+            self.w_kv = torch.cat([k, v], 0).to(bf16).contiguous()
+        self.to_q.w32 = self.to_k.w32 = self.to_v.w32 = None
+        self.to_out[0].pack()
+
+    def project_context(self, ctx):
+        """ctx: bf16 [R, L, cdim] -> (k [R,heads,L,d], vt [R,heads,d,Lpad], L). Step-invariant."""
+        r, L, cd = ctx.shape
+        lp = (L + 7) // 8 * 8
+        k = torch.empty((r, self.heads, L, self.d), device=ctx.device, dtype=bf16)
+        vt = torch.empty((r, self.heads, self.d, lp), device=ctx.device, dtype=bf16)
+        ops.conv_gemm(ctx.view(r * L, cd), self.w_kv, 2 * self.inner, out_mode=OUT_QKV, rows_per_img=L,
+                      qkv=(None, k, vt, 1, self.heads, self.d, lp))
+        return k, vt, L
+
+    def forward(self, xn, resid, nimg, ntok, kv=None):
+        """xn: normalised tokens [nimg*ntok, C]; resid: tokens added after to_out. kv: projected context."""
+        dev = xn.device
+        q = torch.empty((nimg, self.heads, ntok, self.d), device=dev, dtype=bf16)
+        if self.is_self:
+            tp = (ntok + 7) // 8 * 8
+            k = torch.empty((nimg, self.heads, ntok, self.d), device=dev, dtype=bf16)
+            vt = torch.empty((nimg, self.heads, self.d, tp), device=dev, dtype=bf16)
+            ops.conv_gemm(xn, self.w_qkv, 3 * self.inner, out_mode=OUT_QKV, rows_per_img=ntok,
+                          qkv=(q, k, vt, 0, self.heads, self.d, tp))
+            nk = ntok
+        else:
+            k, vt, nk = kv
+            tp = vt.shape[-1]
+            ops.conv_gemm(xn, self.w_q, self.inner, out_mode=OUT_QKV, rows_per_img=ntok,
+                          qkv=(q, q, q, 0, self.heads, self.d, tp))
+        a = torch.empty((nimg * ntok, self.inner), device=dev, dtype=bf16)
+        ops.attention(q, k, vt, a, nimg, self.heads, ntok, nk, self.d, tp)
+        o = self.to_out[0]
+        return ops.conv_gemm(a, o.w, o.cout, bias=o.b, res0=resid)
+
+
+class GEGLU(Layer):
+    def __init__(self, dim, inner):
+        super().__init__()
+        self.inner = inner
+        self.proj = self.add("proj", Linear(dim, 2 * inner))
+
+    def load(self, sd, prefix, dev):
+        super().load(sd, prefix, dev)
+        self.w, self.b = ops.pack_geglu(self.proj.w32, self.proj.b)
+        self.proj.w32 = None
+
+
+class FeedForward(Layer):
+    def __init__(self, dim, mult=4):
+        super().__init__()
+        inner = dim * mult
+        self.net = self.add("net", Seq({0: GEGLU(dim, inner), 2: Linear(inner, dim)}))
+
+    def load(self, sd, prefix, dev):
+        super().load(sd, prefix, dev)
+        self.net[2].pack()
+
+    def forward(self, xn, resid):
+        g = self.net[0]
+        h = ops.conv_gemm(xn, g.w, 2 * g.inner, bias=g.b, out_mode=OUT_GEGLU)      # x * gelu(gate)
+        o = self.net[2]
+        return ops.conv_gemm(h, o.w, o.cout, bias=o.b, res0=resid)
+
+
+class BasicTransformerBlock(Layer):
+    def __init__(self, dim, heads, d_head, context_dim):
+        super().__init__()
+        self.attn1 = self.add("attn1", CrossAttention(dim, None, heads, d_head))
+        self.ff = self.add("ff", FeedForward(dim))
+        self.attn2 = self.add("attn2", CrossAttention(dim, context_dim, heads, d_head))
+        self.norm1 = self.add("norm1", Norm(dim))
+        self.norm2 = self.add("norm2", Norm(dim))
+        self.norm3 = self.add("norm3", Norm(dim))
+
+    def forward(self, t, nimg, ntok, kv):
+        """BasicTransformerBlock._forward, attention.py:234-240."""
+        t = self.attn1.forward(ops.layernorm(t, self.norm1.g, self.norm1.b), t, nimg, ntok)
+        t = self.attn2.forward(ops.layernorm(t, self.norm2.g, self.norm2.b), t, nimg, ntok, kv)
+        return self.ff.forward(ops.layernorm(t, self.norm3.g, self.norm3.b), t)
+
+
+class SpatialTransformer(Layer):
+    def __init__(self, ch, heads, d_head, context_dim):
+        super().__init__()
+        self.ch = ch
+        self.norm = self.add("norm", Norm(ch))
+        self.proj_in = self.add("proj_in", Conv2d(ch, heads * d_head, 1))
+        self.blocks = self.add("transformer_blocks", Seq([BasicTransformerBlock(heads * d_head, heads, d_head,
+                                                                                   context_dim)]))
+        self.proj_out = self.add("proj_out", Conv2d(heads * d_head, ch, 1))
+        self.kv_slot = -1   # index into the per-call list of projected contexts
+
+    def project_context(self, ctx):
+        return self.blocks[0].attn2.project_context(ctx)
+
+    def forward(self, x, kvs, res1=None):
+        """SpatialTransformer.forward attention.py:275-292; GroupNorm eps 1e-6 (attention.py:76-77)."""
+        nb, h, w, c = x.shape
+        xn = ops.groupnorm(x, self.norm.g, self.norm.b, eps=1e-6, silu=False)
+        t = self.proj_in.gemm(xn).view(nb * h * w, -1)
+        t = self.blocks[0].forward(t, nb, h * w, kvs[self.kv_slot])
+        return self.proj_out.gemm(t.view(nb, h, w, -1), res0=x, res1=res1)
+
+
+class Downsample(Layer):
+    """openaimodel.py:146-180 (conv3x3 stride 2 pad 1)."""
+
+    def __init__(self, ch):
+        super().__init__()
+        self.op = self.add("op", Conv2d(ch, ch, 3, stride=2))
+
+    def forward(self, x):
+        return self.op.gemm(x)
+
+
+class Upsample(Layer):
+    """openaimodel.py:95-130; VAE model.py:42-57: nearest 2x then conv3x3."""
+
+    def __init__(self, ch):
+        super().__init__()
+        self.conv = self.add("conv", Conv2d(ch, ch, 3))
+
+    def forward(self, x):
+        return self.conv.gemm(ops.resample(x, 0))
+
+
+class TimeEmbed(Layer):
+    """time_embed = Linear, SiLU, Linear (openaimodel.py:538-542) on timestep_embedding (util.py:160-180)."""
+
+    def __init__(self, mc):
+        super().__init__()
+        self.mc = mc
+        self.add("0", Linear(mc, 4 * mc))
+        self.add("2", Linear(4 * mc, 4 * mc))
+
+    def _load(self, sd, prefix, dev):
+        self.freqs = ops.timestep_freqs(self.mc).to(dev)
+
+    def forward(self, t):
+        l0, l2 = self.children["0"], self.children["2"]
+        e = ops.timestep_embedding(t, self.freqs, self.mc)
+        e = ops.skinny_linear(e, l0.w32, l0.b, out_act=True)
+        return ops.skinny_linear(e, l2.w32, l2.b)
+
+
+def batch_emb_layers(resblocks, dev):
+    """Concatenate every ResBlock's emb_layers Linear (openaimodel.py:238-244) into one fp32 matrix so a
+    single skinny GEMM per step produces all per-block time-embedding vectors."""
+    ws, bs, off = [], [], 0
+    for rb in resblocks:
+        lin = rb.emb_layers[1]
+        ws.append(lin.w32)
+        bs.append(lin.b)
+        rb.emb_off = off
+        off += rb.cout
+        lin.w32 = None
+    return torch.cat(ws, 0).contiguous(), torch.cat(bs, 0).contiguous()

@@ -1,0 +1,554 @@
+"""Networks of the FG-DM sampling hot path, constructor- and state_dict-compatible with the reference:
+
+  UNetModel            ldm/modules/diffusionmodules/openaimodel.py:469-884 (FG-DM: Adapter self-prompting)
+  ControlNet           controlnet/cldm/cldm.py:545-813
+  ControlledUnetModel  controlnet/cldm/cldm.py:27-50
+  AutoencoderKL        ldm/models/autoencoder.py (decode only) + Decoder, ldm/modules/diffusionmodules/model.py:462-569
+
+They are the `target:` classes a maintainer points `instantiate_from_config` (ldm/util.py:78-93) at.
+Inputs/outputs at the model boundary are the reference's NCHW fp32 tensors; inside, everything is NHWC
+bf16 and every arithmetic op is a kernel of libfgdm_b200.so. Only inference (`no_grad`) is provided.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib, ops
+from .layers import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, OUT_F32, OUT_QKV, Conv2d, Downsample, Layer,
+                     Linear, Norm, ResBlock, Seq, SpatialTransformer, TimeEmbed, Upsample, batch_emb_layers, bf16)
+
+
+def _unsupported(**flags):
+    bad = {k: v for k, v in flags.items() if v}
+    if bad:
+        raise NotImplementedError(f"fgdm_b200 implements the SD-v1.4/FG-DM inference configuration only; "
+                                  f"unsupported constructor options: {bad}")
+
+
+class _Net(Layer):
+    """Common module-ish surface (enough of nn.Module for the reference's call sites)."""
+
+    def __init__(self):
+        super().__init__()
+        self.device = None
+        self._loaded = False
+
+    def param_shapes(self) -> dict:
+        return dict(self.specs(""))
+
+    def load_state_dict(self, sd, strict=True, prefix="", device=None):
+        dev = torch.device(device or "cuda")
+        _lib.require_device()
+        want = self.param_shapes()
+        missing = [k for k in want if prefix + k not in sd]
+        if missing:
+            raise KeyError(f"load_state_dict: {len(missing)} missing keys, e.g. {missing[:3]}")
+        if strict:
+            extra = [k for k in sd if k.startswith(prefix) and k[len(prefix):] not in want]
+            if extra:
+                raise KeyError(f"load_state_dict: {len(extra)} unexpected keys, e.g. {extra[:3]}")
+        with torch.no_grad():
+            self.load(sd, prefix, dev)
+            self._finalize(dev)
+        self.device = dev
+        self._loaded = True
+        return self
+
+    def _finalize(self, dev):
+        pass
+
+    # nn.Module look-alikes used by reference-side glue
+    def eval(self):
+        return self
+
+    def cuda(self, *a):
+        return self
+
+    def to(self, *a, **k):
+        return self
+
+    def parameters(self):
+        return iter(())
+
+    def __call__(self, *a, **k):
+        if not self._loaded:
+            raise RuntimeError("weights not loaded: call load_state_dict(reference_state_dict) first")
+        with torch.no_grad():
+            return self.forward(*a, **k)
+
+
+# ---------------------------------------------------------------------------------------------
+# UNet family
+# ---------------------------------------------------------------------------------------------
+class _AdapterBlock(Layer):
+    """ldm/modules/encoders/adapter.py:280-313 with ksize=1, sk=True, use_conv=False."""
+
+    def __init__(self, cin, cout, down):
+        super().__init__()
+        self.down = down
+        self.in_conv = self.add("in_conv", Conv2d(cin, cout, 1)) if cin != cout else None
+        self.block1 = self.add("block1", Conv2d(cout, cout, 3))
+        self.block2 = self.add("block2", Conv2d(cout, cout, 1))
+
+    def forward(self, x):
+        if self.down:
+            x = ops.resample(x, 1)                       # AvgPool2d(2), adapter.py:270-277
+        if self.in_conv is not None:
+            x = self.in_conv.gemm(x)
+        h = self.block1.gemm(x, act=ACT_RELU)
+        return self.block2.gemm(h, res0=x)
+
+
+class Adapter(Layer):
+    """Adapter(cin, channels=[320,640,1280,1280], nums_rb=2, ksize=1, sk=True, use_conv=False):
+    adapter.py:316-346 as instantiated at openaimodel.py:556."""
+
+    def __init__(self, cin, channels=(320, 640, 1280, 1280), nums_rb=2):
+        super().__init__()
+        self.channels, self.nums_rb = list(channels), nums_rb
+        body = []
+        for i in range(len(channels)):
+            for j in range(nums_rb):
+                if i != 0 and j == 0:
+                    body.append(_AdapterBlock(channels[i - 1], channels[i], True))
+                else:
+                    body.append(_AdapterBlock(channels[i], channels[i], False))
+        self.body = self.add("body", Seq(body))
+        self.conv_in = self.add("conv_in", Conv2d(cin, channels[0], 3))
+
+    def forward(self, x_nchw, rows):
+        """x_nchw: fp32 [nb_in, cin, h, w]; `rows` output images (input image index = row % nb_in)."""
+        x = ops.conv_small_cin(x_nchw, self.conv_in.w, self.conv_in.b, self.channels[0], nb_out=rows)
+        feats = []
+        for i in range(len(self.channels)):
+            for j in range(self.nums_rb):
+                x = self.body[i * self.nums_rb + j].forward(x)
+            feats.append(x)
+        return feats
+
+
+class _UNetBase(_Net):
+    def _build(self, in_channels, model_channels, out_channels, num_res_blocks, attention_resolutions, channel_mult,
+               num_heads, context_dim, decoder=True):
+        mc = model_channels
+        self.in_channels, self.model_channels, self.out_channels = in_channels, mc, out_channels
+        self.num_heads, self.context_dim = num_heads, context_dim
+        ted = 4 * mc
+        self.time_embed = self.add("time_embed", TimeEmbed(mc))
+        self._res, self._sts = [], []
+
+        def res(cin, cout):
+            r = ResBlock(cin, ted, cout)
+            self._res.append(r)
+            return r
+
+        def st(ch):
+            s = SpatialTransformer(ch, num_heads, ch // num_heads, context_dim)
+            s.kv_slot = len(self._sts)
+            self._sts.append(s)
+            return s
+
+        blocks = [Seq([Conv2d(in_channels, mc, 3)])]
+        chans = [mc]
+        ch, ds = mc, 1
+        for level, mult in enumerate(channel_mult):
+            for _ in range(num_res_blocks):
+                layers = [res(ch, mult * mc)]
+                ch = mult * mc
+                if ds in attention_resolutions:
+                    layers.append(st(ch))
+                blocks.append(Seq(layers))
+                chans.append(ch)
+            if level != len(channel_mult) - 1:
+                blocks.append(Seq([Downsample(ch)]))
+                chans.append(ch)
+                ds *= 2
+        self.input_blocks = self.add("input_blocks", Seq(blocks))
+        self.input_chans = list(chans)
+        self.middle_block = self.add("middle_block", Seq([res(ch, ch), st(ch), res(ch, ch)]))
+        self.mid_ch = ch
+        if not decoder:
+            return
+        outs = []
+        for level, mult in list(enumerate(channel_mult))[::-1]:
+            for i in range(num_res_blocks + 1):
+                ich = chans.pop()
+                layers = [res(ch + ich, mc * mult)]
+                ch = mc * mult
+                if ds in attention_resolutions:
+                    layers.append(st(ch))
+                if level and i == num_res_blocks:
+                    layers.append(Upsample(ch))
+                    ds //= 2
+                outs.append(Seq(layers))
+        self.output_blocks = self.add("output_blocks", Seq(outs))
+        self.out = self.add("out", Seq({0: Norm(ch), 2: Conv2d(mc, out_channels, 3)}))
+
+    def _finalize(self, dev):
+        self.w_emb, self.b_emb = batch_emb_layers(self._res, dev)
+
+    # -- step-invariant work: text K/V projections of every cross-attention (attention.py:162-163) --
+    def project_context(self, context):
+        """context: [R, L, context_dim] (any float dtype) -> per-SpatialTransformer (k, vt, L)."""
+        ctx = context.to(bf16).contiguous()
+        return [s.project_context(ctx) for s in self._sts]
+
+    def _emb(self, timesteps):
+        emb = self.time_embed.forward(timesteps.to(torch.int64).contiguous())
+        return ops.skinny_linear(emb, self.w_emb, self.b_emb, in_act=True)   # emb_layers = SiLU, Linear
+
+    def _run(self, blk, h, h1, emb_all, kvs, res1=None):
+        """TimestepEmbedSequential.forward (openaimodel.py:85-93). h1: concat partner of the first ResBlock.
+        res1 is added by the block's LAST layer's epilogue."""
+        n = len(blk.children)
+        for j, layer in enumerate(blk.children.values()):
+            r1 = res1 if j == n - 1 else None
+            if isinstance(layer, ResBlock):
+                h = layer.forward(h, h1, emb_all, res1=r1)
+                h1 = None
+            elif isinstance(layer, SpatialTransformer):
+                h = layer.forward(h, kvs, res1=r1)
+            else:
+                assert r1 is None
+                h = layer.forward(h)
+        return h
+
+    def _encode(self, x, rows, emb_all, kvs, fa=None, after_conv_in=None):
+        conv_in = self.input_blocks[0][0]
+        h = ops.conv_small_cin(x, conv_in.w, conv_in.b, self.model_channels, nb_out=rows)
+        if after_conv_in is not None:
+            h = after_conv_in(h)
+        hs = [h]
+        k = 0
+        for idx in range(1, len(self.input_blocks.children)):
+            r1 = None
+            if fa is not None and (idx + 1) % 3 == 0:
+                r1 = fa[k]
+                k += 1
+            h = self._run(self.input_blocks[idx], h, None, emb_all, kvs, res1=r1)
+            hs.append(h)
+        if fa is not None:
+            assert k == len(fa), "Wrong features_adapter"      # openaimodel.py:859
+        return h, hs
+
+    def _decode(self, h, hs, emb_all, kvs):
+        for idx in range(len(self.output_blocks.children)):
+            h = self._run(self.output_blocks[idx], h, hs.pop(), emb_all, kvs)
+        n, c = self.out[0], self.out[2]
+        h = ops.groupnorm(h, n.g, n.b, eps=1e-5, silu=True)
+        return ops.conv_small_cout(h, c.w, c.b, self.out_channels)
+
+
+class UNetModel(_UNetBase):
+    """FG-DM UNetModel (openaimodel.py:469-498 kwargs). forward(x, timesteps, context) -> eps, :808-884."""
+
+    def __init__(self, image_size=32, in_channels=4, model_channels=320, out_channels=4, num_res_blocks=2,
+                 attention_resolutions=(4, 2, 1), dropout=0, channel_mult=(1, 2, 4, 4), conv_resample=True, dims=2,
+                 num_classes=None, use_checkpoint=False, use_fp16=False, num_heads=-1, num_head_channels=-1,
+                 num_heads_upsample=-1, use_scale_shift_norm=False, resblock_updown=False,
+                 use_new_attention_order=False, use_spatial_transformer=False, transformer_depth=1, context_dim=None,
+                 n_embed=None, legacy=True, no_prompting=False, adapter_channels=None, use_time_adapter=False):
+        super().__init__()
+        _unsupported(num_classes=num_classes is not None, use_scale_shift_norm=use_scale_shift_norm,
+                     resblock_updown=resblock_updown, no_spatial_transformer=not use_spatial_transformer,
+                     transformer_depth=transformer_depth != 1, n_embed=n_embed is not None, dims=dims != 2,
+                     num_head_channels=num_head_channels != -1, use_time_adapter=use_time_adapter,
+                     no_conv_resample=not conv_resample, dropout=dropout != 0)
+        self.no_prompting = no_prompting
+        self._build(in_channels, model_channels, out_channels, num_res_blocks, list(attention_resolutions),
+                    list(channel_mult), num_heads, context_dim)
+        if not no_prompting:
+            acin = in_channels if adapter_channels is None else adapter_channels
+            self.adapter = self.add("adapter", Adapter(acin))     # openaimodel.py:549-556
+        else:
+            self.adapter = None
+
+    def forward(self, x, timesteps=None, context=None, y=None, pcond=None, kv=None, rows=None, **kwargs):
+        """x: fp32 [nb_in, 4, h, w]; rows >= nb_in output rows (row r reads x[r % nb_in] — lets the sampler
+        feed ONE copy of x for the cond and uncond halves instead of the reference's torch.cat([x]*2),
+        ddim.py:222). timesteps: int64 [rows]; context [rows, L, 768] or kv = project_context(context)."""
+        if y is not None or pcond is not None:
+            raise NotImplementedError("class labels / pcond are outside the FG-DM sampling path")
+        x = x.float().contiguous()
+        rows = rows or x.shape[0]
+        kvs = kv if kv is not None else self.project_context(context)
+        emb_all = self._emb(timesteps)
+        fa = self.adapter.forward(x, rows) if self.adapter is not None else None   # prompt = h, :836-844
+        h, hs = self._encode(x, rows, emb_all, kvs, fa)
+        h = self._run(self.middle_block, h, None, emb_all, kvs)
+        return self._decode(h, hs, emb_all, kvs)
+
+
+class _HintStem(Layer):
+    """ControlNet.input_hint_block, controlnet/cldm/cldm.py:655-671."""
+    CH = [(None, 16, 1), (16, 16, 1), (16, 32, 2), (32, 32, 1), (32, 96, 2), (96, 96, 1), (96, 256, 2)]
+
+    def __init__(self, hint_channels, mc):
+        super().__init__()
+        self.convs = []
+        for i, (ci, co, s) in enumerate(self.CH):
+            self.convs.append(self.add(str(2 * i), Conv2d(ci or hint_channels, co, 3, stride=s)))
+        self.last = self.add("14", Conv2d(256, mc, 3))
+
+    def forward(self, hint):
+        """hint: fp32 NCHW [B,3,H,W] in [0,1] -> NHWC bf16 [B,H/8,W/8,mc]. Step-invariant."""
+        c0 = self.convs[0]
+        h = ops.conv_small_cin(hint.float().contiguous(), c0.w, c0.b, c0.cout, act=ACT_SILU)
+        for c in self.convs[1:]:
+            h = ops.conv_direct(h, c.w, c.b, c.cout, stride=c.stride, act=ACT_SILU)
+        return self.last.gemm(h)
+
+
+class ControlNet(_UNetBase):
+    """controlnet/cldm/cldm.py:545-813. forward(x, hint, timesteps, context) -> 13 control tensors."""
+
+    def __init__(self, image_size=32, in_channels=4, model_channels=320, hint_channels=3, num_res_blocks=2,
+                 attention_resolutions=(4, 2, 1), dropout=0, channel_mult=(1, 2, 4, 4), conv_resample=True, dims=2,
+                 use_checkpoint=False, use_fp16=False, num_heads=-1, num_head_channels=-1, num_heads_upsample=-1,
+                 use_scale_shift_norm=False, resblock_updown=False, use_new_attention_order=False,
+                 use_spatial_transformer=False, transformer_depth=1, context_dim=None, n_embed=None, legacy=True,
+                 disable_self_attentions=None, num_attention_blocks=None, disable_middle_self_attn=False,
+                 use_linear_in_transformer=False):
+        super().__init__()
+        _unsupported(use_scale_shift_norm=use_scale_shift_norm, resblock_updown=resblock_updown,
+                     no_spatial_transformer=not use_spatial_transformer, transformer_depth=transformer_depth != 1,
+                     dims=dims != 2, num_head_channels=num_head_channels != -1,
+                     use_linear_in_transformer=use_linear_in_transformer, dropout=dropout != 0,
+                     disable_self_attentions=disable_self_attentions is not None,
+                     num_attention_blocks=num_attention_blocks is not None)
+        self._build(in_channels, model_channels, None, num_res_blocks, list(attention_resolutions),
+                    list(channel_mult), num_heads, context_dim, decoder=False)
+        self.zero_convs = self.add("zero_convs", Seq([Seq([Conv2d(c, c, 1)]) for c in self.input_chans]))
+        self.input_hint_block = self.add("input_hint_block", _HintStem(hint_channels, model_channels))
+        self.middle_block_out = self.add("middle_block_out", Seq([Conv2d(self.mid_ch, self.mid_ch, 1)]))
+
+    def encode_hint(self, hint):
+        return self.input_hint_block.forward(hint)
+
+    def forward(self, x, hint=None, timesteps=None, context=None, kv=None, rows=None, guided_hint=None,
+                scales=None, add_to=None, only_mid=False, **kwargs):
+        """Returns the 13 tensors `zero_conv(h) * scale` (cldm.py:801-811, scaling of :846 folded into the
+        epilogue). With add_to = [hs..., h_mid] of the UNet encoder, returns `add_to[k] + scale*control[k]`
+        instead (the adds of cldm.py:39-47 ride the same epilogue). Outputs are NHWC bf16."""
+        x = x.float().contiguous()
+        rows = rows or x.shape[0]
+        kvs = kv if kv is not None else self.project_context(context)
+        emb_all = self._emb(timesteps)
+        if guided_hint is None:
+            guided_hint = self.encode_hint(hint)
+        gb = guided_hint.shape[0]
+
+        def add_hint(h):                                          # h += guided_hint, cldm.py:803-805
+            for r0 in range(0, rows, gb):
+                ops.add_bf16(h[r0:r0 + gb], guided_hint, out=h[r0:r0 + gb])
+            return h
+
+        h, hs = self._encode(x, rows, emb_all, kvs, None, after_conv_in=add_hint)
+        h = self._run(self.middle_block, h, None, emb_all, kvs)
+        scales = scales or [1.0] * (len(hs) + 1)
+        outs = []
+        for k, hk in enumerate(hs + [h]):
+            if only_mid and k < len(hs):
+                outs.append(None)
+                continue
+            zc = self.zero_convs[k][0] if k < len(hs) else self.middle_block_out[0]
+            outs.append(zc.gemm(hk, alpha=float(scales[k]), res0=None if add_to is None else add_to[k]))
+        return outs
+
+
+class ControlledUnetModel(_UNetBase):
+    """controlnet/cldm/cldm.py:27-50: plain SD UNet whose skips / mid receive control residuals."""
+
+    def __init__(self, image_size=32, in_channels=4, model_channels=320, out_channels=4, num_res_blocks=2,
+                 attention_resolutions=(4, 2, 1), dropout=0, channel_mult=(1, 2, 4, 4), conv_resample=True, dims=2,
+                 num_classes=None, use_checkpoint=False, use_fp16=False, num_heads=-1, num_head_channels=-1,
+                 num_heads_upsample=-1, use_scale_shift_norm=False, resblock_updown=False,
+                 use_new_attention_order=False, use_spatial_transformer=False, transformer_depth=1, context_dim=None,
+                 n_embed=None, legacy=True, **ignored):
+        super().__init__()
+        _unsupported(num_classes=num_classes is not None, use_scale_shift_norm=use_scale_shift_norm,
+                     resblock_updown=resblock_updown, no_spatial_transformer=not use_spatial_transformer,
+                     transformer_depth=transformer_depth != 1, n_embed=n_embed is not None, dims=dims != 2,
+                     num_head_channels=num_head_channels != -1, dropout=dropout != 0)
+        self._build(in_channels, model_channels, out_channels, num_res_blocks, list(attention_resolutions),
+                    list(channel_mult), num_heads, context_dim)
+
+    def encode(self, x, timesteps, context=None, kv=None, rows=None):
+        x = x.float().contiguous()
+        rows = rows or x.shape[0]
+        kvs = kv if kv is not None else self.project_context(context)
+        emb_all = self._emb(timesteps)
+        h, hs = self._encode(x, rows, emb_all, kvs)
+        h = self._run(self.middle_block, h, None, emb_all, kvs)
+        return h, hs, emb_all, kvs
+
+    def decode(self, h, hs, emb_all, kvs):
+        return self._decode(h, list(hs), emb_all, kvs)
+
+    def forward(self, x, timesteps=None, context=None, control=None, only_mid_control=False, kv=None, rows=None,
+                **kwargs):
+        """control: 13 NHWC bf16 tensors from ControlNet.forward (already scaled), or None."""
+        h, hs, emb_all, kvs = self.encode(x, timesteps, context, kv, rows)
+        if control is not None:
+            control = list(control)
+            h = ops.add_bf16(h, control.pop())
+            if not only_mid_control:
+                hs = [ops.add_bf16(a, c) for a, c in zip(hs, control)]
+        return self._decode(h, hs, emb_all, kvs)
+
+
+# ---------------------------------------------------------------------------------------------
+# KL-VAE decoder
+# ---------------------------------------------------------------------------------------------
+class _VaeRes(Layer):
+    """ResnetBlock, model.py:82-141 (temb_channels = 0 in the decoder); GroupNorm eps 1e-6."""
+
+    def __init__(self, cin, cout):
+        super().__init__()
+        self.norm1 = self.add("norm1", Norm(cin))
+        self.conv1 = self.add("conv1", Conv2d(cin, cout, 3))
+        self.norm2 = self.add("norm2", Norm(cout))
+        self.conv2 = self.add("conv2", Conv2d(cout, cout, 3))
+        self.nin = self.add("nin_shortcut", Conv2d(cin, cout, 1)) if cin != cout else None
+
+    def forward(self, x):
+        h = self.conv1.gemm(ops.groupnorm(x, self.norm1.g, self.norm1.b, eps=1e-6, silu=True))
+        h = ops.groupnorm(h, self.norm2.g, self.norm2.b, eps=1e-6, silu=True)
+        s = self.nin.gemm(x) if self.nin is not None else x
+        return self.conv2.gemm(h, res0=s)
+
+
+class _VaeAttn(Layer):
+    """AttnBlock, model.py:150-202: single head with d = C = 512 over h*w tokens."""
+
+    def __init__(self, c):
+        super().__init__()
+        self.c = c
+        self.norm = self.add("norm", Norm(c))
+        self.q = self.add("q", Conv2d(c, c, 1))
+        self.k = self.add("k", Conv2d(c, c, 1))
+        self.v = self.add("v", Conv2d(c, c, 1))
+        self.proj_out = self.add("proj_out", Conv2d(c, c, 1))
+
+    def load(self, sd, prefix, dev):
+        super().load(sd, prefix, dev)
+        self.w_qkv = torch.cat([self.q.w, self.k.w, self.v.w], 0).contiguous()
+        self.b_qkv = torch.cat([self.q.b, self.k.b, self.v.b], 0).contiguous()
+        self.q.w = self.k.w = self.v.w = None
+
+    def forward(self, x):
+        nb, h, w, c = x.shape
+        n = h * w
+        dev = x.device
+        xn = ops.groupnorm(x, self.norm.g, self.norm.b, eps=1e-6, silu=False)
+        q = torch.empty((nb, 1, n, c), device=dev, dtype=bf16)
+        k = torch.empty((nb, 1, n, c), device=dev, dtype=bf16)
+        vt = torch.empty((nb, 1, c, n), device=dev, dtype=bf16)
+        ops.conv_gemm(xn.view(nb * n, c), self.w_qkv, 3 * c, bias=self.b_qkv, out_mode=OUT_QKV, rows_per_img=n,
+                      qkv=(q, k, vt, 0, 1, c, n))
+        o = torch.empty((nb, n, c), device=dev, dtype=bf16)
+        s = torch.empty((n, n), device=dev, dtype=torch.float32)
+        p = torch.empty((n, n), device=dev, dtype=bf16)
+        for i in range(nb):
+            ops.conv_gemm(q[i, 0], k[i, 0], n, out_mode=OUT_F32, out=s)                 # S = Q K^T
+            ops.softmax_rows(s, float(c) ** -0.5, out=p)                                # softmax(S * c^-1/2)
+            ops.conv_gemm(p, vt[i, 0], c, out=o[i])                                     # O = P V
+        return self.proj_out.gemm(o.view(nb, h, w, c), res0=x)
+
+
+class _Mid(Layer):
+    def __init__(self, c):
+        super().__init__()
+        self.block_1 = self.add("block_1", _VaeRes(c, c))
+        self.attn_1 = self.add("attn_1", _VaeAttn(c))
+        self.block_2 = self.add("block_2", _VaeRes(c, c))
+
+
+class _UpLevel(Layer):
+    def __init__(self, cin, cout, nblocks, upsample):
+        super().__init__()
+        blocks = []
+        for _ in range(nblocks):
+            blocks.append(_VaeRes(cin, cout))
+            cin = cout
+        self.block = self.add("block", Seq(blocks))
+        self.upsample = self.add("upsample", Upsample(cout)) if upsample else None
+
+
+class Decoder(Layer):
+    """model.py:462-569."""
+
+    def __init__(self, ch=128, out_ch=3, ch_mult=(1, 2, 4, 4), num_res_blocks=2, z_channels=4, **ignored):
+        super().__init__()
+        nres = len(ch_mult)
+        block_in = ch * ch_mult[nres - 1]
+        self.out_ch = out_ch
+        self.conv_in = self.add("conv_in", Conv2d(z_channels, block_in, 3))
+        self.mid = self.add("mid", _Mid(block_in))
+        ups = {}
+        for lvl in reversed(range(nres)):
+            block_out = ch * ch_mult[lvl]
+            ups[lvl] = _UpLevel(block_in, block_out, num_res_blocks + 1, lvl != 0)
+            block_in = block_out
+        self.up = self.add("up", Seq({lvl: ups[lvl] for lvl in range(nres)}))
+        self.norm_out = self.add("norm_out", Norm(block_in))
+        self.conv_out = self.add("conv_out", Conv2d(block_in, out_ch, 3))
+        self.nres = nres
+
+    def forward(self, z):
+        """z: fp32 NCHW [B, z_channels, h, w] -> fp32 NCHW [B, out_ch, 8h, 8w]."""
+        h = ops.conv_small_cin(z, self.conv_in.w, self.conv_in.b, self.conv_in.cout)
+        h = self.mid.block_1.forward(h)
+        h = self.mid.attn_1.forward(h)
+        h = self.mid.block_2.forward(h)
+        for lvl in reversed(range(self.nres)):
+            up = self.up[lvl]
+            for blk in up.block.children.values():
+                h = blk.forward(h)
+            if up.upsample is not None:
+                h = up.upsample.forward(h)
+        h = ops.groupnorm(h, self.norm_out.g, self.norm_out.b, eps=1e-6, silu=True)
+        return ops.conv_small_cout(h, self.conv_out.w, self.conv_out.b, self.out_ch)
+
+
+class _Conv1x1F32(Layer):
+    """post_quant_conv (autoencoder.py:305,331): 1x1 conv on the 4-channel fp32 latent."""
+
+    def __init__(self, c):
+        super().__init__()
+        self.c = c
+        self.params = {"weight": (c, c, 1, 1), "bias": (c,)}
+
+    def _load(self, sd, prefix, dev):
+        self.w = self._get(sd, prefix + "weight", self.params["weight"]).to(dev, torch.float32).reshape(self.c, self.c).contiguous()
+        self.b = self._get(sd, prefix + "bias", (self.c,)).to(dev, torch.float32).contiguous()
+
+
+class AutoencoderKL(_Net):
+    """ldm/models/autoencoder.py AutoencoderKL — decode only (sampling never encodes). Encoder, quant_conv
+    and loss keys of a reference state_dict are ignored (load with strict=False)."""
+
+    def __init__(self, ddconfig=None, lossconfig=None, embed_dim=4, ckpt_path=None, ignore_keys=(), image_key="image",
+                 colorize_nlabels=None, monitor=None, **ignored):
+        super().__init__()
+        dd = dict(ddconfig or {})
+        self.embed_dim = embed_dim
+        self.decoder = self.add("decoder", Decoder(ch=dd.get("ch", 128), out_ch=dd.get("out_ch", 3),
+                                                   ch_mult=tuple(dd.get("ch_mult", (1, 2, 4, 4))),
+                                                   num_res_blocks=dd.get("num_res_blocks", 2),
+                                                   z_channels=dd.get("z_channels", 4)))
+        if dd.get("attn_resolutions"):
+            raise NotImplementedError("VAE attn_resolutions other than [] are outside the FG-DM configuration")
+        self.post_quant_conv = self.add("post_quant_conv", _Conv1x1F32(embed_dim))
+
+    def decode(self, z, n=None, in_scale=1.0):
+        """autoencoder.py:330-333; in_scale folds decode_first_stage's z / scale_factor (ddpm.py:839)."""
+        if not self._loaded:
+            raise RuntimeError("weights not loaded")
+        with torch.no_grad():
+            pq = self.post_quant_conv
+            z = ops.latent_affine(z.float().contiguous(), pq.w, pq.b, in_scale)
+            return self.decoder.forward(z)
+
+    def forward(self, z):
+        return self.decode(z)

@@ -25,6 +25,20 @@ def _p(t):
     return None if t is None else t.data_ptr()
 
 
+_REPLAYED = 0
+
+
+def launch_count() -> int:
+    """Kernels of libfgdm_b200.so launched so far: direct launches + those replayed through CUDA graphs."""
+    return int(_lib.load().fgdm_launch_count()) + _REPLAYED
+
+
+def count_launches(n: int) -> None:
+    """Account for `n` of our kernels executed by a CUDA-graph replay."""
+    global _REPLAYED
+    _REPLAYED += n
+
+
 def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None, bias=None, rowvec=None,
               rows_per_img=0, res0=None, res1=None, alpha=1.0, act=ACT_NONE, out_mode=OUT_BF16, out=None,
               ldo=None, col_off=0, qkv=None, bn_hint=0):
@@ -47,10 +61,10 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
     args.nb, args.h, args.w, args.conv = nb, h, w, conv
     args.weight, args.n = _p(weight), n
     args.bias, args.rowvec = _p(bias), _p(rowvec)
-    args.ld_rowvec = rowvec.shape[-1] if rowvec is not None else 0
+    args.ld_rowvec = rowvec.stride(0) if rowvec is not None else 0
     args.rows_per_img = rows_per_img
-    args.res0, args.ld_res0 = _p(res0), (res0.shape[-1] if res0 is not None else 0)
-    args.res1, args.ld_res1 = _p(res1), (res1.shape[-1] if res1 is not None else 0)
+    args.res0, args.ld_res0 = _p(res0), (res0.stride(-2) if res0 is not None else 0)
+    args.res1, args.ld_res1 = _p(res1), (res1.stride(-2) if res1 is not None else 0)
     args.alpha, args.act, args.out_mode = alpha, act, out_mode
     args.bn_hint = bn_hint
     if out_mode == OUT_QKV:
@@ -76,16 +90,9 @@ def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):
     return out
 
 
-_GN_WS = {}
-
-
 def _gn_workspace(device, nb, groups):
-    need = nb * 64 * groups * 2
-    ws = _GN_WS.get(device)
-    if ws is None or ws.numel() < need:
-        ws = torch.empty(max(need, 1 << 16), device=device, dtype=torch.float32)
-        _GN_WS[device] = ws
-    return ws
+    # per call (a cached buffer that is later re-allocated would dangle inside captured CUDA graphs)
+    return torch.empty(nb * 64 * groups * 2, device=device, dtype=torch.float32)
 
 
 def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=None):
@@ -168,13 +175,19 @@ def add_bf16(a, b, out=None):
     return out
 
 
-def conv_small_cin(x, w, bias, cout, act=ACT_NONE, in_scale=1.0):
-    """x: NCHW fp32 with 3 or 4 channels -> NHWC bf16 [nb, h, w, cout]."""
-    nb, cin, h, wd = x.shape
+def conv_small_cin(x, w, bias, cout, act=ACT_NONE, in_scale=1.0, nb_out=None):
+    """x: NCHW fp32 with 3 or 4 channels -> NHWC bf16 [nb_out, h, w, cout]; output r reads x[r % nb_in]."""
+    nb_in, cin, h, wd = x.shape
+    nb = nb_out or nb_in
     y = torch.empty((nb, h, wd, cout), device=x.device, dtype=bf16)
     _lib.check(_lib.load().fgdm_conv_small_cin(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, act, in_scale,
-                                              _stream()), "fgdm_conv_small_cin")
+                                              nb_in, _stream()), "fgdm_conv_small_cin")
     return y
+
+
+def ddim_advance(counter, t_table, idx_table, t_out, index_out):
+    _lib.check(_lib.load().fgdm_ddim_advance(_p(counter), _p(t_table), _p(idx_table), _p(t_out), t_out.numel(),
+                                            _p(index_out), _stream()), "fgdm_ddim_advance")
 
 
 def conv_direct(x, w, bias, cout, stride=1, act=ACT_NONE):

@@ -31,6 +31,8 @@ extern "C" {
 
 const char* fgdm_last_error(void);
 int fgdm_abi_version(void);
+/* Number of kernels this library has launched (or captured into a CUDA graph) so far in this process. */
+long long fgdm_launch_count(void);
 /* 0 when device 0 is an sm_100 class GPU and the driver exposes cuTensorMapEncodeTiled. */
 int fgdm_device_check(void);
 
@@ -111,6 +113,12 @@ int fgdm_cfg_ddim_step(const float* e_uncond, const float* e_cond, const float* 
                        const float* coef_table, const int* index_ptr, int index, float scale, float temperature,
                        float* x_prev, float* pred_x0, int n, void* stream);
 
+/* Loop bookkeeping of ddim_sampling (ddim.py:147-149: index = total - i - 1; ts = full((b,), step)) done on
+ * the device so one captured CUDA graph replays for every step: i = (*counter)++; t_out[0..rows) =
+ * t_table[i]; *index_out = idx_table[i]. */
+int fgdm_ddim_advance(int* counter, const int64_t* t_table, const int* idx_table, int64_t* t_out, int rows,
+                      int* index_out, void* stream);
+
 /* timestep_embedding: util.py:160-180. t int64 [rows]; freqs fp32 [dim/2]; out fp32 [rows, dim]. */
 int fgdm_timestep_embedding(const int64_t* t, const float* freqs, float* out, int rows, int dim, void* stream);
 
@@ -126,9 +134,10 @@ int fgdm_resample(const void* in, void* out, int nb, int h, int w, int c, int mo
 int fgdm_add_bf16(const void* a, const void* b, void* out, size_t n, void* stream);
 
 /* 3x3 conv, NCHW fp32 input with cin in {3,4} (scaled by in_scale) -> NHWC bf16: openaimodel.py:561,
- * adapter.py:332, cldm.py:645,656; model.py:488. */
+ * adapter.py:332, cldm.py:645,656; model.py:488. Output image r reads input image r % nb_in (nb_in <= 0:
+ * nb) — the CFG halves share one latent instead of torch.cat([x] * 2) (ddim.py:222). */
 int fgdm_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
-                        int cout, int act, float in_scale, void* stream);
+                        int cout, int act, float in_scale, int nb_in, void* stream);
 /* 3x3 direct conv NHWC bf16 -> NHWC bf16, stride 1/2 (ControlNet hint stem, cldm.py:656-666). */
 int fgdm_conv_direct(const void* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
                      int cout, int stride, int act, void* stream);

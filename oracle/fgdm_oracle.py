@@ -1,0 +1,472 @@
+"""TEST INFRASTRUCTURE ONLY — fp32 restatement of FG-DM's sampling hot path (the parity oracle).
+
+This file is the checker, never the product: only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / `--impl reference` leg import it. Nothing under fgdm_b200/ imports it.
+
+It restates, as plain functional torch fp32 over a state_dict that uses the REFERENCE's parameter
+names and shapes, exactly the arithmetic the reference (DeepakSridhar/fgdm, /root/reference) performs on
+this path. The reference is pure PyTorch; its own code cannot travel to the GPU box, so this
+restatement does. Pinning: the reference ships no tests or golden vectors ("parity unpinned" by the
+reference's own tests); instead oracle/make_golden.py runs the UNMODIFIED reference
+modules in the build container on shared seeded weights, checks this restatement against them
+(max |diff| <= 1e-4 relative) and commits the reference's outputs as fixtures under tests/golden/.
+
+Every function cites the reference file:line it follows (paths relative to /root/reference).
+"""
+from __future__ import annotations
+
+import math
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+# ----------------------------------------------------------------------------------------------
+# small building blocks
+# ----------------------------------------------------------------------------------------------
+
+
+def _conv(sd, p, x, stride=1, padding=None):
+    w = sd[p + ".weight"]
+    if padding is None:
+        padding = w.shape[-1] // 2
+    return F.conv2d(x, w, sd.get(p + ".bias"), stride=stride, padding=padding)
+
+
+def _linear(sd, p, x):
+    return F.linear(x, sd[p + ".weight"], sd.get(p + ".bias"))
+
+
+def _gn(sd, p, x, eps):
+    """GroupNorm32: ldm/modules/diffusionmodules/util.py:208-225 (32 groups, computed in fp32)."""
+    return F.group_norm(x.float(), 32, sd[p + ".weight"], sd[p + ".bias"], eps)
+
+
+def _ln(sd, p, x):
+    return F.layer_norm(x, (x.shape[-1],), sd[p + ".weight"], sd[p + ".bias"], 1e-5)
+
+
+def timestep_embedding(t, dim, max_period=10000):
+    """ldm/modules/diffusionmodules/util.py:160-180."""
+    half = dim // 2
+    freqs = torch.exp(-math.log(max_period) * torch.arange(0, half, dtype=torch.float32) / half).to(t.device)
+    args = t[:, None].float() * freqs[None]
+    return torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+
+
+def time_embed(sd, p, t, model_channels):
+    """openaimodel.py:538-542,827-828: Linear, SiLU, Linear on the sinusoidal embedding."""
+    e = timestep_embedding(t, model_channels)
+    return _linear(sd, p + "time_embed.2", F.silu(_linear(sd, p + "time_embed.0", e)))
+
+
+def resblock(sd, p, x, emb):
+    """ResBlock._forward, openaimodel.py:275-301 (no up/down, no scale-shift norm); GN eps 1e-5."""
+    h = _conv(sd, p + ".in_layers.2", F.silu(_gn(sd, p + ".in_layers.0", x, 1e-5)))
+    h = h + _linear(sd, p + ".emb_layers.1", F.silu(emb))[:, :, None, None]
+    h = _conv(sd, p + ".out_layers.3", F.silu(_gn(sd, p + ".out_layers.0", h, 1e-5)))
+    if (p + ".skip_connection.weight") in sd:
+        x = _conv(sd, p + ".skip_connection", x)
+    return x + h
+
+
+def cross_attention(sd, p, x, context, heads):
+    """CrossAttention.forward, ldm/modules/attention.py:177-216 (first return value only; the
+    head-averaged logits are dead at inference, attention.py:235-238)."""
+    context = x if context is None else context
+    q = F.linear(x, sd[p + ".to_q.weight"])
+    k = F.linear(context, sd[p + ".to_k.weight"])
+    v = F.linear(context, sd[p + ".to_v.weight"])
+    b, n, c = q.shape
+    d = c // heads
+
+    def split(t):
+        return t.reshape(b, -1, heads, d).permute(0, 2, 1, 3)
+
+    q, k, v = split(q), split(k), split(v)
+    sim = torch.einsum("bhid,bhjd->bhij", q, k) * (d ** -0.5)
+    attn = sim.softmax(dim=-1)
+    out = torch.einsum("bhij,bhjd->bhid", attn, v)
+    out = out.permute(0, 2, 1, 3).reshape(b, n, c)
+    return _linear(sd, p + ".to_out.0", out)
+
+
+def feed_forward(sd, p, x):
+    """FeedForward with GEGLU, attention.py:37-64 (exact erf GELU)."""
+    h = _linear(sd, p + ".net.0.proj", x)
+    a, gate = h.chunk(2, dim=-1)
+    return _linear(sd, p + ".net.2", a * F.gelu(gate))
+
+
+def spatial_transformer(sd, p, x, context, heads):
+    """SpatialTransformer.forward attention.py:275-292 + BasicTransformerBlock._forward :234-240.
+    Normalize = GroupNorm eps 1e-6 (attention.py:76-77)."""
+    b, c, h, w = x.shape
+    x_in = x
+    t = _conv(sd, p + ".proj_in", _gn(sd, p + ".norm", x, 1e-6))
+    t = t.permute(0, 2, 3, 1).reshape(b, h * w, c)
+    bp = p + ".transformer_blocks.0"
+    t = cross_attention(sd, bp + ".attn1", _ln(sd, bp + ".norm1", t), None, heads) + t
+    t = cross_attention(sd, bp + ".attn2", _ln(sd, bp + ".norm2", t), context, heads) + t
+    t = feed_forward(sd, bp + ".ff", _ln(sd, bp + ".norm3", t)) + t
+    t = t.reshape(b, h, w, c).permute(0, 3, 1, 2)
+    return _conv(sd, p + ".proj_out", t) + x_in
+
+
+def adapter_forward(sd, p, x, channels=(320, 640, 1280, 1280), nums_rb=2):
+    """Adapter.forward ldm/modules/encoders/adapter.py:334-346 with ResnetBlock.forward :301-313,
+    as instantiated at openaimodel.py:556 (ksize=1, sk=True, use_conv=False -> AvgPool2d down)."""
+    feats = []
+    x = _conv(sd, p + ".conv_in", x)
+    for i in range(len(channels)):
+        for j in range(nums_rb):
+            bp = f"{p}.body.{i * nums_rb + j}"
+            if i != 0 and j == 0:
+                x = F.avg_pool2d(x, 2, 2)
+            if (bp + ".in_conv.weight") in sd:
+                x = _conv(sd, bp + ".in_conv", x)
+            h = _conv(sd, bp + ".block2", F.relu(_conv(sd, bp + ".block1", x)))
+            x = h + x
+        feats.append(x)
+    return feats
+
+
+# ----------------------------------------------------------------------------------------------
+# UNet structure (openaimodel.py:469-734): which sub-modules each TimestepEmbedSequential holds
+# ----------------------------------------------------------------------------------------------
+
+
+def unet_layout(cfg):
+    """Returns (input_blocks, middle, output_blocks); each block is a list of ('res'|'st'|'down'|'up'|
+    'conv_in', ...) in the order the reference constructs them (openaimodel.py:559-721)."""
+    mc, mult, nrb = cfg["model_channels"], cfg["channel_mult"], cfg["num_res_blocks"]
+    attn_res = cfg["attention_resolutions"]
+    inputs = [["conv_in"]]
+    ds = 1
+    for level in range(len(mult)):
+        for _ in range(nrb):
+            blk = ["res"]
+            if ds in attn_res:
+                blk.append("st")
+            inputs.append(blk)
+        if level != len(mult) - 1:
+            inputs.append(["down"])
+            ds *= 2
+    middle = ["res", "st", "res"]
+    outputs = []
+    for level in reversed(range(len(mult))):
+        for i in range(nrb + 1):
+            blk = ["res"]
+            if ds in attn_res:
+                blk.append("st")
+            if level and i == nrb:
+                blk.append("up")
+                ds //= 2
+            outputs.append(blk)
+    return inputs, middle, outputs
+
+
+def _run_block(sd, p, kinds, h, emb, context, heads):
+    """TimestepEmbedSequential.forward, openaimodel.py:85-93."""
+    for j, kind in enumerate(kinds):
+        q = f"{p}.{j}"
+        if kind == "conv_in":
+            h = _conv(sd, q, h)
+        elif kind == "res":
+            h = resblock(sd, q, h, emb)
+        elif kind == "st":
+            h = spatial_transformer(sd, q, h, context, heads)
+        elif kind == "down":   # Downsample with conv, openaimodel.py:146-180
+            h = _conv(sd, q + ".op", h, stride=2, padding=1)
+        elif kind == "up":     # Upsample, openaimodel.py:95-130: nearest 2x then conv3x3
+            h = _conv(sd, q + ".conv", F.interpolate(h, scale_factor=2, mode="nearest"))
+    return h
+
+
+DEFAULT_UNET_CFG = dict(in_channels=4, out_channels=4, model_channels=320, attention_resolutions=[4, 2, 1],
+                        num_res_blocks=2, channel_mult=[1, 2, 4, 4], num_heads=8, context_dim=768)
+
+
+def unet_forward(sd, x, t, context, cfg=None, prefix="", adapter=True):
+    """FG-DM UNetModel.forward, openaimodel.py:808-884 (pcond=None => the adapter sees the noisy
+    latent itself, :836-844; features added after input blocks 2,5,8,11, :855-857).
+    adapter=False restates forward_original (:753-806), the plain SD UNet."""
+    cfg = cfg or DEFAULT_UNET_CFG
+    p = prefix
+    heads = cfg["num_heads"]
+    inputs, middle, outputs = unet_layout(cfg)
+    emb = time_embed(sd, p, t, cfg["model_channels"])
+    h = x.float()
+    fa = adapter_forward(sd, p + "adapter", h) if adapter else None
+    hs = []
+    k = 0
+    for idx, kinds in enumerate(inputs):
+        h = _run_block(sd, f"{p}input_blocks.{idx}", kinds, h, emb, context, heads)
+        if adapter and (idx + 1) % 3 == 0:
+            h = h + fa[k]
+            k += 1
+        hs.append(h)
+    h = _run_block(sd, p + "middle_block", middle, h, emb, context, heads)
+    for idx, kinds in enumerate(outputs):
+        h = torch.cat([h, hs.pop()], dim=1)
+        h = _run_block(sd, f"{p}output_blocks.{idx}", kinds, h, emb, context, heads)
+    return _conv(sd, p + "out.2", F.silu(_gn(sd, p + "out.0", h, 1e-5)))
+
+
+def hint_stem(sd, p, hint):
+    """ControlNet.input_hint_block, controlnet/cldm/cldm.py:655-671 (8 convs, SiLU between)."""
+    strides = [1, 1, 2, 1, 2, 1, 2, 1]
+    h = hint
+    for i, s in enumerate(strides):
+        h = _conv(sd, f"{p}.{2 * i}", h, stride=s, padding=1)
+        if i != len(strides) - 1:
+            h = F.silu(h)
+    return h
+
+
+def controlnet_forward(sd, x, hint, t, context, cfg=None, prefix=""):
+    """ControlNet.forward, controlnet/cldm/cldm.py:792-813 -> 13 control tensors."""
+    cfg = cfg or DEFAULT_UNET_CFG
+    p = prefix
+    heads = cfg["num_heads"]
+    inputs, middle, _ = unet_layout(cfg)
+    emb = time_embed(sd, p, t, cfg["model_channels"])
+    guided = hint_stem(sd, p + "input_hint_block", hint.float())
+    outs = []
+    h = x.float()
+    for idx, kinds in enumerate(inputs):
+        h = _run_block(sd, f"{p}input_blocks.{idx}", kinds, h, emb, context, heads)
+        if idx == 0:
+            h = h + guided
+        outs.append(_conv(sd, f"{p}zero_convs.{idx}.0", h))
+    h = _run_block(sd, p + "middle_block", middle, h, emb, context, heads)
+    outs.append(_conv(sd, p + "middle_block_out.0", h))
+    return outs
+
+
+def controlled_unet_forward(sd, x, t, context, control, cfg=None, prefix="", only_mid_control=False):
+    """ControlledUnetModel.forward, controlnet/cldm/cldm.py:27-50."""
+    cfg = cfg or DEFAULT_UNET_CFG
+    p = prefix
+    heads = cfg["num_heads"]
+    inputs, middle, outputs = unet_layout(cfg)
+    emb = time_embed(sd, p, t, cfg["model_channels"])
+    control = None if control is None else list(control)
+    hs = []
+    h = x.float()
+    for idx, kinds in enumerate(inputs):
+        h = _run_block(sd, f"{p}input_blocks.{idx}", kinds, h, emb, context, heads)
+        hs.append(h)
+    h = _run_block(sd, p + "middle_block", middle, h, emb, context, heads)
+    if control is not None:
+        h = h + control.pop()
+    for idx, kinds in enumerate(outputs):
+        if only_mid_control or control is None:
+            h = torch.cat([h, hs.pop()], dim=1)
+        else:
+            h = torch.cat([h, hs.pop() + control.pop()], dim=1)
+        h = _run_block(sd, f"{p}output_blocks.{idx}", kinds, h, emb, context, heads)
+    return _conv(sd, p + "out.2", F.silu(_gn(sd, p + "out.0", h, 1e-5)))
+
+
+def control_ldm_apply(sd, x, t, hint, context, control_scales=None, only_mid_control=False, cfg=None,
+                      unet_prefix="model.diffusion_model.", control_prefix="control_model."):
+    """ControlLDM.apply_model, controlnet/cldm/cldm.py:836-849."""
+    scales = control_scales or [1.0] * 13
+    control = controlnet_forward(sd, x, hint, t, context, cfg, control_prefix)
+    control = [c * s for c, s in zip(control, scales)]
+    return controlled_unet_forward(sd, x, t, context, control, cfg, unet_prefix, only_mid_control)
+
+
+# ----------------------------------------------------------------------------------------------
+# VAE decoder (ldm/modules/diffusionmodules/model.py:462-569; GroupNorm eps 1e-6, swish)
+# ----------------------------------------------------------------------------------------------
+
+DEFAULT_VAE_CFG = dict(ch=128, out_ch=3, ch_mult=[1, 2, 4, 4], num_res_blocks=2, z_channels=4, embed_dim=4)
+
+
+def _vae_res(sd, p, x):
+    """ResnetBlock.forward model.py:121-141 (temb is None in the decoder)."""
+    h = _conv(sd, p + ".conv1", F.silu(_gn(sd, p + ".norm1", x, 1e-6)))
+    h = _conv(sd, p + ".conv2", F.silu(_gn(sd, p + ".norm2", h, 1e-6)))
+    if (p + ".nin_shortcut.weight") in sd:
+        x = _conv(sd, p + ".nin_shortcut", x)
+    return x + h
+
+
+def _vae_attn(sd, p, x):
+    """AttnBlock.forward model.py:172-202: single head, d = C."""
+    h = _gn(sd, p + ".norm", x, 1e-6)
+    q, k, v = _conv(sd, p + ".q", h), _conv(sd, p + ".k", h), _conv(sd, p + ".v", h)
+    b, c, hh, ww = q.shape
+    q = q.reshape(b, c, hh * ww).permute(0, 2, 1)
+    k = k.reshape(b, c, hh * ww)
+    w_ = torch.bmm(q, k) * (int(c) ** (-0.5))
+    w_ = F.softmax(w_, dim=2)
+    v = v.reshape(b, c, hh * ww)
+    h = torch.bmm(v, w_.permute(0, 2, 1)).reshape(b, c, hh, ww)
+    return x + _conv(sd, p + ".proj_out", h)
+
+
+def vae_decode(sd, z, cfg=None, prefix="first_stage_model.", scale_factor=0.18215):
+    """LatentDiffusion.decode_first_stage (ldm/models/diffusion/ddpm.py:831-889: z / scale_factor) ->
+    AutoencoderKL.decode (ldm/models/autoencoder.py:330-333) -> Decoder.forward (model.py:535-569)."""
+    cfg = cfg or DEFAULT_VAE_CFG
+    p = prefix
+    nres = len(cfg["ch_mult"])
+    z = z.float() * (1.0 / scale_factor)
+    z = _conv(sd, p + "post_quant_conv", z)
+    h = _conv(sd, p + "decoder.conv_in", z)
+    h = _vae_res(sd, p + "decoder.mid.block_1", h)
+    h = _vae_attn(sd, p + "decoder.mid.attn_1", h)
+    h = _vae_res(sd, p + "decoder.mid.block_2", h)
+    for lvl in reversed(range(nres)):
+        for i in range(cfg["num_res_blocks"] + 1):
+            h = _vae_res(sd, f"{p}decoder.up.{lvl}.block.{i}", h)
+        if lvl != 0:
+            h = _conv(sd, f"{p}decoder.up.{lvl}.upsample.conv", F.interpolate(h, scale_factor=2.0, mode="nearest"))
+    h = F.silu(_gn(sd, p + "decoder.norm_out", h, 1e-6))
+    return _conv(sd, p + "decoder.conv_out", h)
+
+
+# ----------------------------------------------------------------------------------------------
+# schedules and the DDIM loop
+# ----------------------------------------------------------------------------------------------
+
+
+def make_schedule_buffers(timesteps=1000, linear_start=0.00085, linear_end=0.0120):
+    """DDPM.register_schedule ldm/models/diffusion/ddpm.py:175-203 with make_beta_schedule('linear')
+    util.py:21-25 (float64 numpy, stored as float32)."""
+    betas = (torch.linspace(linear_start ** 0.5, linear_end ** 0.5, timesteps, dtype=torch.float64) ** 2).numpy()
+    alphas_cumprod = np.cumprod(1.0 - betas, axis=0)
+    alphas_cumprod_prev = np.append(1.0, alphas_cumprod[:-1])
+    return dict(betas=torch.tensor(betas, dtype=torch.float32),
+                alphas_cumprod=torch.tensor(alphas_cumprod, dtype=torch.float32),
+                alphas_cumprod_prev=torch.tensor(alphas_cumprod_prev, dtype=torch.float32))
+
+
+def make_ddim_schedule(alphas_cumprod, S, eta=0.0, num_ddpm=1000):
+    """DDIMSampler.make_schedule ldm/models/diffusion/ddim.py:26-55 with util.py:46-74 ('uniform').
+    alphas_cumprod: float32 torch tensor (the model buffer). Returns numpy float arrays exactly as the
+    reference holds them (alphas: torch f32 indexed -> here numpy f32; alphas_prev passes through a
+    float64 numpy array built from float32 values; sigmas likewise)."""
+    c = num_ddpm // S
+    ddim_timesteps = np.asarray(list(range(0, num_ddpm, c))) + 1
+    ac = alphas_cumprod.cpu()
+    alphas = ac[ddim_timesteps]                                   # torch f32
+    alphas_prev = np.asarray([ac[0]] + ac[ddim_timesteps[:-1]].tolist())   # numpy f64 of f32 values
+    sigmas = eta * np.sqrt((1 - alphas_prev) / (1 - alphas) * (1 - alphas / alphas_prev))
+    sqrt_one_minus_alphas = np.sqrt(1.0 - alphas)
+    return dict(timesteps=ddim_timesteps, alphas=alphas, alphas_prev=alphas_prev,
+                sigmas=torch.as_tensor(sigmas), sqrt_one_minus_alphas=torch.as_tensor(sqrt_one_minus_alphas))
+
+
+def ddim_update(x, e_t, sched, index, noise=None, temperature=1.0):
+    """p_sample_ddim's update, ddim.py:249-268 (= ddim_hacked.py:207-230): scalars become fp32
+    [b,1,1,1] tensors via torch.full (:254-257)."""
+    b, dev = x.shape[0], x.device
+    a_t = torch.full((b, 1, 1, 1), float(sched["alphas"][index]), device=dev)
+    a_prev = torch.full((b, 1, 1, 1), float(sched["alphas_prev"][index]), device=dev)
+    sigma_t = torch.full((b, 1, 1, 1), float(sched["sigmas"][index]), device=dev)
+    s1m = torch.full((b, 1, 1, 1), float(sched["sqrt_one_minus_alphas"][index]), device=dev)
+    pred_x0 = (x - s1m * e_t) / a_t.sqrt()
+    dir_xt = (1.0 - a_prev - sigma_t ** 2).sqrt() * e_t
+    if noise is None:
+        noise = torch.zeros_like(x)
+    x_prev = a_prev.sqrt() * pred_x0 + dir_xt + sigma_t * noise * temperature
+    return x_prev, pred_x0
+
+
+def ddim_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod, eta=0.0, log_every_t=100,
+                sequential_cfg=False, record=None):
+    """DDIMSampler.sample/ddim_sampling/p_sample_ddim with CFG.
+    sequential_cfg=False: ldm/models/diffusion/ddim.py:116-177,221-243 (one batched call on cat([uc, c])).
+    sequential_cfg=True:  controlnet/cldm/ddim_hacked.py:150-192 (cond call then uncond call).
+    apply_model(x, t, c) -> eps. eta must be 0 here (the noise term vanishes; the reference still draws
+    and discards randn, ddim.py:265). record: optional list receiving (e_t, x_prev) per step."""
+    assert eta == 0.0
+    sched = make_ddim_schedule(alphas_cumprod, S, eta)
+    ts = sched["timesteps"]
+    img = x_T
+    b = shape[0]
+    inter = {"x_inter": [img], "pred_x0": [img]}
+    total = ts.shape[0]
+    for i, step in enumerate(np.flip(ts)):
+        index = total - i - 1
+        t = torch.full((b,), int(step), device=img.device, dtype=torch.long)
+        if uncond is None or scale == 1.0:
+            e_t = apply_model(img, t, cond)
+        elif sequential_cfg:
+            e_c = apply_model(img, t, cond)
+            e_u = apply_model(img, t, uncond)
+            e_t = e_u + scale * (e_c - e_u)
+        else:
+            x_in = torch.cat([img] * 2)
+            t_in = torch.cat([t] * 2)
+            c_in = torch.cat([uncond, cond])
+            e_u, e_c = apply_model(x_in, t_in, c_in).chunk(2)
+            e_t = e_u + scale * (e_c - e_u)
+        img, pred_x0 = ddim_update(img, e_t, sched, index)
+        if record is not None:
+            record.append((e_t, img))
+        if index % log_every_t == 0 or index == total - 1:
+            inter["x_inter"].append(img)
+            inter["pred_x0"].append(pred_x0)
+    return img, inter
+
+
+# ----------------------------------------------------------------------------------------------
+# factor hand-off (scripts/txt2img_fgdm_inference.py:244-261; controlnet/initialize_cn.py:77-80,98-99)
+# ----------------------------------------------------------------------------------------------
+
+
+def seg_image_to_u8(x):
+    """txt2img_fgdm_inference.py:245,249-251: clamp((x+1)/2, 0, 1); 255 * (c h w -> h w c); astype(uint8)
+    (truncation). x: [B,3,H,W] float -> numpy uint8 [B,H,W,3]."""
+    x = torch.clamp((x.float() + 1.0) / 2.0, min=0.0, max=1.0)
+    arr = 255.0 * x.permute(0, 2, 3, 1).cpu().numpy()
+    return arr.astype(np.uint8)
+
+
+def final_image_to_u8(x):
+    """initialize_cn.py:98-99: (b c h w -> b h w c) * 127.5 + 127.5, clip(0, 255), astype(uint8)."""
+    arr = (x.float().permute(0, 2, 3, 1) * 127.5 + 127.5).cpu().numpy().clip(0, 255)
+    return arr.astype(np.uint8)
+
+
+def resize_u8_bilinear(img, dh, dw):
+    """cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR) for 8-bit images
+    (txt2img_fgdm_inference.py:257-259). OpenCV (third-party, opencv-python 4.x; algorithm in
+    modules/imgproc/src/resize.cpp) uses half-pixel centres, coefficients rounded to 11-bit fixed point
+    (INTER_RESIZE_COEF_SCALE = 2048), a horizontal pass in int32 and the vertical pass
+    (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2. img: uint8 [H,W,C]."""
+    sh, sw, c = img.shape
+
+    def coeffs(dst, src):
+        scale = np.float32(src) / np.float32(dst)
+        f = (np.arange(dst, dtype=np.float32) + np.float32(0.5)) * scale - np.float32(0.5)
+        s = np.floor(f).astype(np.int32)
+        f = (f - s).astype(np.float32)
+        lo = s < 0
+        f[lo] = 0
+        s[lo] = 0
+        hi = s >= src - 1
+        f[hi] = 0
+        s[hi] = src - 1
+        c0 = np.rint((np.float32(1.0) - f) * np.float32(2048)).astype(np.int32)
+        c1 = np.rint(f * np.float32(2048)).astype(np.int32)
+        return s, np.minimum(s + 1, src - 1), c0, c1
+
+    sx0, sx1, a0, a1 = coeffs(dw, sw)
+    sy0, sy1, b0, b1 = coeffs(dh, sh)
+    src = img.astype(np.int32)
+    rows = src[:, sx0, :] * a0[None, :, None] + src[:, sx1, :] * a1[None, :, None]     # [SH, DW, C]
+    r0, r1 = rows[sy0], rows[sy1]
+    out = (((b0[:, None, None] * (r0 >> 4)) >> 16) + ((b1[:, None, None] * (r1 >> 4)) >> 16) + 2) >> 2
+    return np.clip(out, 0, 255).astype(np.uint8)
+
+
+def u8_to_hint(u8):
+    """initialize_cn.py:78-80: uint8 [B,H,W,3] -> float / 255 -> [B,3,H,W]."""
+    t = torch.from_numpy(np.ascontiguousarray(u8)).float() / 255.0
+    return t.permute(0, 3, 1, 2).contiguous()
