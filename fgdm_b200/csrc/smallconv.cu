@@ -248,13 +248,18 @@ int launch_image_to_u8(const float* x, void* y, int NB, int C, int HW, int mode,
 // ---- F: bilinear resize of NHWC uint8, reproducing cv2.resize(..., INTER_LINEAR) for 8-bit images
 // (txt2img_fgdm_inference.py:257-259): half-pixel centres, 11-bit fixed-point coefficients,
 // horizontal pass in int32, vertical pass ((b0*(r0>>4))>>16) + ((b1*(r1>>4))>>16) + 2 >> 2.
-__device__ __forceinline__ void cv_coeff(int dst, float scale, int src_size, int* s0, short* c0, short* c1) {
+__device__ __forceinline__ void cv_coeff(int dst, float scale, int src_size, bool clamp_frac, int* s0, int* s1,
+                                         short* c0, short* c1) {
   float fx = (dst + 0.5f) * scale - 0.5f;
   int sx = static_cast<int>(floorf(fx));
   fx -= sx;
-  if (sx < 0) { fx = 0.f; sx = 0; }
-  if (sx >= src_size - 1) { fx = 0.f; sx = src_size - 1; }
-  *s0 = sx;
+  if (clamp_frac) {  // horizontal pass: resize.cpp zeroes the fraction at the borders
+    if (sx < 0) { fx = 0.f; sx = 0; }
+    if (sx >= src_size - 1) { fx = 0.f; sx = src_size - 1; }
+  }
+  // vertical pass: the fraction is kept and both source rows are clipped into the image
+  *s0 = min(max(sx, 0), src_size - 1);
+  *s1 = min(max(sx + 1, 0), src_size - 1);
   // cv::saturate_cast<short>(float) rounds to nearest even (cvRound)
   *c0 = static_cast<short>(__float2int_rn((1.f - fx) * 2048.f));
   *c1 = static_cast<short>(__float2int_rn(fx * 2048.f));
@@ -269,11 +274,10 @@ __global__ void resize_u8_kernel(const unsigned char* __restrict__ src, unsigned
   const int dx = p % DW; p /= DW;
   const int dy = p % DH;
   const int n = p / DH;
-  int sx, sy;
+  int sx, sy, sx1, sy1;
   short a0, a1, b0, b1;
-  cv_coeff(dx, static_cast<float>(SW) / DW, SW, &sx, &a0, &a1);
-  cv_coeff(dy, static_cast<float>(SH) / DH, SH, &sy, &b0, &b1);
-  const int sx1 = min(sx + 1, SW - 1), sy1 = min(sy + 1, SH - 1);
+  cv_coeff(dx, static_cast<float>(SW) / DW, SW, true, &sx, &sx1, &a0, &a1);
+  cv_coeff(dy, static_cast<float>(SH) / DH, SH, false, &sy, &sy1, &b0, &b1);
   const unsigned char* s = src + static_cast<size_t>(n) * SH * SW * C;
   const int r0 = s[(static_cast<size_t>(sy) * SW + sx) * C + c] * a0 + s[(static_cast<size_t>(sy) * SW + sx1) * C + c] * a1;
   const int r1 = s[(static_cast<size_t>(sy1) * SW + sx) * C + c] * a0 + s[(static_cast<size_t>(sy1) * SW + sx1) * C + c] * a1;

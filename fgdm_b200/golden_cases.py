@@ -1,0 +1,99 @@
+"""Seeded definitions of the golden parity cases (inputs + weight seeds + model configs).
+
+Shared by oracle/make_golden.py (build container: runs the real reference, writes tests/golden/*.npz)
+and tests/ (GPU box: re-derives the same inputs/weights and compares the CUDA path with the fixtures).
+Pure data/plumbing: no arithmetic of the hot path lives here.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import synth
+
+FGDM_WEIGHT_SEED = 11
+CONTROL_WEIGHT_SEED = 12
+CONTROL_SCALES_VARIANT = tuple(0.5 + 0.1 * i for i in range(13))
+
+# models/config.yaml:33-48 and controlnet/models/cldm_v15_canny.yaml:21-53
+UNET_PARAMS = dict(image_size=32, in_channels=4, out_channels=4, model_channels=320, attention_resolutions=[4, 2, 1],
+                   num_res_blocks=2, channel_mult=[1, 2, 4, 4], num_heads=8, use_spatial_transformer=True,
+                   transformer_depth=1, context_dim=768, use_checkpoint=True, legacy=False)
+CONTROLNET_PARAMS = dict(image_size=32, in_channels=4, hint_channels=3, model_channels=320,
+                         attention_resolutions=[4, 2, 1], num_res_blocks=2, channel_mult=[1, 2, 4, 4], num_heads=8,
+                         use_spatial_transformer=True, transformer_depth=1, context_dim=768, use_checkpoint=True,
+                         legacy=False)
+# models/config.yaml:50-71
+VAE_PARAMS = dict(embed_dim=4, monitor="val/rec_loss",
+                  ddconfig=dict(double_z=True, z_channels=4, resolution=256, in_channels=3, out_ch=3, ch=128,
+                                ch_mult=[1, 2, 4, 4], num_res_blocks=2, attn_resolutions=[], dropout=0.0),
+                  lossconfig=dict(target="torch.nn.Identity"))
+
+
+def fgdm_config():
+    """models/config.yaml with our target strings (the reference's own strings also resolve through
+    fgdm_b200.ldm.TARGET_ALIASES)."""
+    return dict(target="fgdm_b200.ldm.LatentDiffusion", params=dict(
+        linear_start=0.00085, linear_end=0.0120, num_timesteps_cond=1, log_every_t=200, timesteps=1000,
+        first_stage_key="image", cond_stage_key="caption", image_size=32, channels=4, cond_stage_trainable=False,
+        conditioning_key="crossattn", scale_factor=0.18215, use_ema=False,
+        unet_config=dict(target="fgdm_b200.nets.UNetModel", params=dict(UNET_PARAMS)),
+        first_stage_config=dict(target="fgdm_b200.nets.AutoencoderKL", params=dict(VAE_PARAMS)),
+        cond_stage_config=dict(target="torch.nn.Identity")))
+
+
+def control_config():
+    """controlnet/models/cldm_v15_canny.yaml with our target strings."""
+    return dict(target="fgdm_b200.ldm.ControlLDM", params=dict(
+        linear_start=0.00085, linear_end=0.0120, num_timesteps_cond=1, log_every_t=200, timesteps=1000,
+        first_stage_key="jpg", cond_stage_key="txt", control_key="hint", image_size=64, channels=4,
+        cond_stage_trainable=False, conditioning_key="crossattn", scale_factor=0.18215, use_ema=False,
+        only_mid_control=False,
+        control_stage_config=dict(target="fgdm_b200.nets.ControlNet", params=dict(CONTROLNET_PARAMS)),
+        unet_config=dict(target="fgdm_b200.nets.ControlledUnetModel", params=dict(UNET_PARAMS)),
+        first_stage_config=dict(target="fgdm_b200.nets.AutoencoderKL", params=dict(VAE_PARAMS)),
+        cond_stage_config=dict(target="torch.nn.Identity")))
+
+
+def fgdm_param_shapes():
+    from .ldm import instantiate_from_config
+    return instantiate_from_config(fgdm_config()).param_shapes()
+
+
+def control_param_shapes():
+    from .ldm import instantiate_from_config
+    return instantiate_from_config(control_config()).param_shapes()
+
+
+# ---- cases (16x16 latents: UNet levels 16/8/4/2, attention at 256/64/16/4 tokens) ----------------
+def unet_case():
+    return dict(x=synth.randn((2, 4, 16, 16), 21), t=torch.tensor([981, 441], dtype=torch.int64),
+                ctx=synth.randn((2, 77, 768), 22))
+
+
+def ddim_case():
+    return dict(S=5, B=1, shape=(4, 16, 16), scale=7.5, x_T=synth.randn((1, 4, 16, 16), 31),
+                c=synth.randn((1, 77, 768), 32), uc=synth.randn((1, 77, 768), 33))
+
+
+def vae_case():
+    return dict(z=synth.randn((1, 4, 16, 16), 41) * 0.18215 * 3.0)
+
+
+def _hint(b, hw, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    u8 = torch.randint(0, 256, (b, hw, hw, 3), generator=g, dtype=torch.uint8)
+    return (u8.float() / 255.0).permute(0, 3, 1, 2).contiguous()
+
+
+def control_case():
+    return dict(x=synth.randn((2, 4, 16, 16), 51), t=torch.tensor([801, 201], dtype=torch.int64),
+                ctx=synth.randn((2, 77, 768), 52), hint=_hint(2, 128, 53))
+
+
+def control_ddim_case():
+    return dict(S=4, B=1, shape=(4, 16, 16), scale=9.0, x_T=synth.randn((1, 4, 16, 16), 61),
+                c=synth.randn((1, 77, 768), 62), uc=synth.randn((1, 77, 768), 63), hint=_hint(1, 128, 64))
+
+
+def handoff_case():
+    return dict(img=synth.randn((2, 3, 64, 64), 71) * 0.8, dh=128, dw=128)

@@ -136,6 +136,7 @@ class _UNetBase(_Net):
         ted = 4 * mc
         self.time_embed = self.add("time_embed", TimeEmbed(mc))
         self._res, self._sts = [], []
+        self.trace = None
 
         def res(cin, cout):
             r = ResBlock(cin, ted, cout)
@@ -211,6 +212,8 @@ class _UNetBase(_Net):
             else:
                 assert r1 is None
                 h = layer.forward(h)
+        if self.trace is not None:          # debugging aid: NHWC bf16 block outputs in execution order
+            self.trace.append(h)
         return h
 
     def _encode(self, x, rows, emb_all, kvs, fa=None, after_conv_in=None):

@@ -166,8 +166,18 @@ def unet_layout(cfg):
     return inputs, middle, outputs
 
 
+TRACE = None   # debugging aid: set to a list to collect every block output (NCHW fp32) in execution order
+
+
 def _run_block(sd, p, kinds, h, emb, context, heads):
     """TimestepEmbedSequential.forward, openaimodel.py:85-93."""
+    h = _run_block_inner(sd, p, kinds, h, emb, context, heads)
+    if TRACE is not None:
+        TRACE.append((p, h))
+    return h
+
+
+def _run_block_inner(sd, p, kinds, h, emb, context, heads):
     for j, kind in enumerate(kinds):
         q = f"{p}.{j}"
         if kind == "conv_in":
@@ -205,6 +215,8 @@ def unet_forward(sd, x, t, context, cfg=None, prefix="", adapter=True):
         if adapter and (idx + 1) % 3 == 0:
             h = h + fa[k]
             k += 1
+            if TRACE is not None:
+                TRACE[-1] = (TRACE[-1][0], h)
         hs.append(h)
     h = _run_block(sd, p + "middle_block", middle, h, emb, context, heads)
     for idx, kinds in enumerate(outputs):
@@ -442,23 +454,26 @@ def resize_u8_bilinear(img, dh, dw):
     (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2. img: uint8 [H,W,C]."""
     sh, sw, c = img.shape
 
-    def coeffs(dst, src):
+    def coeffs(dst, src, clamp_frac):
         scale = np.float32(src) / np.float32(dst)
         f = (np.arange(dst, dtype=np.float32) + np.float32(0.5)) * scale - np.float32(0.5)
         s = np.floor(f).astype(np.int32)
         f = (f - s).astype(np.float32)
-        lo = s < 0
-        f[lo] = 0
-        s[lo] = 0
-        hi = s >= src - 1
-        f[hi] = 0
-        s[hi] = src - 1
+        if clamp_frac:
+            # horizontal pass only (resize.cpp: `if (sx < 0) fx = 0, sx = 0; if (sx >= ssize.width-1) fx = 0, ...`)
+            lo = s < 0
+            f[lo] = 0
+            s[lo] = 0
+            hi = s >= src - 1
+            f[hi] = 0
+            s[hi] = src - 1
+        # vertical pass: the fraction is kept and BOTH source rows are clipped into the image
         c0 = np.rint((np.float32(1.0) - f) * np.float32(2048)).astype(np.int32)
         c1 = np.rint(f * np.float32(2048)).astype(np.int32)
-        return s, np.minimum(s + 1, src - 1), c0, c1
+        return np.clip(s, 0, src - 1), np.clip(s + 1, 0, src - 1), c0, c1
 
-    sx0, sx1, a0, a1 = coeffs(dw, sw)
-    sy0, sy1, b0, b1 = coeffs(dh, sh)
+    sx0, sx1, a0, a1 = coeffs(dw, sw, True)
+    sy0, sy1, b0, b1 = coeffs(dh, sh, False)
     src = img.astype(np.int32)
     rows = src[:, sx0, :] * a0[None, :, None] + src[:, sx1, :] * a1[None, :, None]     # [SH, DW, C]
     r0, r1 = rows[sy0], rows[sy1]
