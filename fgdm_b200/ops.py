@@ -28,6 +28,42 @@ def _p(t):
 _REPLAYED = 0
 
 
+_PROF = None   # when a list: every launch is bracketed by CUDA events (bench.py's per-kernel roofline pass)
+
+
+def profile_start():
+    global _PROF
+    _PROF = []
+
+
+def profile_stop():
+    """-> {kernel: {shape_key: [launches, ms, algorithmic flops, algorithmic bytes]}} (synchronises)."""
+    global _PROF
+    rec, _PROF = _PROF, None
+    torch.cuda.synchronize()
+    out = {}
+    for name, (key, flops, nbytes), e0, e1 in rec:
+        slot = out.setdefault(name, {}).setdefault(key, [0, 0.0, 0.0, 0.0])
+        slot[0] += 1
+        slot[1] += e0.elapsed_time(e1)
+        slot[2] += flops
+        slot[3] += nbytes
+    return out
+
+
+def _call(name, work, *args):
+    fn = getattr(_lib.load(), name)
+    if _PROF is None:
+        _lib.check(fn(*args), name)
+        return
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rc = fn(*args)
+    e1.record()
+    _lib.check(rc, name)
+    _PROF.append((name, work, e0, e1))
+
+
 def launch_count() -> int:
     """Kernels of libfgdm_b200.so launched so far: direct launches + those replayed through CUDA graphs."""
     return int(_lib.load().fgdm_launch_count()) + _REPLAYED
@@ -47,7 +83,6 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
     For CONV_3X3_S2, a0 is the phase-split tensor `[4, nb, h, w, c]` (see resample(mode=2)) and
     (nb, h, w) describe the OUTPUT. Returns the output tensor (or None in QKV mode).
     """
-    lib = _lib.load()
     c0 = a0.shape[-1]
     c1 = a1.shape[-1] if a1 is not None else 0
     if nb is None:
@@ -79,14 +114,17 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
         elif ldo is None:
             ldo = out.shape[-1]
         args.out, args.ldo, args.col_off = _p(out), ldo, col_off
-    _lib.check(lib.fgdm_conv_gemm(C.byref(args), _stream()), "fgdm_conv_gemm")
+    kdim = (9 if conv != CONV_1X1 else 1) * (c0 + c1)
+    nres = (res0 is not None) + (res1 is not None)
+    _call("fgdm_conv_gemm", ("gemm taps=%d m=%d k=%d n=%d" % (9 if conv != CONV_1X1 else 1, m, kdim, n), 2.0 * m * n * kdim,
+                             2.0 * (m * (c0 + c1) + n * kdim + m * n * (1 + nres))), C.byref(args), _stream())
     return out
 
 
 def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):
     scale = d ** -0.5 if scale is None else scale
-    _lib.check(_lib.load().fgdm_attention(_p(q), _p(k), _p(vt), _p(out), images, heads, nq, nk, d, tok_pad,
-                                         scale, _stream()), "fgdm_attention")
+    _call("fgdm_attention", ("attn d=%d nq=%d nk=%d" % (d, nq, nk), 4.0 * images * heads * nq * nk * d, 2.0 * images * heads * d * (2 * nq + 2 * nk)), _p(q), _p(k), _p(vt), _p(out), images, heads, nq, nk, d, tok_pad,
+                                         scale, _stream())
     return out
 
 
@@ -104,8 +142,8 @@ def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=
     if out is None:
         out = torch.empty(tuple(x0.shape[:-1]) + (c0 + c1,), device=x0.device, dtype=bf16)
     ws = _gn_workspace(x0.device, nb, groups)
-    _lib.check(_lib.load().fgdm_groupnorm(_p(x0), _p(x1), _p(out), _p(gamma), _p(beta), _p(ws), nb, hw, c0, c1,
-                                         groups, eps, 1 if silu else 0, _stream()), "fgdm_groupnorm")
+    _call("fgdm_groupnorm", ("gn c=%d hw=%d" % (c0 + c1, hw), 0.0, 4.0 * nb * hw * (c0 + c1)), _p(x0), _p(x1), _p(out), _p(gamma), _p(beta), _p(ws), nb, hw, c0, c1,
+                                         groups, eps, 1 if silu else 0, _stream())
     return out
 
 
@@ -114,8 +152,7 @@ def layernorm(x, gamma, beta, eps=1e-5, out=None):
     rows = x.numel() // c
     if out is None:
         out = torch.empty_like(x)
-    _lib.check(_lib.load().fgdm_layernorm(_p(x), _p(out), _p(gamma), _p(beta), rows, c, eps, _stream()),
-               "fgdm_layernorm")
+    _call("fgdm_layernorm", ("ln c=%d" % c, 0.0, 4.0 * rows * c), _p(x), _p(out), _p(gamma), _p(beta), rows, c, eps, _stream())
     return out
 
 
@@ -123,7 +160,7 @@ def softmax_rows(s, scale, out=None):
     rows, cols = s.shape
     if out is None:
         out = torch.empty((rows, cols), device=s.device, dtype=bf16)
-    _lib.check(_lib.load().fgdm_softmax_rows(_p(s), _p(out), rows, cols, scale, _stream()), "fgdm_softmax_rows")
+    _call("fgdm_softmax_rows", ("softmax", 0.0, 6.0 * rows * cols), _p(s), _p(out), rows, cols, scale, _stream())
     return out
 
 
@@ -133,16 +170,15 @@ def cfg_ddim_step(e_uncond, e_cond, x, coef_table, index, scale, *, noise=None, 
         x_prev = torch.empty_like(x)
     if pred_x0 is None:
         pred_x0 = torch.empty_like(x)
-    _lib.check(_lib.load().fgdm_cfg_ddim_step(_p(e_uncond), _p(e_cond), _p(x), _p(noise), _p(coef_table),
+    _call("fgdm_cfg_ddim_step", ("cfg_ddim", 0.0, 20.0 * x.numel()), _p(e_uncond), _p(e_cond), _p(x), _p(noise), _p(coef_table),
                                              _p(index_ptr), index, scale, temperature, _p(x_prev), _p(pred_x0),
-                                             x.numel(), _stream()), "fgdm_cfg_ddim_step")
+                                             x.numel(), _stream())
     return x_prev, pred_x0
 
 
 def timestep_embedding(t, freqs, dim):
     out = torch.empty((t.shape[0], dim), device=t.device, dtype=torch.float32)
-    _lib.check(_lib.load().fgdm_timestep_embedding(_p(t), _p(freqs), _p(out), t.shape[0], dim, _stream()),
-               "fgdm_timestep_embedding")
+    _call("fgdm_timestep_embedding", ("temb", 0.0, 4.0 * t.shape[0] * dim), _p(t), _p(freqs), _p(out), t.shape[0], dim, _stream())
     return out
 
 
@@ -150,8 +186,8 @@ def skinny_linear(x, w, b, in_act=False, out_act=False):
     rows, k = x.shape
     n = w.shape[0]
     y = torch.empty((rows, n), device=x.device, dtype=torch.float32)
-    _lib.check(_lib.load().fgdm_skinny_linear(_p(x), _p(w), _p(b), _p(y), rows, k, n, int(in_act), int(out_act),
-                                             _stream()), "fgdm_skinny_linear")
+    _call("fgdm_skinny_linear", ("skinny k=%d n=%d" % (k, n), 2.0 * rows * k * n, 4.0 * (k * n + rows * (k + n))), _p(x), _p(w), _p(b), _p(y), rows, k, n, int(in_act), int(out_act),
+                                             _stream())
     return y
 
 
@@ -164,14 +200,14 @@ def resample(x, mode):
         out = torch.empty((nb, h // 2, w // 2, c), device=x.device, dtype=bf16)
     else:
         out = torch.empty((4, nb, h // 2, w // 2, c), device=x.device, dtype=bf16)
-    _lib.check(_lib.load().fgdm_resample(_p(x), _p(out), nb, h, w, c, mode, _stream()), "fgdm_resample")
+    _call("fgdm_resample", ("resample mode=%d" % mode, 0.0, 2.0 * (x.numel() + out.numel())), _p(x), _p(out), nb, h, w, c, mode, _stream())
     return out
 
 
 def add_bf16(a, b, out=None):
     if out is None:
         out = torch.empty_like(a)
-    _lib.check(_lib.load().fgdm_add_bf16(_p(a), _p(b), _p(out), a.numel(), _stream()), "fgdm_add_bf16")
+    _call("fgdm_add_bf16", ("add", 0.0, 6.0 * a.numel()), _p(a), _p(b), _p(out), a.numel(), _stream())
     return out
 
 
@@ -180,21 +216,21 @@ def conv_small_cin(x, w, bias, cout, act=ACT_NONE, in_scale=1.0, nb_out=None):
     nb_in, cin, h, wd = x.shape
     nb = nb_out or nb_in
     y = torch.empty((nb, h, wd, cout), device=x.device, dtype=bf16)
-    _lib.check(_lib.load().fgdm_conv_small_cin(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, act, in_scale,
-                                              nb_in, _stream()), "fgdm_conv_small_cin")
+    _call("fgdm_conv_small_cin", ("conv_small_cin %d->%d" % (cin, cout), 18.0 * nb * h * wd * cin * cout, 4.0 * nb * cin * h * wd + 2.0 * y.numel()), _p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, act, in_scale,
+                                              nb_in, _stream())
     return y
 
 
 def ddim_advance(counter, t_table, idx_table, t_out, index_out):
-    _lib.check(_lib.load().fgdm_ddim_advance(_p(counter), _p(t_table), _p(idx_table), _p(t_out), t_out.numel(),
-                                            _p(index_out), _stream()), "fgdm_ddim_advance")
+    _call("fgdm_ddim_advance", ("advance", 0.0, 0.0), _p(counter), _p(t_table), _p(idx_table), _p(t_out), t_out.numel(),
+                                            _p(index_out), _stream())
 
 
 def conv_direct(x, w, bias, cout, stride=1, act=ACT_NONE):
     nb, h, wd, cin = x.shape
     y = torch.empty((nb, h // stride, wd // stride, cout), device=x.device, dtype=bf16)
-    _lib.check(_lib.load().fgdm_conv_direct(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, stride, act,
-                                           _stream()), "fgdm_conv_direct")
+    _call("fgdm_conv_direct", ("conv_direct %d->%d s%d" % (cin, cout, stride), 18.0 * y.numel() * cin, 2.0 * (x.numel() + y.numel())), _p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, stride, act,
+                                           _stream())
     return y
 
 
@@ -202,37 +238,35 @@ def conv_small_cout(x, w, bias, cout):
     """x: NHWC bf16 -> NCHW fp32 [nb, cout, h, w] with cout in {3, 4}."""
     nb, h, wd, cin = x.shape
     y = torch.empty((nb, cout, h, wd), device=x.device, dtype=torch.float32)
-    _lib.check(_lib.load().fgdm_conv_small_cout(_p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, _stream()),
-               "fgdm_conv_small_cout")
+    _call("fgdm_conv_small_cout", ("conv_small_cout %d->%d" % (cin, cout), 18.0 * nb * h * wd * cin * cout, 2.0 * x.numel() + 4.0 * y.numel()), _p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, _stream())
     return y
 
 
 def latent_affine(x, w, b, in_scale):
     nb, c, h, wd = x.shape
     y = torch.empty_like(x)
-    _lib.check(_lib.load().fgdm_latent_affine(_p(x), _p(w), _p(b), _p(y), nb, c, h * wd, in_scale, _stream()),
-               "fgdm_latent_affine")
+    _call("fgdm_latent_affine", ("latent_affine", 0.0, 8.0 * x.numel()), _p(x), _p(w), _p(b), _p(y), nb, c, h * wd, in_scale, _stream())
     return y
 
 
 def image_to_u8(x, mode):
     nb, c, h, wd = x.shape
     y = torch.empty((nb, h, wd, c), device=x.device, dtype=torch.uint8)
-    _lib.check(_lib.load().fgdm_image_to_u8(_p(x), _p(y), nb, c, h * wd, mode, _stream()), "fgdm_image_to_u8")
+    _call("fgdm_image_to_u8", ("image_to_u8", 0.0, 5.0 * x.numel()), _p(x), _p(y), nb, c, h * wd, mode, _stream())
     return y
 
 
 def resize_u8(src, dh, dw):
     nb, sh, sw, c = src.shape
     dst = torch.empty((nb, dh, dw, c), device=src.device, dtype=torch.uint8)
-    _lib.check(_lib.load().fgdm_resize_u8(_p(src), _p(dst), nb, sh, sw, dh, dw, c, _stream()), "fgdm_resize_u8")
+    _call("fgdm_resize_u8", ("resize_u8", 0.0, 1.0 * (src.numel() + dst.numel())), _p(src), _p(dst), nb, sh, sw, dh, dw, c, _stream())
     return dst
 
 
 def u8_to_hint(src):
     nb, h, wd, c = src.shape
     dst = torch.empty((nb, c, h, wd), device=src.device, dtype=torch.float32)
-    _lib.check(_lib.load().fgdm_u8_to_hint(_p(src), _p(dst), nb, c, h * wd, _stream()), "fgdm_u8_to_hint")
+    _call("fgdm_u8_to_hint", ("u8_to_hint", 0.0, 5.0 * src.numel()), _p(src), _p(dst), nb, c, h * wd, _stream())
     return dst
 
 

@@ -390,7 +390,7 @@ def ddim_update(x, e_t, sched, index, noise=None, temperature=1.0):
 
 
 def ddim_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod, eta=0.0, log_every_t=100,
-                sequential_cfg=False, record=None):
+                sequential_cfg=False, record=None, max_steps=None):
     """DDIMSampler.sample/ddim_sampling/p_sample_ddim with CFG.
     sequential_cfg=False: ldm/models/diffusion/ddim.py:116-177,221-243 (one batched call on cat([uc, c])).
     sequential_cfg=True:  controlnet/cldm/ddim_hacked.py:150-192 (cond call then uncond call).
@@ -404,6 +404,8 @@ def ddim_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod,
     inter = {"x_inter": [img], "pred_x0": [img]}
     total = ts.shape[0]
     for i, step in enumerate(np.flip(ts)):
+        if max_steps is not None and i >= max_steps:   # timing aid: run only the first steps of the loop
+            break
         index = total - i - 1
         t = torch.full((b,), int(step), device=img.device, dtype=torch.long)
         if uncond is None or scale == 1.0:
