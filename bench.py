@@ -182,6 +182,9 @@ def kernel_rooflines(pipe, dev_in, pk):
     kv_u, kv_c, gh = unet.project_context(ctx), cn.project_context(ctx), cn.encode_hint(hint)
     for it in range(2):                                    # first pass warms, second is recorded
         if it == 1:
+            # let the host run ahead of the device: with every launch already queued, the event intervals are
+            # kernel execution time, not Python launch latency
+            torch.cuda._sleep(int(0.25 * 1.9e9))
             ops.profile_start()
         seg.model.diffusion_model.forward(dev_in["xT_seg"], t, kv=kv_s, rows=2 * B)
         img.control_step(dev_in["xT_img"], t, kv_u, kv_c, gh, 2 * B)
@@ -298,7 +301,27 @@ def run_ours(args, rank, world, local_rank):
 
     if rank != 0:
         return
-    roof, table, _ = kernel_rooflines(pipe, dev_in, pk)
+    # phase timings (CUDA events around graph replays / decodes): the "UNet step ms" half of the metric
+    def ms_of(fn, n):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+    gs = next(iter(pipe.seg_sampler._graphs.values()))
+    gi = next(iter(pipe.img_sampler._graphs.values()))
+    phases = {"seg_unet_cfg_step_ms": ms_of(gs.graph.replay, 10), "img_controlnet_unet_cfg_step_ms": ms_of(gi.graph.replay, 10),
+              "vae_decode_ms": ms_of(lambda: seg.decode_first_stage(dev_in["xT_seg"] * 0.18215), 3),
+              "rows_per_step": 2 * B, "kernels_per_seg_step": gs.launches_per_step,
+              "kernels_per_img_step": gi.launches_per_step}
+    roof, table, prof = kernel_rooflines(pipe, dev_in, pk)
+    if args.dump_shapes:
+        flat = [{"kernel": k, "shape": sk, "launches": v[0], "ms": v[1], "flops": v[2], "bytes": v[3]}
+                for k, sh in prof.items() for sk, v in sh.items()]
+        json.dump(sorted(flat, key=lambda r: -r["ms"]), open(args.dump_shapes, "w"), indent=0)
     flop_img = S * 1717.4e9 + S * 2173.2e9 + 2 * 2514.5e9
     step_tf = flop_img * B / (ms / args.steps * 1e-3) / 1e12
     line = {"metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
@@ -315,7 +338,7 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roof,
             "roofline_step": {"algorithmic_tflop_per_image": flop_img / 1e12, "achieved_tflops_per_gpu": step_tf,
                               "frac_of_bf16_sustained": step_tf / pk["tf_sust"]},
-            "kernels": table}
+            "phases": phases, "kernels": table}
     if keep_sd:
         cpu = CpuChain(sd_seg, sd_img)
         cpu.decode_once()
@@ -338,6 +361,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8, help="prompts per GPU (BASELINE configs[1]: 8)")
     ap.add_argument("--ddim-steps", type=int, default=50)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dump-shapes", default="", help="write the per-launch-shape table of the roofline pass here")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -12,9 +12,9 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfgdm_b200.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
-OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32 = 0, 1, 2, 3
+OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32, OUT_NCHW_F32 = 0, 1, 2, 3, 4
 ACT_NONE, ACT_SILU, ACT_RELU = 0, 1, 2
 CONV_1X1, CONV_3X3, CONV_3X3_S2 = 0, 1, 2
 
@@ -31,7 +31,7 @@ class GemmArgs(C.Structure):
         ("alpha", C.c_float), ("act", C.c_int), ("out_mode", C.c_int),
         ("out", vp), ("ldo", C.c_int), ("col_off", C.c_int),
         ("q_out", vp), ("k_out", vp), ("vt_out", vp), ("qkv_first", C.c_int),
-        ("heads", C.c_int), ("dhead", C.c_int), ("tok_pad", C.c_int), ("bn_hint", C.c_int),
+        ("heads", C.c_int), ("dhead", C.c_int), ("tok_pad", C.c_int), ("bn_hint", C.c_int), ("n_store", C.c_int),
     ]
 
 
@@ -51,6 +51,7 @@ SIGNATURES = {
     "fgdm_add_bf16": [vp, vp, vp, C.c_size_t, vp],
     "fgdm_conv_small_cin": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int,
                             vp],
+    "fgdm_im2col_small": [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp],
     "fgdm_ddim_advance": [vp, vp, vp, vp, C.c_int, vp, vp],
     "fgdm_conv_direct": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_conv_small_cout": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],

@@ -104,12 +104,14 @@ int launch_cfg_ddim(const float* e_u, const float* e_c, const float* x, const fl
                     int n, cudaStream_t stream);
 int launch_timestep_embedding(const long long* t, const float* freqs, float* out, int rows, int dim,
                               cudaStream_t stream);
-int launch_skinny_linear(const float* x, const float* w, const float* b, float* y, int R, int K, int N, int in_act,
+int launch_skinny_linear(const float* x, const void* w, const float* b, float* y, int R, int K, int N, int in_act,
                          int out_act, cudaStream_t stream);
 int launch_resample(const void* in, void* out, int NB, int H, int W, int C, int mode, cudaStream_t stream);
 int launch_add_bf16(const void* a, const void* b, void* out, size_t n, cudaStream_t stream);
 int launch_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int NB, int H, int W, int Cin,
                           int Cout, int act, float in_scale, int nb_in, cudaStream_t stream);
+int launch_im2col_small(const float* x, void* out, int NB, int H, int W, int Cin, float in_scale, int nb_in,
+                        cudaStream_t stream);
 int launch_ddim_advance(int* counter, const long long* t_table, const int* idx_table, long long* t_out, int rows,
                         int* index_out, cudaStream_t stream);
 int launch_conv_direct(const void* x, const void* w, const float* bias, void* y, int NB, int H, int W, int Cin,
@@ -201,6 +203,7 @@ int fgdm_conv_gemm(const fgdm_gemm_args* a, void* stream) {
   p.out = a->out;
   p.ldo = a->ldo;
   p.col_off = a->col_off;
+  p.n_store = a->n_store;
   if (a->out_mode == FGDM_OUT_QKV) {
     if (a->dhead % 8 != 0 || a->heads <= 0 || a->tok_pad % 8 != 0) {
       set_error("fgdm_conv_gemm: QKV mode needs dhead %% 8 == 0, tok_pad %% 8 == 0 (dhead=%d tok_pad=%d)", a->dhead,
@@ -218,6 +221,9 @@ int fgdm_conv_gemm(const fgdm_gemm_args* a, void* stream) {
     p.dhead = a->dhead;
     p.inner = a->heads * a->dhead;
     p.tok_pad = a->tok_pad;
+  } else if (a->out_mode == FGDM_OUT_NCHW_F32) {
+    FGDM_NONNULL(a->out, "out");
+    if (a->n_store <= 0 || a->n_store > a->n) { set_error("fgdm_conv_gemm: n_store=%d out of range", a->n_store); return -2; }
   } else {
     FGDM_NONNULL(a->out, "out");
     if (a->ldo % 8 != 0 || a->col_off % 8 != 0) {
@@ -270,7 +276,7 @@ int fgdm_timestep_embedding(const int64_t* t, const float* freqs, float* out, in
                                    reinterpret_cast<cudaStream_t>(stream));
 }
 
-int fgdm_skinny_linear(const float* x, const float* w, const float* b, float* y, int rows, int k, int n, int in_act,
+int fgdm_skinny_linear(const float* x, const void* w, const float* b, float* y, int rows, int k, int n, int in_act,
                        int out_act, void* stream) {
   FGDM_NONNULL(x, "x"); FGDM_NONNULL(w, "w"); FGDM_NONNULL(y, "y");
   return launch_skinny_linear(x, w, b, y, rows, k, n, in_act, out_act, reinterpret_cast<cudaStream_t>(stream));
@@ -292,6 +298,12 @@ int fgdm_conv_small_cin(const float* x, const void* w, const float* bias, void* 
   FGDM_NONNULL(x, "x"); FGDM_NONNULL(w, "w"); FGDM_NONNULL(y, "y");
   return launch_conv_small_cin(x, w, bias, y, nb, h, w_, cin, cout, act, in_scale, nb_in,
                                reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_im2col_small(const float* x, void* out, int nb, int h, int w_, int cin, float in_scale, int nb_in,
+                      void* stream) {
+  FGDM_NONNULL(x, "x"); FGDM_NONNULL(out, "out");
+  return launch_im2col_small(x, out, nb, h, w_, cin, in_scale, nb_in, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int fgdm_ddim_advance(int* counter, const int64_t* t_table, const int* idx_table, int64_t* t_out, int rows,

@@ -16,6 +16,7 @@
 // attention.py:199-200) is dead at inference (only [0] is used, attention.py:235-238) and is not
 // produced.
 #include "common.cuh"
+#include <type_traits>
 
 namespace fgdm {
 
@@ -34,21 +35,33 @@ struct AttnParams {
 };
 
 static constexpr int kAttnThreads = 128;
+static constexpr float kRescaleThreshold = 8.0f;   // log2 units: P <= 2^8 before a row's reference max is refreshed
 
-template <int KA, int DV>
+// KA: 64-wide K-chunks of the head dim (Q/K tiles are KA swizzle atoms), DV: V columns of this CTA,
+// BN: keys per tile (128, or 64 when the head dim is large so that two CTAs still fit on an SM).
+template <int KA, int DV, int BN>
 struct AttnCfg {
-  static constexpr int kQBytes = KA * 128 * 128;       // KA swizzle atoms of [128 rows x 128 B]
-  static constexpr int kKBytes = KA * 128 * 128;
-  static constexpr int kVBytes = 2 * DV * 128;         // two key-atoms of [DV rows x 128 B]
-  static constexpr int kPBytes = 2 * 128 * 128;
+  static constexpr int kQBytes = KA * 128 * 128;       // KA atoms of [128 rows x 128 B]
+  static constexpr int kKBytes = KA * BN * 128;        // KA atoms of [BN rows x 128 B]
+  static constexpr int kVAtom = DV * 128;              // one key-atom (64 keys) of [DV rows x 128 B]
+  static constexpr int kVBytes = (BN / 64) * kVAtom;
+  static constexpr int kPBytes = (BN / 64) * 128 * 128;
   static constexpr int kSmemBytes = kQBytes + 2 * (kKBytes + kVBytes) + kPBytes + 1024 + 128;
+  static constexpr int kTmemCols = (BN + DV <= 128) ? 128 : 256;
 };
 
-template <int KA, int DV>
-__global__ void __launch_bounds__(kAttnThreads)
+// Flow per KV tile j (one thread per query row, all 128 threads alike; thread 0 also drives TMA + MMA):
+//   wait S(j) | tcgen05.ld the whole S row into registers | row max | wait PV(j-1) | refresh the row's
+//   reference max only if it grew by > 2^8 (then rescale l and the O row in TMEM: rare) | exp2 -> bf16 P tile
+//   in swizzled smem | barrier | thread 0: issue S(j+1) then PV(j) (O accumulates in TMEM) and prefetch K/V.
+// The softmax of tile j+1 therefore overlaps PV(j) on the tensor pipe, and the second CTA resident on the SM
+// covers this CTA's wait for S(j+1). O is read from TMEM once, at the end.
+template <int KA, int DV, int BN>
+__global__ void __launch_bounds__(kAttnThreads, 2)
 attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
-  using Cfg = AttnCfg<KA, DV>;
+  using Cfg = AttnCfg<KA, DV, BN>;
+  constexpr int kPA = BN / 64;                          // key-atoms per tile
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -58,32 +71,34 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   uint8_t* sP = sV + 2 * Cfg::kVBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + Cfg::kPBytes);
   uint64_t* bar_q = bars;
-  uint64_t* bar_kv = bars + 1;  // [2]
-  uint64_t* bar_s = bars + 3;
-  uint64_t* bar_o = bars + 4;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 5);
+  uint64_t* bar_k = bars + 1;   // [2]
+  uint64_t* bar_v = bars + 3;   // [2]
+  uint64_t* bar_s = bars + 5;
+  uint64_t* bar_o = bars + 6;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 7);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int q0 = blockIdx.x * 128;
   const int bh = blockIdx.y;
-  const int split = blockIdx.z;
-  const int v0 = split * p.dv_per;                  // first V column of this CTA
-  const int num_kv = (p.Nk + 127) / 128;
+  const int v0 = blockIdx.z * p.dv_per;             // first V column of this CTA
+  const int num_kv = (p.Nk + BN - 1) / BN;
 
   if (tid == 0) {
     tma_prefetch_desc(&map_q);
     tma_prefetch_desc(&map_k);
     tma_prefetch_desc(&map_vt);
     mbar_init(bar_q, 1);
-    mbar_init(&bar_kv[0], 1);
-    mbar_init(&bar_kv[1], 1);
+    mbar_init(&bar_k[0], 1);
+    mbar_init(&bar_k[1], 1);
+    mbar_init(&bar_v[0], 1);
+    mbar_init(&bar_v[1], 1);
     mbar_init(bar_s, 1);
     mbar_init(bar_o, 1);
     fence_barrier_init();
   }
   if (warp == 0) {
-    tmem_alloc(tmem_ptr, 256);
+    tmem_alloc(tmem_ptr, Cfg::kTmemCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -91,100 +106,143 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   const uint32_t tmem_s = tmem_base;
-  const uint32_t tmem_o = tmem_base + 128;
+  const uint32_t tmem_o = tmem_base + BN;
 
-  auto load_kv = [&](int j) {
+  // K(j) is released as soon as S(j) has completed, V(j) only after PV(j): separate barriers let K run two
+  // tiles ahead and V one and a half.
+  auto load_k = [&](int j) {
     const int st = j & 1;
-    mbar_expect_tx(&bar_kv[st], Cfg::kKBytes + Cfg::kVBytes);
+    mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
 #pragma unroll
     for (int a = 0; a < KA; ++a)
-      tma_load_3d(sK + st * Cfg::kKBytes + a * 16384, &map_k, &bar_kv[st], a * 64, j * 128, bh);
+      tma_load_3d(sK + st * Cfg::kKBytes + a * (BN * 128), &map_k, &bar_k[st], a * 64, j * BN, bh);
+  };
+  auto load_v = [&](int j) {
+    const int st = j & 1;
+    mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
-      tma_load_3d(sV + st * Cfg::kVBytes + a * (DV * 128), &map_vt, &bar_kv[st], j * 128 + a * 64, v0, bh);
+    for (int a = 0; a < kPA; ++a)
+      tma_load_3d(sV + st * Cfg::kVBytes + a * Cfg::kVAtom, &map_vt, &bar_v[st], j * BN + a * 64, v0, bh);
   };
   auto issue_s = [&](int j) {
     const int st = j & 1;
-    constexpr uint32_t idesc = make_idesc_bf16(128, 128);
+    constexpr uint32_t idesc = make_idesc_bf16(128, BN);
 #pragma unroll
     for (int a = 0; a < KA; ++a) {
       const uint64_t dq = make_desc_sw128(smem_u32(sQ + a * 16384));
-      const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes + a * 16384));
+      const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes + a * (BN * 128)));
 #pragma unroll
       for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem_s, dq + 2 * k, dk + 2 * k, idesc, (a | k) != 0 ? 1u : 0u);
     }
     tc_commit(bar_s);
+  };
+  auto issue_pv = [&](int j) {
+    const int st = j & 1;
+    constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
+#pragma unroll
+    for (int ks = 0; ks < BN / 16; ++ks) {
+      const uint64_t dp = make_desc_sw128(smem_u32(sP + (ks >> 2) * 16384)) + 2 * (ks & 3);
+      const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes + (ks >> 2) * Cfg::kVAtom)) + 2 * (ks & 3);
+      tc_mma_bf16(tmem_o, dp, dv, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+    }
+    tc_commit(bar_o);
   };
 
   if (tid == 0) {
     mbar_expect_tx(bar_q, Cfg::kQBytes);
 #pragma unroll
     for (int a = 0; a < KA; ++a) tma_load_3d(sQ + a * 16384, &map_q, bar_q, a * 64, q0, bh);
-    load_kv(0);
-    if (num_kv > 1) load_kv(1);
+    load_k(0);
+    load_v(0);
+    if (num_kv > 1) {
+      load_k(1);
+      load_v(1);
+    }
     mbar_wait(bar_q, 0);
-    mbar_wait(&bar_kv[0], 0);
+    mbar_wait(&bar_k[0], 0);
     tc_fence_after();
     issue_s(0);
   }
 
-  const int quarter = warp & 3;
-  const int row = quarter * 32 + (tid & 31);          // == tid for a 128-thread CTA
-  const uint32_t lane_addr = static_cast<uint32_t>(quarter * 32) << 16;
-  float m_run = -INFINITY;
+  const int row = tid;                                // TMEM lane == query row within the tile
+  const uint32_t lane_addr = static_cast<uint32_t>(warp * 32) << 16;
+  float m_ref = -INFINITY;                            // reference max (scaled, log2 domain) used for exp2
   float l_run = 0.0f;
-  float acc[DV];
-#pragma unroll
-  for (int i = 0; i < DV; ++i) acc[i] = 0.0f;
 
   for (int j = 0; j < num_kv; ++j) {
-    const int kv0 = j * 128;
-    const int valid = p.Nk - kv0;                      // keys valid in this tile (may exceed 128)
+    const int valid = p.Nk - j * BN;                   // keys valid in this tile (may exceed BN)
     mbar_wait(bar_s, j & 1);
     tc_fence_after();
+    if (tid == 0 && j + 2 < num_kv) load_k(j + 2);     // K stage j&1 is free: S(j) has completed
 
-    // ---- pass 1: row maximum ----
+    // ---- whole S row -> registers, row maximum ----
+    uint32_t s[BN];
+#pragma unroll
+    for (int c = 0; c < BN; c += 32) tmem_ld_32x32(tmem_s + lane_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
+    tmem_ld_wait();
     float tmax = -INFINITY;
-#pragma unroll 1
-    for (int c = 0; c < 128; c += 32) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_s + lane_addr + c, r);
-      tmem_ld_wait();
+    if (valid >= BN) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float s = (c + i < valid) ? __uint_as_float(r[i]) : -INFINITY;
-        tmax = fmaxf(tmax, s);
-      }
+      for (int i = 0; i < BN; ++i) tmax = fmaxf(tmax, __uint_as_float(s[i]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < BN; ++i) tmax = fmaxf(tmax, (i < valid) ? __uint_as_float(s[i]) : -INFINITY);
     }
-    const float m_new = fmaxf(m_run, tmax * p.scale_log2);
-    const float alpha = fast_exp2(m_run - m_new);          // exp2(-inf) = 0 on the first tile
-    m_run = m_new;
+    tmax *= p.scale_log2;
 
-    // ---- pass 2: probabilities -> bf16 P tile in smem (128B swizzle, K-major) ----
-    float lsum = 0.0f;
-#pragma unroll 1
-    for (int c = 0; c < 128; c += 32) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_s + lane_addr + c, r);
-      tmem_ld_wait();
-      uint32_t packed[16];
+    // ---- PV(j-1) must have drained before O is touched or the P tile is overwritten ----
+    if (j > 0) {
+      mbar_wait(bar_o, (j - 1) & 1);
+      tc_fence_after();
+      if (tid == 0 && j + 1 < num_kv) load_v(j + 1);   // V stage (j+1)&1 == (j-1)&1 is free now
+    }
+
+    // ---- lazy rescale: refresh the reference max only when it grew by more than 2^8 ----
+    const bool need = tmax > m_ref + kRescaleThreshold;
+    if (__any_sync(0xffffffffu, need)) {
+      const float m_new = need ? tmax : m_ref;
+      const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
+      l_run *= alpha;
+      m_ref = m_new;
+      if (j > 0) {
 #pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        float p0 = (c + i < valid) ? fast_exp2(__uint_as_float(r[i]) * p.scale_log2 - m_new) : 0.0f;
-        float p1 = (c + i + 1 < valid) ? fast_exp2(__uint_as_float(r[i + 1]) * p.scale_log2 - m_new) : 0.0f;
-        lsum += p0 + p1;
-        packed[i >> 1] = pack_bf16x2(p0, p1);
-      }
-      uint8_t* atom = sP + (c >> 6) * 16384 + row * 128;
-      const int chunk0 = (c & 63) >> 3;                // first 16-byte chunk of this 32-column slice
+        for (int c = 0; c < DV; c += 16) {
+          uint32_t r[16];
+          tmem_ld_32x16(tmem_o + lane_addr + c, r);
+          tmem_ld_wait();
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int chunk = (chunk0 + q) ^ (row & 7);
-        *reinterpret_cast<uint4*>(atom + chunk * 16) =
-            make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+          for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st_32x16(tmem_o + lane_addr + c, r);
+        }
+        tmem_st_wait();
       }
     }
-    l_run = l_run * alpha + lsum;
+
+    // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major); row sum ----
+    float lsum = 0.0f;
+    const float neg_m = -m_ref;
+    auto emit = [&](auto masked) {
+#pragma unroll
+      for (int c = 0; c < BN; c += 8) {
+        uint32_t pk[4];
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+          float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
+          float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
+          if constexpr (decltype(masked)::value) {
+            if (c + i >= valid) p0 = 0.0f;
+            if (c + i + 1 >= valid) p1 = 0.0f;
+          }
+          lsum += p0 + p1;
+          pk[i >> 1] = pack_bf16x2(p0, p1);
+        }
+        uint8_t* atom = sP + (c >> 6) * 16384 + row * 128;
+        const int chunk = ((c & 63) >> 3) ^ (row & 7);
+        *reinterpret_cast<uint4*>(atom + chunk * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      }
+    };
+    if (valid >= BN) emit(std::false_type{}); else emit(std::true_type{});
+    l_run += lsum;
 
     fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
     tc_fence_before();
@@ -192,52 +250,40 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 
     if (tid == 0) {
       tc_fence_after();
-      const int st = j & 1;
-      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
-#pragma unroll
-      for (int ks = 0; ks < 8; ++ks) {
-        const uint64_t dp = make_desc_sw128(smem_u32(sP + (ks >> 2) * 16384)) + 2 * (ks & 3);
-        const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes + (ks >> 2) * (DV * 128))) + 2 * (ks & 3);
-        tc_mma_bf16(tmem_o, dp, dv, idesc_pv, ks != 0 ? 1u : 0u);
-      }
-      tc_commit(bar_o);
       if (j + 1 < num_kv) {
-        mbar_wait(&bar_kv[(j + 1) & 1], ((j + 1) >> 1) & 1);
+        mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
         tc_fence_after();
-        issue_s(j + 1);          // runs behind PV(j) in the tensor pipe; S(j) has been fully read
+        issue_s(j + 1);          // ahead of PV(j) in the tensor pipe: the next softmax can start sooner
       }
+      mbar_wait(&bar_v[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      issue_pv(j);
     }
-    __syncwarp();
-
-    // ---- O = O * alpha + P V ----
-    mbar_wait(bar_o, j & 1);
-    tc_fence_after();
-#pragma unroll
-    for (int c = 0; c < DV; c += 16) {
-      uint32_t r[16];
-      tmem_ld_32x16(tmem_o + lane_addr + c, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 16; ++i) acc[c + i] = acc[c + i] * alpha + __uint_as_float(r[i]);
-    }
-    // K/V stage (j&1) is free now: S(j) and PV(j) have completed.
-    if (tid == 0 && j + 2 < num_kv) load_kv(j + 2);
-    tc_fence_before();  // order this iteration's TMEM reads before the next S/PV writes (after barrier)
   }
 
   // ---- normalise and store: out[img, q, head*d + v0 + e] ----
+  mbar_wait(bar_o, (num_kv - 1) & 1);
+  tc_fence_after();
   const int q = q0 + row;
-  if (q < p.Nq) {
-    const float inv = 1.0f / l_run;
-    const int img = bh / p.heads;
-    const int head = bh - img * p.heads;
-    __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0;
+  const float inv = 1.0f / l_run;
+  const int img = bh / p.heads;
+  const int head = bh - img * p.heads;
+  __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0;
 #pragma unroll
-    for (int c = 0; c < DV; c += 8) {
-      if (c < p.dv_per && v0 + c < p.d) {
-        *reinterpret_cast<uint4*>(dst + c) =
-            make_uint4(pack_bf16x2(acc[c] * inv, acc[c + 1] * inv), pack_bf16x2(acc[c + 2] * inv, acc[c + 3] * inv),
-                       pack_bf16x2(acc[c + 4] * inv, acc[c + 5] * inv), pack_bf16x2(acc[c + 6] * inv, acc[c + 7] * inv));
+  for (int c = 0; c < DV; c += 16) {
+    uint32_t r[16];
+    tmem_ld_32x16(tmem_o + lane_addr + c, r);
+    tmem_ld_wait();
+    if (q < p.Nq) {
+#pragma unroll
+      for (int h8 = 0; h8 < 16; h8 += 8) {
+        if (c + h8 < p.dv_per && v0 + c + h8 < p.d) {
+          *reinterpret_cast<uint4*>(dst + c + h8) =
+              make_uint4(pack_bf16x2(__uint_as_float(r[h8]) * inv, __uint_as_float(r[h8 + 1]) * inv),
+                         pack_bf16x2(__uint_as_float(r[h8 + 2]) * inv, __uint_as_float(r[h8 + 3]) * inv),
+                         pack_bf16x2(__uint_as_float(r[h8 + 4]) * inv, __uint_as_float(r[h8 + 5]) * inv),
+                         pack_bf16x2(__uint_as_float(r[h8 + 6]) * inv, __uint_as_float(r[h8 + 7]) * inv));
+        }
       }
     }
   }
@@ -246,17 +292,17 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   __syncthreads();
   if (warp == 0) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256);
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
-template <int KA, int DV>
+template <int KA, int DV, int BN>
 static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
                        int nsplit, cudaStream_t stream) {
-  using Cfg = AttnCfg<KA, DV>;
+  using Cfg = AttnCfg<KA, DV, BN>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention_kernel<KA, DV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(attention_kernel<KA, DV, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("attention: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -265,7 +311,7 @@ static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUten
     configured = true;
   }
   dim3 grid((p.Nq + 127) / 128, p.BH, nsplit);
-  attention_kernel<KA, DV><<<grid, kAttnThreads, Cfg::kSmemBytes, stream>>>(mq, mk, mv, p);
+  attention_kernel<KA, DV, BN><<<grid, kAttnThreads, Cfg::kSmemBytes, stream>>>(mq, mk, mv, p);
   return check_launch("attention_kernel");
 }
 
@@ -285,6 +331,7 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   p.out = reinterpret_cast<__nv_bfloat16*>(out);
   p.ld_out = heads * d;
   const int KA = (d + 63) / 64;
+  const int BN = (KA == 1) ? 128 : 64;   // keys per tile: two CTAs must fit on an SM
   const int nsplit = (d + 79) / 80;
   int dv_per = (d + nsplit - 1) / nsplit;
   dv_per = (dv_per + 15) / 16 * 16;
@@ -300,7 +347,7 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   {
     uint64_t dims[3] = {static_cast<uint64_t>(d), static_cast<uint64_t>(Nk), static_cast<uint64_t>(p.BH)};
     uint64_t strides[2] = {static_cast<uint64_t>(d) * 2, static_cast<uint64_t>(Nk) * d * 2};
-    uint32_t box[3] = {64, 128, 1};
+    uint32_t box[3] = {64, static_cast<uint32_t>(BN), 1};
     if (encode_tmap(&mk, k, 3, dims, strides, box)) return -1;
   }
   {
@@ -309,18 +356,18 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
     uint32_t box[3] = {64, static_cast<uint32_t>(dv_per), 1};
     if (encode_tmap(&mv, vt, 3, dims, strides, box)) return -1;
   }
-#define FGDM_ATTN_CASE(KA_, DV_) \
-  if (KA == KA_ && dv_per == DV_) return launch_attn<KA_, DV_>(mq, mk, mv, p, nsplit, stream);
-  FGDM_ATTN_CASE(1, 16)
-  FGDM_ATTN_CASE(1, 32)
-  FGDM_ATTN_CASE(1, 48)
-  FGDM_ATTN_CASE(1, 64)
-  FGDM_ATTN_CASE(2, 48)
-  FGDM_ATTN_CASE(2, 64)
-  FGDM_ATTN_CASE(2, 80)
-  FGDM_ATTN_CASE(3, 48)
-  FGDM_ATTN_CASE(3, 64)
-  FGDM_ATTN_CASE(3, 80)
+#define FGDM_ATTN_CASE(KA_, DV_, BN_) \
+  if (KA == KA_ && dv_per == DV_) return launch_attn<KA_, DV_, BN_>(mq, mk, mv, p, nsplit, stream);
+  FGDM_ATTN_CASE(1, 16, 128)
+  FGDM_ATTN_CASE(1, 32, 128)
+  FGDM_ATTN_CASE(1, 48, 128)
+  FGDM_ATTN_CASE(1, 64, 128)
+  FGDM_ATTN_CASE(2, 48, 64)
+  FGDM_ATTN_CASE(2, 64, 64)
+  FGDM_ATTN_CASE(2, 80, 64)
+  FGDM_ATTN_CASE(3, 48, 64)
+  FGDM_ATTN_CASE(3, 64, 64)
+  FGDM_ATTN_CASE(3, 80, 64)
 #undef FGDM_ATTN_CASE
   set_error("attention: no kernel instance for d=%d (KA=%d, dv_per=%d)", d, KA, dv_per);
   return -1;

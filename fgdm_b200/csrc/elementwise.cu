@@ -100,53 +100,82 @@ int launch_timestep_embedding(const long long* t, const float* freqs, float* out
 }
 
 // ---------------------------------------------------------------------------------------------
-// Skinny Linear: y[r, n] = out_act( in_act(x[r, :]) . W[n, :] + b[n] ), fp32, R small (<= a few
-// dozen rows). One warp per output column, 8 rows per pass. Used for time_embed
-// (openaimodel.py:538-542) and all ResBlock emb_layers (openaimodel.py:238-244) batched into one
-// weight matrix. Weight-read bound (each W row is read once per 8 rows).
+// Skinny Linear: y[r, n] = out_act( in_act(x[r, :]) . W[n, :] + b[n] ), x/y fp32, W bf16 [N, K], R small.
+// Used for time_embed (openaimodel.py:538-542) and all ResBlock emb_layers (openaimodel.py:238-244)
+// batched into one [20160, 1280] matrix. Weight-read bound: each W row is read exactly once per launch
+// (16-byte loads, one warp per output column, all <= 16 rows of a row-block accumulated together);
+// the activated x block is staged once per CTA in shared memory.
 // ---------------------------------------------------------------------------------------------
-__global__ void skinny_linear_kernel(const float* __restrict__ x, const float* __restrict__ w,
-                                     const float* __restrict__ b, float* __restrict__ y, int R, int K, int N,
-                                     int in_act, int out_act) {
-  const int n = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+static constexpr int kSkinnyRows = 16;
+
+__global__ void __launch_bounds__(256)
+skinny_linear_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w, const float* __restrict__ b,
+                     float* __restrict__ y, int R, int K, int N, int in_act, int out_act) {
+  extern __shared__ float xs[];   // [kSkinnyRows][K], in_act applied, rows >= R zero
+  const int r0 = blockIdx.y * kSkinnyRows;
+  for (int i = threadIdx.x; i < kSkinnyRows * K; i += blockDim.x) {
+    const int r = i / K, k = i - r * K;
+    float v = (r0 + r < R) ? x[static_cast<size_t>(r0 + r) * K + k] : 0.0f;
+    if (in_act) v = silu_f(v);
+    xs[i] = v;
+  }
+  __syncthreads();
   const int lane = threadIdx.x & 31;
-  if (n >= N) return;
-  const int r0 = blockIdx.y * 8;
-  float acc[8];
+  const int warp = threadIdx.x >> 5;
+  const int nwarps = gridDim.x * (blockDim.x >> 5);
+  for (int n = blockIdx.x * (blockDim.x >> 5) + warp; n < N; n += nwarps) {
+    float acc[kSkinnyRows];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
-  const float* wr = w + static_cast<size_t>(n) * K;
-  for (int k = lane; k < K; k += 32) {
-    const float wv = __ldg(wr + k);
+    for (int r = 0; r < kSkinnyRows; ++r) acc[r] = 0.0f;
+    const __nv_bfloat16* wr = w + static_cast<size_t>(n) * K;
+    // per 256-wide K slab a lane owns columns [k, k+4) and [k+128, k+132): both the 8-byte weight loads and
+    // the 16-byte shared-memory reads of x are then contiguous across the warp (no bank conflicts)
+    for (int k = lane * 4; k < K; k += 256) {
+      const bool hi = k + 128 < K;
+      const uint2 u0 = *reinterpret_cast<const uint2*>(wr + k);
+      const uint2 u1 = hi ? *reinterpret_cast<const uint2*>(wr + k + 128) : make_uint2(0, 0);
+      const float2 w0 = unpack_bf16x2(u0.x), w1 = unpack_bf16x2(u0.y), w2 = unpack_bf16x2(u1.x), w3 = unpack_bf16x2(u1.y);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (r0 + i < R) {
-        float xv = __ldg(x + static_cast<size_t>(r0 + i) * K + k);
-        if (in_act) xv = silu_f(xv);
-        acc[i] += xv * wv;
+      for (int r = 0; r < kSkinnyRows; ++r) {
+        const float4 a0 = *reinterpret_cast<const float4*>(xs + r * K + k);
+        acc[r] += a0.x * w0.x + a0.y * w0.y + a0.z * w1.x + a0.w * w1.y;
+        if (hi) {
+          const float4 a1 = *reinterpret_cast<const float4*>(xs + r * K + k + 128);
+          acc[r] += a1.x * w2.x + a1.y * w2.y + a1.z * w3.x + a1.w * w3.y;
+        }
       }
     }
-  }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = warp_sum(acc[i]);
-  if (lane == 0) {
-    const float bias = b ? b[n] : 0.0f;
+    for (int r = 0; r < kSkinnyRows; ++r) acc[r] = warp_sum(acc[r]);
+    if (lane < kSkinnyRows && r0 + lane < R) {
+      float v = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (r0 + i < R) {
-        float v = acc[i] + bias;
-        if (out_act) v = silu_f(v);
-        y[static_cast<size_t>(r0 + i) * N + n] = v;
-      }
+      for (int r = 0; r < kSkinnyRows; ++r) v = (lane == r) ? acc[r] : v;
+      v += b ? b[n] : 0.0f;
+      if (out_act) v = silu_f(v);
+      y[static_cast<size_t>(r0 + lane) * N + n] = v;
     }
   }
 }
 
-int launch_skinny_linear(const float* x, const float* w, const float* b, float* y, int R, int K, int N, int in_act,
+int launch_skinny_linear(const float* x, const void* w, const float* b, float* y, int R, int K, int N, int in_act,
                          int out_act, cudaStream_t stream) {
-  const int threads = 256;
-  dim3 grid((N * 32 + threads - 1) / threads, (R + 7) / 8);
-  skinny_linear_kernel<<<grid, threads, 0, stream>>>(x, w, b, y, R, K, N, in_act, out_act);
+  if (K % 4 != 0) { set_error("skinny_linear: K=%d must be a multiple of 4", K); return -1; }
+  const size_t smem = static_cast<size_t>(kSkinnyRows) * K * sizeof(float);
+  if (smem > 200 * 1024) { set_error("skinny_linear: K=%d too large", K); return -1; }
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(skinny_linear_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) { set_error("skinny_linear: smem opt-in failed: %s", cudaGetErrorString(e)); return -1; }
+    configured = smem;
+  }
+  int blocks_x = (N + 7) / 8;
+  const int cap = 2 * num_sms();
+  if (blocks_x > cap) blocks_x = cap;
+  dim3 grid(blocks_x, (R + kSkinnyRows - 1) / kSkinnyRows);
+  skinny_linear_kernel<<<grid, 256, smem, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(w), b, y, R, K, N,
+                                                    in_act, out_act);
   return check_launch("skinny_linear_kernel");
 }
 

@@ -278,6 +278,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               dst[q] = make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
                                   pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
             }
+          } else if (p.out_mode == kOutNchwF32) {
+            // lanes hold consecutive pixels: each channel plane gets a coalesced 128-byte store
+            const int pix = m - img * p.rows_per_img;
+            float* dst = reinterpret_cast<float*>(p.out) + static_cast<size_t>(img) * p.n_store * p.rows_per_img + pix;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col + j < p.n_store) dst[static_cast<size_t>(col + j) * p.rows_per_img] = v[j];
           } else if (p.out_mode == kOutF32) {
             float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
                                                     static_cast<size_t>(m) * p.ldo + p.col_off + col);

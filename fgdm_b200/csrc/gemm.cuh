@@ -9,6 +9,7 @@ enum GemmOutMode : int {
   kOutGeglu = 1,   // tile holds BN/2 value columns then BN/2 gate columns: out = x * gelu(gate)
   kOutQkv = 2,     // head-split Q/K [img, head, tok, d] and transposed V [img, head, d, tok_pad]
   kOutF32 = 3,     // out[m, n] fp32 row-major
+  kOutNchwF32 = 4, // out[img, n, pix] fp32 for n < n_store (tiny-Cout convs: eps / RGB at the model boundary)
 };
 
 enum GemmAct : int { kActNone = 0, kActSilu = 1, kActRelu = 2 };
@@ -40,6 +41,7 @@ struct GemmParams {
   void* out;
   int ldo;
   int col_off;
+  int n_store;          // kOutNchwF32: number of real output channels (<= N)
   // kOutQkv
   __nv_bfloat16* q_out;
   __nv_bfloat16* k_out;

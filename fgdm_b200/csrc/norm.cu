@@ -15,12 +15,14 @@
 
 namespace fgdm {
 
-static constexpr int kGnMaxChunks = 64;
+static constexpr int kGnMaxChunks = 128;
+static constexpr int kGnUnroll = 4;
 
 struct GnGeom {
   int NB, HW, C0, C1, G;
   int V;        // vectors of 8 channels per pixel
-  int k;        // pixel lanes per block; blockDim = V * k
+  int k;        // pixel lanes per block; V*k worker threads, blockDim rounded up to a warp multiple
+  int threads;
   int chunks;   // blocks per image
   int pix_per_chunk;
 };
@@ -31,7 +33,8 @@ static GnGeom gn_geom(int NB, int HW, int C0, int C1, int G) {
   g.V = (C0 + C1) / 8;
   g.k = 256 / g.V;
   if (g.k < 1) g.k = 1;
-  int want = (4 * num_sms() + NB - 1) / NB;      // ~4 blocks per SM in total
+  g.threads = (g.V * g.k + 31) / 32 * 32;
+  int want = (8 * num_sms() + NB - 1) / NB;      // ~8 blocks per SM in total: enough loads in flight
   if (want > kGnMaxChunks) want = kGnMaxChunks;
   if (want < 1) want = 1;
   int ppc = (HW + want - 1) / want;
@@ -58,25 +61,36 @@ __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
   const int p_begin = blockIdx.x * g.pix_per_chunk;
   int p_end = p_begin + g.pix_per_chunk;
   if (p_end > g.HW) p_end = g.HW;
-  float s[8], ss[8];
+  if (pl < g.k) {
+    float s[8], ss[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
-  for (int pix = p_begin + pl; pix < p_end; pix += g.k) {
-    const uint4 u = ld_nc_16(gn_src(x0, x1, g.C0, g.C1, static_cast<size_t>(img) * g.HW + pix, v));
-    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
+    const size_t base = static_cast<size_t>(img) * g.HW;
+    for (int pix = p_begin + pl; pix < p_end; pix += g.k * kGnUnroll) {
+      uint4 u[kGnUnroll];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float2 f = unpack_bf16x2(w[e]);
-      s[2 * e] += f.x; ss[2 * e] += f.x * f.x;
-      s[2 * e + 1] += f.y; ss[2 * e + 1] += f.y * f.y;
+      for (int q = 0; q < kGnUnroll; ++q) {   // issue all loads before consuming any
+        const int pq = pix + q * g.k;
+        u[q] = (pq < p_end) ? ld_nc_16(gn_src(x0, x1, g.C0, g.C1, base + pq, v)) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int q = 0; q < kGnUnroll; ++q) {
+        const uint32_t w[4] = {u[q].x, u[q].y, u[q].z, u[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = unpack_bf16x2(w[e]);
+          s[2 * e] += f.x; ss[2 * e] += f.x * f.x;
+          s[2 * e + 1] += f.y; ss[2 * e + 1] += f.y * f.y;
+        }
+      }
     }
-  }
-  float* sm_s = sm;
-  float* sm_ss = sm + g.k * C;
+    float* sm_s = sm;
+    float* sm_ss = sm + g.k * C;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    sm_s[pl * C + v * 8 + i] = s[i];
-    sm_ss[pl * C + v * 8 + i] = ss[i];
+    for (int i = 0; i < 8; ++i) {
+      sm_s[pl * C + v * 8 + i] = s[i];
+      sm_ss[pl * C + v * 8 + i] = ss[i];
+    }
   }
   __syncthreads();
   const int cpg = C / g.G;
@@ -84,8 +98,8 @@ __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
     float a = 0.0f, b = 0.0f;
     for (int l = 0; l < g.k; ++l)
       for (int c = grp * cpg; c < (grp + 1) * cpg; ++c) {
-        a += sm_s[l * C + c];
-        b += sm_ss[l * C + c];
+        a += sm[l * C + c];
+        b += sm[g.k * C + l * C + c];
       }
     partial[(static_cast<size_t>(img) * g.chunks + blockIdx.x) * g.G + grp] = make_float2(a, b);
   }
@@ -95,76 +109,90 @@ __global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
                                 const float2* __restrict__ partial, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, __nv_bfloat16* __restrict__ y, float eps, int silu,
                                 GnGeom g) {
+  __shared__ float s_mean[64], s_rstd[64];
   const int C = g.C0 + g.C1;
   const int cpg = C / g.G;
+  const int img = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const float inv_cnt = 1.0f / (static_cast<float>(g.HW) * cpg);
+  // fixed-order cooperative reduction of the per-chunk partials (bit-reproducible run to run)
+  for (int grp = warp; grp < g.G; grp += nwarps) {
+    float sum = 0.0f, sq = 0.0f;
+    for (int ch = lane; ch < g.chunks; ch += 32) {
+      const float2 t = partial[(static_cast<size_t>(img) * g.chunks + ch) * g.G + grp];
+      sum += t.x; sq += t.y;
+    }
+    sum = warp_sum(sum);
+    sq = warp_sum(sq);
+    if (lane == 0) {
+      const float mean = sum * inv_cnt;
+      const float var = fmaxf(sq * inv_cnt - mean * mean, 0.0f);
+      s_mean[grp] = mean;
+      s_rstd[grp] = rsqrtf(var + eps);
+    }
+  }
+  __syncthreads();
   const int v = threadIdx.x % g.V;
   const int pl = threadIdx.x / g.V;
-  const int img = blockIdx.y;
-  const float inv_cnt = 1.0f / (static_cast<float>(g.HW) * cpg);
+  if (pl >= g.k) return;
   float a[8], b[8];
-  {
-    int last_grp = -1;
-    float mean = 0.0f, rstd = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = v * 8 + i;
-      const int grp = c / cpg;
-      if (grp != last_grp) {
-        float sum = 0.0f, sq = 0.0f;
-        for (int ch = 0; ch < g.chunks; ++ch) {
-          const float2 t = partial[(static_cast<size_t>(img) * g.chunks + ch) * g.G + grp];
-          sum += t.x; sq += t.y;
-        }
-        mean = sum * inv_cnt;
-        const float var = fmaxf(sq * inv_cnt - mean * mean, 0.0f);
-        rstd = rsqrtf(var + eps);
-        last_grp = grp;
-      }
-      const float ga = gamma[c] * rstd;
-      a[i] = ga;
-      b[i] = beta[c] - mean * ga;
-    }
+  for (int i = 0; i < 8; ++i) {
+    const int c = v * 8 + i;
+    const int grp = c / cpg;
+    const float ga = gamma[c] * s_rstd[grp];
+    a[i] = ga;
+    b[i] = beta[c] - s_mean[grp] * ga;
   }
   const int p_begin = blockIdx.x * g.pix_per_chunk;
   int p_end = p_begin + g.pix_per_chunk;
   if (p_end > g.HW) p_end = g.HW;
-  for (int pix = p_begin + pl; pix < p_end; pix += g.k) {
-    const size_t gp = static_cast<size_t>(img) * g.HW + pix;
-    const uint4 u = ld_nc_16(gn_src(x0, x1, g.C0, g.C1, gp, v));
-    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-    uint32_t o[4];
+  const size_t base = static_cast<size_t>(img) * g.HW;
+  for (int pix = p_begin + pl; pix < p_end; pix += g.k * kGnUnroll) {
+    uint4 u[kGnUnroll];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float2 f = unpack_bf16x2(w[e]);
-      float r0 = f.x * a[2 * e] + b[2 * e];
-      float r1 = f.y * a[2 * e + 1] + b[2 * e + 1];
-      if (silu) { r0 = silu_f(r0); r1 = silu_f(r1); }
-      o[e] = pack_bf16x2(r0, r1);
+    for (int q = 0; q < kGnUnroll; ++q) {
+      const int pq = pix + q * g.k;
+      if (pq < p_end) u[q] = ld_nc_16(gn_src(x0, x1, g.C0, g.C1, base + pq, v));
     }
-    *reinterpret_cast<uint4*>(y + gp * C + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+    for (int q = 0; q < kGnUnroll; ++q) {
+      const int pq = pix + q * g.k;
+      if (pq >= p_end) break;
+      const uint32_t w[4] = {u[q].x, u[q].y, u[q].z, u[q].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = unpack_bf16x2(w[e]);
+        float r0 = f.x * a[2 * e] + b[2 * e];
+        float r1 = f.y * a[2 * e + 1] + b[2 * e + 1];
+        if (silu) { r0 = silu_f(r0); r1 = silu_f(r1); }
+        o[e] = pack_bf16x2(r0, r1);
+      }
+      *reinterpret_cast<uint4*>(y + (base + pq) * C + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
   }
 }
 
-// workspace: at least NB * 64 * G float2. x1 may be null (C1 = 0). y: [NB, HW, C0+C1] bf16.
+// workspace: at least NB * 128 * G float2. x1 may be null (C1 = 0). y: [NB, HW, C0+C1] bf16.
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                      int NB, int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream) {
   const int C = C0 + C1;
-  if (C0 % 8 || C1 % 8 || C % G || C / 8 > 1024) {
+  if (C0 % 8 || C1 % 8 || C % G || C / 8 > 1024 || G > 64) {
     set_error("groupnorm: unsupported channels C0=%d C1=%d G=%d", C0, C1, G);
     return -1;
   }
   const GnGeom g = gn_geom(NB, HW, C0, C1, G);
   const dim3 grid(g.chunks, NB);
-  const int threads = g.V * g.k;
   const size_t smem = static_cast<size_t>(2) * g.k * C * sizeof(float);
-  gn_stats_kernel<<<grid, threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
-                                                   reinterpret_cast<const __nv_bfloat16*>(x1),
-                                                   reinterpret_cast<float2*>(workspace), g);
+  gn_stats_kernel<<<grid, g.threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
+                                                     reinterpret_cast<const __nv_bfloat16*>(x1),
+                                                     reinterpret_cast<float2*>(workspace), g);
   if (check_launch("gn_stats_kernel")) return -1;
-  gn_apply_kernel<<<grid, threads, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
-                                                reinterpret_cast<const __nv_bfloat16*>(x1),
-                                                reinterpret_cast<const float2*>(workspace), gamma, beta,
-                                                reinterpret_cast<__nv_bfloat16*>(y), eps, silu, g);
+  gn_apply_kernel<<<grid, g.threads, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
+                                                  reinterpret_cast<const __nv_bfloat16*>(x1),
+                                                  reinterpret_cast<const float2*>(workspace), gamma, beta,
+                                                  reinterpret_cast<__nv_bfloat16*>(y), eps, silu, g);
   return check_launch("gn_apply_kernel");
 }
 

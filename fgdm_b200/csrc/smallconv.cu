@@ -62,6 +62,45 @@ int launch_conv_small_cin(const float* x, const void* w, const float* bias, void
   return check_launch("conv_small_cin_kernel");
 }
 
+// ---- A2: im2col of a tiny-Cin NCHW fp32 tensor -> bf16 [NB*H*W, 64] (k = tap*CIN + c) ------------
+// One thread per (pixel, 8-column group): 16-byte coalesced stores; consecutive lanes = consecutive
+// column groups of the same pixel, so the <= 36 distinct inputs of a pixel are L1 broadcasts.
+template <int CIN>
+__global__ void im2col_small_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int NB, int H, int W,
+                                    float in_scale, int nb_in) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t total = static_cast<size_t>(NB) * H * W * 8;
+  if (i >= total) return;
+  const int g = i & 7;
+  size_t p = i >> 3;
+  const int ow = p % W; p /= W;
+  const int oh = p % H;
+  const int n = (p / H) % nb_in;
+  float v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int k = g * 8 + j;
+    const int t = k / CIN, c = k - t * CIN;
+    const int ih = oh + t / 3 - 1, iw = ow + t % 3 - 1;
+    const bool ok = k < 9 * CIN && ih >= 0 && ih < H && iw >= 0 && iw < W;
+    v[j] = ok ? __ldg(x + ((static_cast<size_t>(n) * CIN + c) * H + ih) * W + iw) * in_scale : 0.0f;
+  }
+  *reinterpret_cast<uint4*>(out + i * 8) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                                      pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+}
+
+int launch_im2col_small(const float* x, void* out, int NB, int H, int W, int Cin, float in_scale, int nb_in,
+                        cudaStream_t stream) {
+  if (nb_in <= 0) nb_in = NB;
+  const size_t total = static_cast<size_t>(NB) * H * W * 8;
+  const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+  if (Cin == 3) im2col_small_kernel<3><<<blocks, 256, 0, stream>>>(x, o, NB, H, W, in_scale, nb_in);
+  else if (Cin == 4) im2col_small_kernel<4><<<blocks, 256, 0, stream>>>(x, o, NB, H, W, in_scale, nb_in);
+  else { set_error("im2col_small: Cin=%d unsupported (3 or 4)", Cin); return -1; }
+  return check_launch("im2col_small_kernel");
+}
+
 // ---- B: generic direct conv NHWC bf16 -> NHWC bf16 (3x3 pad 1, stride 1 or 2) ------------------
 __global__ void conv_direct_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w,
                                    const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, int NB, int H, int W,

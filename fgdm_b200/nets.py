@@ -118,7 +118,7 @@ class Adapter(Layer):
 
     def forward(self, x_nchw, rows):
         """x_nchw: fp32 [nb_in, cin, h, w]; `rows` output images (input image index = row % nb_in)."""
-        x = ops.conv_small_cin(x_nchw, self.conv_in.w, self.conv_in.b, self.channels[0], nb_out=rows)
+        x = self.conv_in.from_nchw(x_nchw, rows)
         feats = []
         for i in range(len(self.channels)):
             for j in range(self.nums_rb):
@@ -217,8 +217,7 @@ class _UNetBase(_Net):
         return h
 
     def _encode(self, x, rows, emb_all, kvs, fa=None, after_conv_in=None):
-        conv_in = self.input_blocks[0][0]
-        h = ops.conv_small_cin(x, conv_in.w, conv_in.b, self.model_channels, nb_out=rows)
+        h = self.input_blocks[0][0].from_nchw(x, rows)
         if after_conv_in is not None:
             h = after_conv_in(h)
         hs = [h]
@@ -239,7 +238,7 @@ class _UNetBase(_Net):
             h = self._run(self.output_blocks[idx], h, hs.pop(), emb_all, kvs)
         n, c = self.out[0], self.out[2]
         h = ops.groupnorm(h, n.g, n.b, eps=1e-5, silu=True)
-        return ops.conv_small_cout(h, c.w, c.b, self.out_channels)
+        return c.to_nchw(h)
 
 
 class UNetModel(_UNetBase):
@@ -500,7 +499,7 @@ class Decoder(Layer):
 
     def forward(self, z):
         """z: fp32 NCHW [B, z_channels, h, w] -> fp32 NCHW [B, out_ch, 8h, 8w]."""
-        h = ops.conv_small_cin(z, self.conv_in.w, self.conv_in.b, self.conv_in.cout)
+        h = self.conv_in.from_nchw(z)
         h = self.mid.block_1.forward(h)
         h = self.mid.attn_1.forward(h)
         h = self.mid.block_2.forward(h)
@@ -511,7 +510,7 @@ class Decoder(Layer):
             if up.upsample is not None:
                 h = up.upsample.forward(h)
         h = ops.groupnorm(h, self.norm_out.g, self.norm_out.b, eps=1e-6, silu=True)
-        return ops.conv_small_cout(h, self.conv_out.w, self.conv_out.b, self.out_ch)
+        return self.conv_out.to_nchw(h)
 
 
 class _Conv1x1F32(Layer):

@@ -12,7 +12,7 @@ import torch
 
 from . import _lib
 from ._lib import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU,
-                   OUT_QKV, GemmArgs)
+                   OUT_NCHW_F32, OUT_QKV, GemmArgs)
 
 bf16 = torch.bfloat16
 
@@ -77,7 +77,7 @@ def count_launches(n: int) -> None:
 
 def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None, bias=None, rowvec=None,
               rows_per_img=0, res0=None, res1=None, alpha=1.0, act=ACT_NONE, out_mode=OUT_BF16, out=None,
-              ldo=None, col_off=0, qkv=None, bn_hint=0):
+              ldo=None, col_off=0, qkv=None, bn_hint=0, n_store=0):
     """Implicit-GEMM conv / Linear. a0 (and a1) are NHWC bf16 `[nb, h, w, c]` or token `[rows, c]` tensors.
 
     For CONV_3X3_S2, a0 is the phase-split tensor `[4, nb, h, w, c]` (see resample(mode=2)) and
@@ -106,6 +106,12 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
         q, k, vt, first, heads, dhead, tok_pad = qkv
         args.q_out, args.k_out, args.vt_out = _p(q), _p(k), _p(vt)
         args.qkv_first, args.heads, args.dhead, args.tok_pad = first, heads, dhead, tok_pad
+    elif out_mode == OUT_NCHW_F32:
+        if out is None:
+            out = torch.empty((nb, n_store, h, w), device=a0.device, dtype=torch.float32)
+        args.out, args.ldo, args.n_store = _p(out), 0, n_store
+        if rows_per_img == 0:
+            args.rows_per_img = h * w
     else:
         n_out = n // 2 if out_mode == OUT_GEGLU else n
         if out is None:
@@ -130,7 +136,7 @@ def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):
 
 def _gn_workspace(device, nb, groups):
     # per call (a cached buffer that is later re-allocated would dangle inside captured CUDA graphs)
-    return torch.empty(nb * 64 * groups * 2, device=device, dtype=torch.float32)
+    return torch.empty(nb * 128 * groups * 2, device=device, dtype=torch.float32)
 
 
 def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=None):
@@ -186,7 +192,7 @@ def skinny_linear(x, w, b, in_act=False, out_act=False):
     rows, k = x.shape
     n = w.shape[0]
     y = torch.empty((rows, n), device=x.device, dtype=torch.float32)
-    _call("fgdm_skinny_linear", ("skinny k=%d n=%d" % (k, n), 2.0 * rows * k * n, 4.0 * (k * n + rows * (k + n))), _p(x), _p(w), _p(b), _p(y), rows, k, n, int(in_act), int(out_act),
+    _call("fgdm_skinny_linear", ("skinny k=%d n=%d" % (k, n), 2.0 * rows * k * n, 2.0 * k * n + 4.0 * rows * (k + n)), _p(x), _p(w), _p(b), _p(y), rows, k, n, int(in_act), int(out_act),
                                              _stream())
     return y
 
@@ -219,6 +225,16 @@ def conv_small_cin(x, w, bias, cout, act=ACT_NONE, in_scale=1.0, nb_out=None):
     _call("fgdm_conv_small_cin", ("conv_small_cin %d->%d" % (cin, cout), 18.0 * nb * h * wd * cin * cout, 4.0 * nb * cin * h * wd + 2.0 * y.numel()), _p(x), _p(w), _p(bias), _p(y), nb, h, wd, cin, cout, act, in_scale,
                                               nb_in, _stream())
     return y
+
+
+def im2col_small(x, nb_out=None, in_scale=1.0):
+    """x: NCHW fp32 with 3 or 4 channels -> bf16 [nb_out*h*w, 64] im2col rows (k = tap*cin + c)."""
+    nb_in, cin, h, wd = x.shape
+    nb = nb_out or nb_in
+    out = torch.empty((nb * h * wd, 64), device=x.device, dtype=bf16)
+    _call("fgdm_im2col_small", ("im2col cin=%d" % cin, 0.0, 4.0 * nb * cin * h * wd + 128.0 * nb * h * wd),
+          _p(x), _p(out), nb, h, wd, cin, in_scale, nb_in, _stream())
+    return out
 
 
 def ddim_advance(counter, t_table, idx_table, t_out, index_out):

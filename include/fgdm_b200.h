@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define FGDM_ABI_VERSION 1
+#define FGDM_ABI_VERSION 2
 
 const char* fgdm_last_error(void);
 int fgdm_abi_version(void);
@@ -41,7 +41,8 @@ enum {
   FGDM_OUT_BF16 = 0,   /* out[m, col_off + n] bf16, row stride ldo */
   FGDM_OUT_GEGLU = 1,  /* weights row-interleaved per 128 (64 value rows, 64 gate rows): out = x * gelu(gate) */
   FGDM_OUT_QKV = 2,    /* q/k -> [img, head, tok, d]; v -> transposed [img, head, d, tok_pad] */
-  FGDM_OUT_F32 = 3     /* out[m, n] fp32 */
+  FGDM_OUT_F32 = 3,    /* out[m, n] fp32 */
+  FGDM_OUT_NCHW_F32 = 4 /* out[img, c, pix] fp32 for c < n_store: conv_out 320->4 (openaimodel.py:727), 128->3 (model.py:529) */
 };
 enum { FGDM_ACT_NONE = 0, FGDM_ACT_SILU = 1, FGDM_ACT_RELU = 2 };
 /* A-operand addressing of fgdm_conv_gemm */
@@ -84,6 +85,7 @@ typedef struct {
   int heads, dhead;
   int tok_pad;
   int bn_hint;             /* N tile (0 = auto; 64/128/160/256) */
+  int n_store;             /* FGDM_OUT_NCHW_F32: real output channels (weights zero-padded to n) */
 } fgdm_gemm_args;
 
 /* nn.Conv2d / nn.Linear call sites: openaimodel.py:224,250,261,112,164-166; attention.py:40,60,
@@ -96,7 +98,7 @@ int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int 
                    int d, int tok_pad, float scale, void* stream);
 
 /* GroupNorm32 (+SiLU): util.py:223-225, openaimodel.py:221-224; attention.py:76-77; model.py:33-39.
- * x0/x1 virtual channel concat; workspace >= nb*64*groups*8 bytes. */
+ * x0/x1 virtual channel concat; workspace >= nb*128*groups*8 bytes. */
 int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                    int nb, int hw, int c0, int c1, int groups, float eps, int silu, void* stream);
 
@@ -122,9 +124,9 @@ int fgdm_ddim_advance(int* counter, const int64_t* t_table, const int* idx_table
 /* timestep_embedding: util.py:160-180. t int64 [rows]; freqs fp32 [dim/2]; out fp32 [rows, dim]. */
 int fgdm_timestep_embedding(const int64_t* t, const float* freqs, float* out, int rows, int dim, void* stream);
 
-/* Skinny fp32 Linear y = out_act(in_act(x) W^T + b): time_embed (openaimodel.py:538-542) and the
- * batched ResBlock emb_layers (openaimodel.py:238-244). act flags: 0 none, 1 SiLU. */
-int fgdm_skinny_linear(const float* x, const float* w, const float* b, float* y, int rows, int k, int n, int in_act,
+/* Skinny Linear y = out_act(in_act(x) W^T + b), x/y fp32 [rows, k]/[rows, n], W bf16 [n, k]: time_embed
+ * (openaimodel.py:538-542) and the batched ResBlock emb_layers (openaimodel.py:238-244). act: 0 none, 1 SiLU. */
+int fgdm_skinny_linear(const float* x, const void* w, const float* b, float* y, int rows, int k, int n, int in_act,
                        int out_act, void* stream);
 
 /* NHWC bf16 resampling. mode 0: nearest 2x up (openaimodel.py:123, model.py:53); 1: 2x2 avg pool
@@ -138,6 +140,12 @@ int fgdm_add_bf16(const void* a, const void* b, void* out, size_t n, void* strea
  * nb) — the CFG halves share one latent instead of torch.cat([x] * 2) (ddim.py:222). */
 int fgdm_conv_small_cin(const float* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
                         int cout, int act, float in_scale, int nb_in, void* stream);
+/* im2col for 3x3/pad-1 convs with cin in {3,4} on an NCHW fp32 tensor (scaled by in_scale): out bf16
+ * [nb*h*w, 64], column k = tap*cin + c (zero for k >= 9*cin), row r reads image r % nb_in. Followed by
+ * fgdm_conv_gemm (K = 64) this is conv_in 4->320 / 4->512 on tensor cores: openaimodel.py:561, adapter.py:332,
+ * cldm.py:645; model.py:488. */
+int fgdm_im2col_small(const float* x, void* out, int nb, int h, int w_, int cin, float in_scale, int nb_in,
+                      void* stream);
 /* 3x3 direct conv NHWC bf16 -> NHWC bf16, stride 1/2 (ControlNet hint stem, cldm.py:656-666). */
 int fgdm_conv_direct(const void* x, const void* w, const float* bias, void* y, int nb, int h, int w_, int cin,
                      int cout, int stride, int act, void* stream);

@@ -210,10 +210,15 @@ def test_timestep_embedding_and_skinny_linear():
     torch.testing.assert_close(emb, ref, rtol=1e-4, atol=2e-4)
     w = torch.randn(1280, 320, device=DEV) / 18
     b = torch.randn(1280, device=DEV)
-    y = ops.skinny_linear(emb, w, b, in_act=True, out_act=True)
-    torch.testing.assert_close(y, F.silu(F.silu(emb) @ w.t() + b), rtol=1e-3, atol=1e-3)
+    wb = w.to(torch.bfloat16)
+    y = ops.skinny_linear(emb, wb, b, in_act=True, out_act=True)
+    torch.testing.assert_close(y, F.silu(F.silu(emb) @ wb.float().t() + b), rtol=1e-3, atol=1e-3)
     x19 = torch.randn(19, 320, device=DEV)
-    torch.testing.assert_close(ops.skinny_linear(x19, w, None), x19 @ w.t(), rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(ops.skinny_linear(x19, wb, None), x19 @ wb.float().t(), rtol=1e-3, atol=1e-3)
+    w2 = (torch.randn(2000, 1280, device=DEV) / 36).to(torch.bfloat16)
+    x16 = torch.randn(16, 1280, device=DEV)
+    torch.testing.assert_close(ops.skinny_linear(x16, w2, None, in_act=True), F.silu(x16) @ w2.float().t(),
+                               rtol=1e-3, atol=1e-3)
 
 
 def test_resample_modes():
@@ -254,6 +259,23 @@ def test_small_convs():
     z = torch.randn(2, 4, 8, 8, device=DEV)
     wq = torch.randn(4, 4, device=DEV)
     bq = torch.randn(4, device=DEV)
+    # tensor-core routes for the tiny-channel convs: im2col + GEMM (cin 4), NCHW-fp32 epilogue (cout 4 / 3)
+    from fgdm_b200.layers import Conv2d
+    for (ci, co, hw2, rows) in [(4, 320, 32, 4), (320, 4, 16, 2), (128, 3, 32, 1)]:
+        cv = Conv2d(ci, co, 3)
+        wt = torch.randn(co, ci, 3, 3, device=DEV) / math.sqrt(9 * ci)
+        bt = torch.randn(co, device=DEV)
+        cv.load({"weight": wt, "bias": bt}, "", DEV)
+        if ci == 4:
+            xin = torch.randn(2, 4, hw2, hw2, device=DEV)
+            out = cv.from_nchw(xin, rows, in_scale=0.5)
+            ref = F.conv2d((xin * 0.5).repeat(rows // 2, 1, 1, 1), wt.to(torch.bfloat16).float(), bt, padding=1)
+            assert relerr(nchw(out), ref) < 1e-2
+        else:
+            xin = nhwc(torch.randn(rows, ci, hw2, hw2, device=DEV))
+            out = cv.to_nchw(xin)
+            assert out.shape == (rows, co, hw2, hw2) and out.dtype == torch.float32
+            assert relerr(out, F.conv2d(nchw(xin), wt.to(torch.bfloat16).float(), bt, padding=1)) < 1e-2
     ya = ops.latent_affine(z, wq, bq, 1 / 0.18215)
     torch.testing.assert_close(ya, F.conv2d(z / 0.18215, wq[:, :, None, None], bq), rtol=1e-4, atol=1e-4)
 
