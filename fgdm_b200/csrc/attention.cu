@@ -180,13 +180,29 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 #pragma unroll
     for (int c = 0; c < BN; c += 32) tmem_ld_32x32(tmem_s + lane_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
     tmem_ld_wait();
-    float tmax = -INFINITY;
-    if (valid >= BN) {
+    float tmax;
+    {
+      // four independent chains of 3-input max: no 128-deep dependency chain (only 2 warps share an SMSP)
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      if (valid >= BN) {
 #pragma unroll
-      for (int i = 0; i < BN; ++i) tmax = fmaxf(tmax, __uint_as_float(s[i]));
-    } else {
+        for (int i = 0; i < BN; i += 8) {
 #pragma unroll
-      for (int i = 0; i < BN; ++i) tmax = fmaxf(tmax, (i < valid) ? __uint_as_float(s[i]) : -INFINITY);
+          for (int u = 0; u < 4; ++u)
+            mx[u] = fmax3(mx[u], __uint_as_float(s[i + 2 * u]), __uint_as_float(s[i + 2 * u + 1]));
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < BN; i += 8) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int c = i + 2 * u;
+            mx[u] = fmax3(mx[u], (c < valid) ? __uint_as_float(s[c]) : -INFINITY,
+                          (c + 1 < valid) ? __uint_as_float(s[c + 1]) : -INFINITY);
+          }
+        }
+      }
+      tmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
     }
     tmax *= p.scale_log2;
 
@@ -219,8 +235,9 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     }
 
     // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major); row sum ----
-    float lsum = 0.0f;
+    float ls[4] = {0.0f, 0.0f, 0.0f, 0.0f};           // independent partial row sums
     const float neg_m = -m_ref;
+    const uint32_t sP_row = smem_u32(sP) + row * 128;
     auto emit = [&](auto masked) {
 #pragma unroll
       for (int c = 0; c < BN; c += 8) {
@@ -233,16 +250,15 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             if (c + i >= valid) p0 = 0.0f;
             if (c + i + 1 >= valid) p1 = 0.0f;
           }
-          lsum += p0 + p1;
+          ls[(i >> 1) & 3] += p0 + p1;
           pk[i >> 1] = pack_bf16x2(p0, p1);
         }
-        uint8_t* atom = sP + (c >> 6) * 16384 + row * 128;
         const int chunk = ((c & 63) >> 3) ^ (row & 7);
-        *reinterpret_cast<uint4*>(atom + chunk * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        st_shared_16(sP_row + (c >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
       }
     };
     if (valid >= BN) emit(std::false_type{}); else emit(std::true_type{});
-    l_run += lsum;
+    l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
 
     fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
     tc_fence_before();

@@ -31,7 +31,10 @@ int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dim
 
 static constexpr int kBM = 128;
 static constexpr int kBK = 64;
-static constexpr int kGemmThreads = 192;
+static constexpr int kEpiWarps = 8;                      // two warps per TMEM lane quarter, alternating 32-col panels
+static constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
+static constexpr int kStgRow = 80;                       // staging row: 32 bf16 (64 B) + 16 B pad (conflict-free)
+static constexpr int kStgBytes = 32 * kStgRow;           // per epilogue warp
 
 template <int BN>
 struct GemmCfg {
@@ -41,7 +44,7 @@ struct GemmCfg {
   static constexpr int kStages = (BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4;
   static constexpr int kAccStride = (BN <= 64) ? 64 : (BN <= 128) ? 128 : 256;  // TMEM columns
   static constexpr int kTmemCols = 2 * kAccStride;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kStgBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
 
 template <int BN>
@@ -55,7 +58,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * Cfg::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* smem_stg = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stg + kEpiWarps * kStgBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* acc_full = bars + 2 * kStages;
@@ -75,7 +79,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], 4);
+      mbar_init(&acc_empty[i], kEpiWarps);
     }
     fence_barrier_init();
   }
@@ -166,14 +170,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
   } else {
     // ===================== epilogue warps (TMEM -> registers -> global) =====================
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    // Warp w may only touch TMEM lanes 32*(w%4)..+31; warps sharing a lane quarter alternate 32-column panels.
+    // bf16 outputs (and the first residual) go through a per-warp padded smem panel so that every global access
+    // is a run of full 64-byte row segments instead of 32 scattered 16-byte pieces.
+    const int ew = warp - 2;
+    const int quarter = warp & 3;
+    const int half = ew >> 2;
     const int row = quarter * 32 + lane;
+    uint8_t* stg = smem_stg + ew * kStgBytes;
+    const uint32_t stg_u32 = smem_u32(stg);
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
-      const int m = m_tile * kBM + row;
+      const int m_warp = m_tile * kBM + quarter * 32;   // first row of this warp
+      const int m = m_warp + lane;
       const bool row_ok = m < p.M;
       const int img = row_ok ? (m / p.rows_per_img) : 0;
       mbar_wait(&acc_full[acc], acc_phase);
@@ -183,14 +195,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       if (p.out_mode == kOutGeglu) {
         constexpr int kHalf = BN / 2;
 #pragma unroll 1
-        for (int c0 = 0; c0 < kHalf; c0 += 32) {
+        for (int c0 = half * 32; c0 < kHalf; c0 += 64) {
           uint32_t rx[32], rg[32];
           tmem_ld_32x32(taddr + c0, rx);
           tmem_ld_32x32(taddr + kHalf + c0, rg);
           tmem_ld_wait();
           const int ocol = n_tile * kHalf + c0;          // output column (value index)
           const int bcol = n_tile * BN + c0;             // interleaved bias index
-          if (row_ok && ocol < p.N / 2) {
+          const bool col_ok = ocol < p.N / 2;            // warp-uniform
+          if (col_ok) {
             uint32_t packed[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
@@ -204,32 +217,59 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               }
               packed[j >> 1] = pack_bf16x2(x0 * gelu_erf_f(g0), x1 * gelu_erf_f(g1));
             }
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                                  static_cast<size_t>(m) * p.ldo + ocol);
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              dst[j] = make_uint4(packed[4 * j], packed[4 * j + 1], packed[4 * j + 2], packed[4 * j + 3]);
+            for (int q = 0; q < 4; ++q)
+              st_shared_16(stg_u32 + lane * kStgRow + q * 16,
+                           make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]));
+            __syncwarp();
+            __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + ocol;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int idx = lane + 32 * i, r = idx >> 2, ch = idx & 3;
+              if (m_warp + r < p.M)
+                *reinterpret_cast<uint4*>(obase + static_cast<size_t>(m_warp + r) * p.ldo + ch * 8) =
+                    ld_shared_16(stg_u32 + r * kStgRow + ch * 16);
+            }
+            __syncwarp();
           }
         }
       } else {
+        const bool staged = p.out_mode == kOutBf16;
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = half * 32; c0 < BN; c0 += 64) {
           uint32_t r[32];
           tmem_ld_32x32(taddr + c0, r);
           tmem_ld_wait();
           const int col = n_tile * BN + c0;
-          if (!row_ok || col >= p.N) continue;
+          if (col >= p.N) continue;                      // warp-uniform
+          if (staged && p.res0) {                        // coalesced load of the residual panel
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int idx = lane + 32 * i, rr = idx >> 2, ch = idx & 3;
+              uint4 u = make_uint4(0, 0, 0, 0);
+              if (m_warp + rr < p.M)
+                u = *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m_warp + rr) * p.ld_res0 + col + ch * 8);
+              st_shared_16(stg_u32 + rr * kStgRow + ch * 16, u);
+            }
+            __syncwarp();
+          }
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           if (p.bias) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += __ldg(p.bias + col + j);
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+              v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+            }
           }
           if (p.rowvec) {
             const float* rv = p.rowvec + static_cast<size_t>(img) * p.ld_rowvec + col;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] += __ldg(rv + j);
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(rv + j));
+              v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+            }
           }
           if (p.alpha != 1.0f) {
 #pragma unroll
@@ -243,10 +283,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
             for (int j = 0; j < 32; ++j) v[j] = silu_f(v[j]);
           }
           if (p.res0) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m) * p.ld_res0 + col);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              const uint4 u = rp[q];
+              uint4 u;
+              if (staged) u = ld_shared_16(stg_u32 + lane * kStgRow + q * 16);
+              else u = row_ok ? *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m) * p.ld_res0 + col + q * 8)
+                              : make_uint4(0, 0, 0, 0);
               const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
@@ -256,7 +298,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               }
             }
           }
-          if (p.res1) {
+          if (p.res1 && row_ok) {
             const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(m) * p.ld_res1 + col);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -270,14 +312,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               }
             }
           }
-          if (p.out_mode == kOutBf16) {
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) +
-                                                  static_cast<size_t>(m) * p.ldo + p.col_off + col);
+          if (staged) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              dst[q] = make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                  pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+            for (int q = 0; q < 4; ++q)
+              st_shared_16(stg_u32 + lane * kStgRow + q * 16,
+                           make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                      pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+            __syncwarp();
+            __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + p.col_off + col;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int idx = lane + 32 * i, rr = idx >> 2, ch = idx & 3;
+              if (m_warp + rr < p.M)
+                *reinterpret_cast<uint4*>(obase + static_cast<size_t>(m_warp + rr) * p.ldo + ch * 8) =
+                    ld_shared_16(stg_u32 + rr * kStgRow + ch * 16);
             }
+            __syncwarp();
+          } else if (!row_ok) {
+            // nothing to store for padding rows
           } else if (p.out_mode == kOutNchwF32) {
             // lanes hold consecutive pixels: each channel plane gets a coalesced 128-byte store
             const int pix = m - img * p.rows_per_img;

@@ -93,14 +93,24 @@ __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
     }
   }
   __syncthreads();
+  // two-level reduction: per-channel over the k pixel lanes (all threads), then per-group over cpg channels
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.0f, b = 0.0f;
+    for (int l = 0; l < g.k; ++l) {
+      a += sm[l * C + c];
+      b += sm[g.k * C + l * C + c];
+    }
+    sm[c] = a;                      // row l = 0 of each half now holds the column sums
+    sm[g.k * C + c] = b;
+  }
+  __syncthreads();
   const int cpg = C / g.G;
   for (int grp = threadIdx.x; grp < g.G; grp += blockDim.x) {
     float a = 0.0f, b = 0.0f;
-    for (int l = 0; l < g.k; ++l)
-      for (int c = grp * cpg; c < (grp + 1) * cpg; ++c) {
-        a += sm[l * C + c];
-        b += sm[g.k * C + l * C + c];
-      }
+    for (int c = grp * cpg; c < (grp + 1) * cpg; ++c) {
+      a += sm[c];
+      b += sm[g.k * C + c];
+    }
     partial[(static_cast<size_t>(img) * g.chunks + blockIdx.x) * g.G + grp] = make_float2(a, b);
   }
 }

@@ -269,10 +269,11 @@ __global__ void image_to_u8_kernel(const float* __restrict__ x, unsigned char* _
   const float v = x[(static_cast<size_t>(n) * C + c) * HW + px];
   float r;
   if (mode == 0) {
-    r = fminf(fmaxf((v + 1.0f) / 2.0f, 0.0f), 1.0f);
-    r = 255.0f * r;
+    r = fminf(fmaxf(__fmul_rn(__fadd_rn(v, 1.0f), 0.5f), 0.0f), 1.0f);
+    r = __fmul_rn(255.0f, r);
   } else {
-    r = fminf(fmaxf(v * 127.5f + 127.5f, 0.0f), 255.0f);
+    // separate multiply and add (no FMA contraction): the reference rounds twice (x * 127.5, then + 127.5)
+    r = fminf(fmaxf(__fadd_rn(__fmul_rn(v, 127.5f), 127.5f), 0.0f), 255.0f);
   }
   y[i] = static_cast<unsigned char>(r);
 }
