@@ -29,15 +29,17 @@ struct AttnParams {
   int Nq, Nk;
   int d;            // head dim
   int dv_per;       // V columns per blockIdx.z split
+  int dv_real;      // V columns this CTA really owns (== index of the ones-row in its V^T tile)
   float scale_log2; // softmax scale * log2(e)
   __nv_bfloat16* out;  // [images, Nq, heads*d]
   int ld_out;
 };
 
-static constexpr int kAttnThreads = 128;
+static constexpr int kAttnThreads = 256;
 static constexpr float kRescaleThreshold = 8.0f;   // log2 units: P <= 2^8 before a row's reference max is refreshed
 
-// KA: 64-wide K-chunks of the head dim (Q/K tiles are KA swizzle atoms), DV: V columns of this CTA,
+// KA: 64-wide K-chunks of the head dim (Q/K tiles are KA swizzle atoms), DV: V^T rows of this CTA's tile (the
+// real V columns plus the all-ones row that makes the tensor core produce the softmax denominator),
 // BN: keys per tile (128, or 64 when the head dim is large so that two CTAs still fit on an SM).
 template <int KA, int DV, int BN>
 struct AttnCfg {
@@ -46,22 +48,29 @@ struct AttnCfg {
   static constexpr int kVAtom = DV * 128;              // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kVBytes = (BN / 64) * kVAtom;
   static constexpr int kPBytes = (BN / 64) * 128 * 128;
-  static constexpr int kSmemBytes = kQBytes + 2 * (kKBytes + kVBytes) + kPBytes + 1024 + 128;
+  static constexpr int kSmemBytes = kQBytes + 2 * (kKBytes + kVBytes) + kPBytes + 1024 /*align*/ + 1024 /*row max*/ + 128;
   static constexpr int kTmemCols = (BN + DV <= 128) ? 128 : 256;
 };
 
-// Flow per KV tile j (one thread per query row, all 128 threads alike; thread 0 also drives TMA + MMA):
-//   wait S(j) | tcgen05.ld the whole S row into registers | row max | wait PV(j-1) | refresh the row's
-//   reference max only if it grew by > 2^8 (then rescale l and the O row in TMEM: rare) | exp2 -> bf16 P tile
-//   in swizzled smem | barrier | thread 0: issue S(j+1) then PV(j) (O accumulates in TMEM) and prefetch K/V.
-// The softmax of tile j+1 therefore overlaps PV(j) on the tensor pipe, and the second CTA resident on the SM
-// covers this CTA's wait for S(j+1). O is read from TMEM once, at the end.
+// 256 threads: TWO threads per query row (warps w and w+4 own the same 32 TMEM lanes and split the tile's key
+// columns), so each SM sub-partition has 4 warps (2 resident CTAs) to hide MUFU / TMEM latency behind.
+// Flow per KV tile j (thread 0 also drives TMA + MMA):
+//   wait S(j) | tcgen05.ld this thread's half of the S row | half-row max -> smem | barrier A |
+//   thread 0 issues S(j+1) (S is in registers everywhere: its TMEM columns are free) | row max = max of the two
+//   halves | wait PV(j-1) | lazy refresh of the row's reference max (then rescale the O row in TMEM: rare) |
+//   exp2 -> bf16 P tile in swizzled smem | barrier B | warp 0 writes the ones-row of V(j), issues PV(j).
+// The softmax denominator is NOT accumulated on the CUDA cores: V^T row `dv_real` of every tile is overwritten with
+// 1.0, so O[:, dv_real] = sum_j P[:, j] comes out of the PV tensor-core product (from the same bf16-rounded P as
+// the numerator) and is rescaled together with O.
 template <int KA, int DV, int BN>
 __global__ void __launch_bounds__(kAttnThreads, 2)
 attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
   using Cfg = AttnCfg<KA, DV, BN>;
   constexpr int kPA = BN / 64;                          // key-atoms per tile
+  constexpr int HB = BN / 2;                            // S columns per thread
+  constexpr int HV = DV / 2;                            // O columns per thread
+  static_assert(DV % 16 == 0 && HV % 8 == 0, "DV must be a multiple of 16");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -69,7 +78,8 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   uint8_t* sK = sQ + Cfg::kQBytes;                  // 2 stages
   uint8_t* sV = sK + 2 * Cfg::kKBytes;              // 2 stages
   uint8_t* sP = sV + 2 * Cfg::kVBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + Cfg::kPBytes);
+  float* sMax = reinterpret_cast<float*>(sP + Cfg::kPBytes);   // [2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + 256);
   uint64_t* bar_q = bars;
   uint64_t* bar_k = bars + 1;   // [2]
   uint64_t* bar_v = bars + 3;   // [2]
@@ -79,6 +89,9 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int half = warp >> 2;                       // which half of the S / O columns this thread owns
+  const int row = tid & 127;                        // query row within the tile == TMEM lane
   const int q0 = blockIdx.x * 128;
   const int bh = blockIdx.y;
   const int v0 = blockIdx.z * p.dv_per;             // first V column of this CTA
@@ -164,36 +177,34 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     issue_s(0);
   }
 
-  const int row = tid;                                // TMEM lane == query row within the tile
-  const uint32_t lane_addr = static_cast<uint32_t>(warp * 32) << 16;
+  const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const uint32_t s_addr = tmem_s + lane_addr + half * HB;
+  const uint32_t o_addr = tmem_o + lane_addr + half * HV;
   float m_ref = -INFINITY;                            // reference max (scaled, log2 domain) used for exp2
-  float l_run = 0.0f;
 
   for (int j = 0; j < num_kv; ++j) {
-    const int valid = p.Nk - j * BN;                   // keys valid in this tile (may exceed BN)
+    const int valid = p.Nk - j * BN - half * HB;       // keys valid in this thread's half tile (may exceed HB)
     mbar_wait(bar_s, j & 1);
     tc_fence_after();
-    if (tid == 0 && j + 2 < num_kv) load_k(j + 2);     // K stage j&1 is free: S(j) has completed
 
-    // ---- whole S row -> registers, row maximum ----
-    uint32_t s[BN];
+    // ---- this thread's half of the S row -> registers, half-row maximum ----
+    uint32_t s[HB];
 #pragma unroll
-    for (int c = 0; c < BN; c += 32) tmem_ld_32x32(tmem_s + lane_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
+    for (int c = 0; c < HB; c += 32) tmem_ld_32x32(s_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
     tmem_ld_wait();
-    float tmax;
+    float hmax;
     {
-      // four independent chains of 3-input max: no 128-deep dependency chain (only 2 warps share an SMSP)
       float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-      if (valid >= BN) {
+      if (valid >= HB) {
 #pragma unroll
-        for (int i = 0; i < BN; i += 8) {
+        for (int i = 0; i < HB; i += 8) {
 #pragma unroll
           for (int u = 0; u < 4; ++u)
             mx[u] = fmax3(mx[u], __uint_as_float(s[i + 2 * u]), __uint_as_float(s[i + 2 * u + 1]));
         }
       } else {
 #pragma unroll
-        for (int i = 0; i < BN; i += 8) {
+        for (int i = 0; i < HB; i += 8) {
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const int c = i + 2 * u;
@@ -202,9 +213,22 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
           }
         }
       }
-      tmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
     }
-    tmax *= p.scale_log2;
+    sMax[half * 128 + row] = hmax;
+    tc_fence_before();
+    __syncthreads();                                   // barrier A: S(j) is in registers, half maxima are in smem
+
+    if (tid == 0) {
+      tc_fence_after();
+      if (j + 2 < num_kv) load_k(j + 2);               // K stage j&1 is free: S(j) has completed
+      if (j + 1 < num_kv) {
+        mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
+        tc_fence_after();
+        issue_s(j + 1);                                // overlaps this tile's softmax
+      }
+    }
+    const float tmax = fmaxf(hmax, sMax[(half ^ 1) * 128 + row]) * p.scale_log2;
 
     // ---- PV(j-1) must have drained before O is touched or the P tile is overwritten ----
     if (j > 0) {
@@ -218,29 +242,27 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     if (__any_sync(0xffffffffu, need)) {
       const float m_new = need ? tmax : m_ref;
       const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
-      l_run *= alpha;
       m_ref = m_new;
       if (j > 0) {
 #pragma unroll
-        for (int c = 0; c < DV; c += 16) {
-          uint32_t r[16];
-          tmem_ld_32x16(tmem_o + lane_addr + c, r);
+        for (int c = 0; c < HV; c += 8) {
+          uint32_t r[8];
+          tmem_ld_32x8(o_addr + c, r);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st_32x16(tmem_o + lane_addr + c, r);
+          for (int i = 0; i < 8; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st_32x8(o_addr + c, r);
         }
         tmem_st_wait();
       }
     }
 
-    // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major); row sum ----
-    float ls[4] = {0.0f, 0.0f, 0.0f, 0.0f};           // independent partial row sums
+    // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major) ----
     const float neg_m = -m_ref;
     const uint32_t sP_row = smem_u32(sP) + row * 128;
     auto emit = [&](auto masked) {
 #pragma unroll
-      for (int c = 0; c < BN; c += 8) {
+      for (int c = 0; c < HB; c += 8) {
         uint32_t pk[4];
 #pragma unroll
         for (int i = 0; i < 8; i += 2) {
@@ -250,57 +272,61 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             if (c + i >= valid) p0 = 0.0f;
             if (c + i + 1 >= valid) p1 = 0.0f;
           }
-          ls[(i >> 1) & 3] += p0 + p1;
           pk[i >> 1] = pack_bf16x2(p0, p1);
         }
-        const int chunk = ((c & 63) >> 3) ^ (row & 7);
-        st_shared_16(sP_row + (c >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
+        const int cc = half * HB + c;                    // column within the tile
+        const int chunk = ((cc & 63) >> 3) ^ (row & 7);
+        st_shared_16(sP_row + (cc >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
       }
     };
-    if (valid >= BN) emit(std::false_type{}); else emit(std::true_type{});
-    l_run += (ls[0] + ls[1]) + (ls[2] + ls[3]);
+    if (valid >= HB) emit(std::false_type{}); else emit(std::true_type{});
 
     fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
     tc_fence_before();
-    __syncthreads();
+    __syncthreads();            // barrier B: the P tile is complete
 
-    if (tid == 0) {
-      tc_fence_after();
-      if (j + 1 < num_kv) {
-        mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
-        tc_fence_after();
-        issue_s(j + 1);          // ahead of PV(j) in the tensor pipe: the next softmax can start sooner
-      }
+    if (warp == 0) {
       mbar_wait(&bar_v[j & 1], (j >> 1) & 1);
-      tc_fence_after();
-      issue_pv(j);
+      // ones-row: V^T row dv_real of every key-atom := 1.0 (a full 128-byte swizzle row, so the swizzle is moot)
+      if (lane < kPA * 8) {
+        const uint32_t a = smem_u32(sV + (j & 1) * Cfg::kVBytes + (lane >> 3) * Cfg::kVAtom) + p.dv_real * 128 + (lane & 7) * 16;
+        st_shared_16(a, make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u));
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tc_fence_after();
+        issue_pv(j);
+      }
     }
   }
 
-  // ---- normalise and store: out[img, q, head*d + v0 + e] ----
+  // ---- normalise and store: out[img, q, head*d + v0 + e]; the denominator is O column dv_real ----
   mbar_wait(bar_o, (num_kv - 1) & 1);
   tc_fence_after();
   const int q = q0 + row;
-  const float inv = 1.0f / l_run;
+  float inv;
+  {
+    uint32_t r1[1];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1[0]) : "r"(tmem_o + lane_addr + p.dv_real) : "memory");
+    tmem_ld_wait();
+    inv = 1.0f / __uint_as_float(r1[0]);
+  }
   const int img = bh / p.heads;
   const int head = bh - img * p.heads;
-  __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0;
+  __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0 + half * HV;
 #pragma unroll
-  for (int c = 0; c < DV; c += 16) {
-    uint32_t r[16];
-    tmem_ld_32x16(tmem_o + lane_addr + c, r);
+  for (int c = 0; c < HV; c += 8) {
+    uint32_t r[8];
+    tmem_ld_32x8(o_addr + c, r);
     tmem_ld_wait();
-    if (q < p.Nq) {
-#pragma unroll
-      for (int h8 = 0; h8 < 16; h8 += 8) {
-        if (c + h8 < p.dv_per && v0 + c + h8 < p.d) {
-          *reinterpret_cast<uint4*>(dst + c + h8) =
-              make_uint4(pack_bf16x2(__uint_as_float(r[h8]) * inv, __uint_as_float(r[h8 + 1]) * inv),
-                         pack_bf16x2(__uint_as_float(r[h8 + 2]) * inv, __uint_as_float(r[h8 + 3]) * inv),
-                         pack_bf16x2(__uint_as_float(r[h8 + 4]) * inv, __uint_as_float(r[h8 + 5]) * inv),
-                         pack_bf16x2(__uint_as_float(r[h8 + 6]) * inv, __uint_as_float(r[h8 + 7]) * inv));
-        }
-      }
+    const int col = half * HV + c;                       // column within this CTA's V slice
+    if (q < p.Nq && col < p.dv_real && v0 + col < p.d) {
+      *reinterpret_cast<uint4*>(dst + c) =
+          make_uint4(pack_bf16x2(__uint_as_float(r[0]) * inv, __uint_as_float(r[1]) * inv),
+                     pack_bf16x2(__uint_as_float(r[2]) * inv, __uint_as_float(r[3]) * inv),
+                     pack_bf16x2(__uint_as_float(r[4]) * inv, __uint_as_float(r[5]) * inv),
+                     pack_bf16x2(__uint_as_float(r[6]) * inv, __uint_as_float(r[7]) * inv));
     }
   }
 
@@ -350,8 +376,10 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   const int BN = (KA == 1) ? 128 : 64;   // keys per tile: two CTAs must fit on an SM
   const int nsplit = (d + 79) / 80;
   int dv_per = (d + nsplit - 1) / nsplit;
-  dv_per = (dv_per + 15) / 16 * 16;
+  dv_per = (dv_per + 7) / 8 * 8;
   p.dv_per = dv_per;
+  p.dv_real = dv_per;
+  const int DV = (dv_per + 1 + 15) / 16 * 16;   // + the ones-row, MMA N granularity 16
 
   CUtensorMap mq, mk, mv;
   {
@@ -369,23 +397,20 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   {
     uint64_t dims[3] = {static_cast<uint64_t>(Nk), static_cast<uint64_t>(d), static_cast<uint64_t>(p.BH)};
     uint64_t strides[2] = {static_cast<uint64_t>(tok_pad) * 2, static_cast<uint64_t>(d) * tok_pad * 2};
-    uint32_t box[3] = {64, static_cast<uint32_t>(dv_per), 1};
+    uint32_t box[3] = {64, static_cast<uint32_t>(DV), 1};
     if (encode_tmap(&mv, vt, 3, dims, strides, box)) return -1;
   }
 #define FGDM_ATTN_CASE(KA_, DV_, BN_) \
-  if (KA == KA_ && dv_per == DV_) return launch_attn<KA_, DV_, BN_>(mq, mk, mv, p, nsplit, stream);
+  if (KA == KA_ && DV == DV_) return launch_attn<KA_, DV_, BN_>(mq, mk, mv, p, nsplit, stream);
   FGDM_ATTN_CASE(1, 16, 128)
   FGDM_ATTN_CASE(1, 32, 128)
   FGDM_ATTN_CASE(1, 48, 128)
   FGDM_ATTN_CASE(1, 64, 128)
-  FGDM_ATTN_CASE(2, 48, 64)
-  FGDM_ATTN_CASE(2, 64, 64)
-  FGDM_ATTN_CASE(2, 80, 64)
-  FGDM_ATTN_CASE(3, 48, 64)
-  FGDM_ATTN_CASE(3, 64, 64)
-  FGDM_ATTN_CASE(3, 80, 64)
+  FGDM_ATTN_CASE(1, 80, 128)
+  FGDM_ATTN_CASE(2, 96, 64)
+  FGDM_ATTN_CASE(3, 96, 64)
 #undef FGDM_ATTN_CASE
-  set_error("attention: no kernel instance for d=%d (KA=%d, dv_per=%d)", d, KA, dv_per);
+  set_error("attention: no kernel instance for d=%d (KA=%d, DV=%d)", d, KA, DV);
   return -1;
 }
 

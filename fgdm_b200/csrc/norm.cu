@@ -12,10 +12,12 @@
 // The input may be a virtual channel concatenation of two tensors (UNet skip `th.cat`,
 // openaimodel.py:869) — GroupNorm groups can straddle the seam (1920 = 1280 + 640 channels).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace fgdm {
 
 static constexpr int kGnMaxChunks = 128;
+static constexpr int kGnMaxImages = 4096;
 static constexpr int kGnUnroll = 4;
 
 struct GnGeom {
@@ -34,7 +36,9 @@ static GnGeom gn_geom(int NB, int HW, int C0, int C1, int G) {
   g.k = 256 / g.V;
   if (g.k < 1) g.k = 1;
   g.threads = (g.V * g.k + 31) / 32 * 32;
-  int want = (8 * num_sms() + NB - 1) / NB;      // ~8 blocks per SM in total: enough loads in flight
+  static int bps = 0;
+  if (bps == 0) { const char* e = getenv("FGDM_GN_BPS"); bps = e ? atoi(e) : 4; if (bps < 1) bps = 4; }
+  int want = (bps * num_sms() + NB - 1) / NB;    // ~4 fat blocks per SM in total (measured best: prologue amortised, loads still deep)
   if (want > kGnMaxChunks) want = kGnMaxChunks;
   if (want < 1) want = 1;
   int ppc = (HW + want - 1) / want;
@@ -51,8 +55,11 @@ FGDM_DEVINL const __nv_bfloat16* gn_src(const __nv_bfloat16* x0, const __nv_bflo
 }
 
 // partial[(img*chunks + chunk)*G + g] = {sum, sumsq} over this block's pixels
+// The last block of each image to finish (atomic ticket) reduces the partials in FIXED order (bit-reproducible)
+// into stats[img*G + g] = {mean, rstd}, so the apply kernel's prologue is a single 256-byte read.
 __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __restrict__ x1,
-                                float2* __restrict__ partial, GnGeom g) {
+                                float2* partial, float2* __restrict__ stats, unsigned int* counters, float eps,
+                                GnGeom g) {
   extern __shared__ float sm[];  // [k][C] sums, then [k][C] sumsq
   const int C = g.C0 + g.C1;
   const int v = threadIdx.x % g.V;
@@ -113,23 +120,20 @@ __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
     }
     partial[(static_cast<size_t>(img) * g.chunks + blockIdx.x) * g.G + grp] = make_float2(a, b);
   }
-}
-
-__global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __restrict__ x1,
-                                const float2* __restrict__ partial, const float* __restrict__ gamma,
-                                const float* __restrict__ beta, __nv_bfloat16* __restrict__ y, float eps, int silu,
-                                GnGeom g) {
-  __shared__ float s_mean[64], s_rstd[64];
-  const int C = g.C0 + g.C1;
-  const int cpg = C / g.G;
-  const int img = blockIdx.y;
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(&counters[img], 1u) == static_cast<unsigned>(g.chunks - 1));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x == 0) counters[img] = 0;        // ready for the next launch on this stream
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const float inv_cnt = 1.0f / (static_cast<float>(g.HW) * cpg);
-  // fixed-order cooperative reduction of the per-chunk partials (bit-reproducible run to run)
   for (int grp = warp; grp < g.G; grp += nwarps) {
     float sum = 0.0f, sq = 0.0f;
     for (int ch = lane; ch < g.chunks; ch += 32) {
-      const float2 t = partial[(static_cast<size_t>(img) * g.chunks + ch) * g.G + grp];
+      const float2 t = __ldcg(&partial[(static_cast<size_t>(img) * g.chunks + ch) * g.G + grp]);
       sum += t.x; sq += t.y;
     }
     sum = warp_sum(sum);
@@ -137,11 +141,17 @@ __global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
     if (lane == 0) {
       const float mean = sum * inv_cnt;
       const float var = fmaxf(sq * inv_cnt - mean * mean, 0.0f);
-      s_mean[grp] = mean;
-      s_rstd[grp] = rsqrtf(var + eps);
+      stats[img * g.G + grp] = make_float2(mean, rsqrtf(var + eps));
     }
   }
-  __syncthreads();
+}
+
+__global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __restrict__ x1,
+                                const float2* __restrict__ stats, const float* __restrict__ gamma,
+                                const float* __restrict__ beta, __nv_bfloat16* __restrict__ y, int silu, GnGeom g) {
+  const int C = g.C0 + g.C1;
+  const int cpg = C / g.G;
+  const int img = blockIdx.y;
   const int v = threadIdx.x % g.V;
   const int pl = threadIdx.x / g.V;
   if (pl >= g.k) return;
@@ -150,9 +160,10 @@ __global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
   for (int i = 0; i < 8; ++i) {
     const int c = v * 8 + i;
     const int grp = c / cpg;
-    const float ga = gamma[c] * s_rstd[grp];
+    const float2 st = stats[img * g.G + grp];
+    const float ga = gamma[c] * st.y;
     a[i] = ga;
-    b[i] = beta[c] - s_mean[grp] * ga;
+    b[i] = beta[c] - st.x * ga;
   }
   const int p_begin = blockIdx.x * g.pix_per_chunk;
   int p_end = p_begin + g.pix_per_chunk;
@@ -184,7 +195,158 @@ __global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
   }
 }
 
-// workspace: at least NB * 128 * G float2. x1 may be null (C1 = 0). y: [NB, HW, C0+C1] bf16.
+// ---------------------------------------------------------------------------------------------
+// Single-launch, single-read GroupNorm for the low-resolution activations (hw <= 1024: most UNet launches).
+// One CTA owns an (image, channel slab) pair, a slab being the smallest run of channels that is both a whole
+// number of groups and a whole number of 8-channel vectors (lcm(C/G, 8): 40 channels for C = 320/640/1280).
+// The slab is read ONCE into registers (<= R 16-byte vectors per thread), reduced through shared memory in fixed
+// order, normalised from the registers and written: no partial buffer, no second launch, no second read.
+// ---------------------------------------------------------------------------------------------
+struct GnSlabGeom {
+  int HW, C0, C1, G;
+  int SV;        // 8-channel vectors per slab
+  int k;         // pixel lanes per CTA (threads = SV * k rounded up to a warp)
+  int cpg;       // channels per group
+  int gps;       // groups per slab
+};
+
+template <int R>
+__global__ void __launch_bounds__(512)
+gn_slab_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __restrict__ x1,
+               const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+               float eps, int silu, GnSlabGeom g) {
+  extern __shared__ float sm[];            // [k][SC] sums, then [k][SC] sums of squares (SC = slab channels)
+  __shared__ float s_mean[16], s_rstd[16];
+  const int C = g.C0 + g.C1;
+  const int SC = g.SV * 8;
+  const int sv = threadIdx.x % g.SV;
+  const int pl = threadIdx.x / g.SV;
+  const int img = blockIdx.y;
+  const int v = blockIdx.x * g.SV + sv;    // 8-channel vector index within the pixel
+  const size_t base = static_cast<size_t>(img) * g.HW;
+  const bool worker = pl < g.k;
+
+  uint4 u[R];
+  if (worker) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int pix = pl + r * g.k;
+      u[r] = (pix < g.HW) ? ld_nc_16(gn_src(x0, x1, g.C0, g.C1, base + pix, v)) : make_uint4(0, 0, 0, 0);
+    }
+    float s[8], ss[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = ss[i] = 0.0f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint32_t w[4] = {u[r].x, u[r].y, u[r].z, u[r].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = unpack_bf16x2(w[e]);
+        s[2 * e] += f.x; ss[2 * e] += f.x * f.x;
+        s[2 * e + 1] += f.y; ss[2 * e + 1] += f.y * f.y;
+      }
+    }
+    float4* d0 = reinterpret_cast<float4*>(sm + pl * SC + sv * 8);
+    float4* d1 = reinterpret_cast<float4*>(sm + g.k * SC + pl * SC + sv * 8);
+    d0[0] = make_float4(s[0], s[1], s[2], s[3]);
+    d0[1] = make_float4(s[4], s[5], s[6], s[7]);
+    d1[0] = make_float4(ss[0], ss[1], ss[2], ss[3]);
+    d1[1] = make_float4(ss[4], ss[5], ss[6], ss[7]);
+  }
+  __syncthreads();
+  // per-channel sums over the pixel lanes: 2*SC columns, each summed by 4 threads (strided) then combined in order
+  float* red = sm + 2 * g.k * SC;          // [SC] sums, [SC] sums of squares
+  for (int cb = 0; cb < 2 * SC; cb += blockDim.x >> 2) {
+    const int col = cb + (threadIdx.x >> 2), part = threadIdx.x & 3;
+    float a = 0.0f;
+    if (col < 2 * SC) {
+      const float* src = sm + (col < SC ? col : g.k * SC + (col - SC));
+      for (int l = part; l < g.k; l += 4) a += src[l * SC];
+    }
+    const float a1 = __shfl_down_sync(0xffffffffu, a, 1);
+    const float a2 = __shfl_down_sync(0xffffffffu, a, 2);
+    const float a3 = __shfl_down_sync(0xffffffffu, a, 3);
+    if (col < 2 * SC && part == 0) red[col] = (a + a1) + (a2 + a3);
+  }
+  __syncthreads();
+  if (threadIdx.x < g.gps) {
+    float a = 0.0f, b = 0.0f;
+    for (int c = threadIdx.x * g.cpg; c < (threadIdx.x + 1) * g.cpg; ++c) {
+      a += red[c];
+      b += red[SC + c];
+    }
+    const float inv_cnt = 1.0f / (static_cast<float>(g.HW) * g.cpg);
+    const float mean = a * inv_cnt;
+    const float var = fmaxf(b * inv_cnt - mean * mean, 0.0f);
+    s_mean[threadIdx.x] = mean;
+    s_rstd[threadIdx.x] = rsqrtf(var + eps);
+  }
+  __syncthreads();
+  if (!worker) return;
+  float a[8], b[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = v * 8 + i;
+    const int grp = (sv * 8 + i) / g.cpg;
+    const float ga = gamma[c] * s_rstd[grp];
+    a[i] = ga;
+    b[i] = beta[c] - s_mean[grp] * ga;
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int pix = pl + r * g.k;
+    if (pix >= g.HW) break;
+    const uint32_t w[4] = {u[r].x, u[r].y, u[r].z, u[r].w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = unpack_bf16x2(w[e]);
+      float r0 = f.x * a[2 * e] + b[2 * e];
+      float r1 = f.y * a[2 * e + 1] + b[2 * e + 1];
+      if (silu) { r0 = silu_f(r0); r1 = silu_f(r1); }
+      o[e] = pack_bf16x2(r0, r1);
+    }
+    *reinterpret_cast<uint4*>(y + (base + pix) * C + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+static int gcd_int(int a, int b) { return b == 0 ? a : gcd_int(b, a % b); }
+
+// Returns 1 if the slab path was launched, 0 if it does not apply, -1 on error.
+static int try_groupnorm_slab(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, int NB,
+                              int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream) {
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("FGDM_GN_SLAB"); enabled = (e && e[0] == '0') ? 0 : 1; }
+  if (!enabled) return 0;
+  const int C = C0 + C1;
+  GnSlabGeom g;
+  g.HW = HW; g.C0 = C0; g.C1 = C1; g.G = G;
+  g.cpg = C / G;
+  const int slab = g.cpg / gcd_int(g.cpg, 8) * 8;      // lcm(cpg, 8)
+  if (C % slab != 0) return 0;
+  g.SV = slab / 8;
+  g.gps = slab / g.cpg;
+  if (g.gps > 16 || g.SV > 64) return 0;
+  int tmax = (static_cast<long long>(HW) * g.SV > 256 * 8) ? 512 : 256;
+  g.k = tmax / g.SV;
+  if (g.k > HW) g.k = HW;
+  if (g.k < 1) return 0;
+  const int R = (HW + g.k - 1) / g.k;
+  if (R > 16) return 0;
+  const int threads = (g.SV * g.k + 31) / 32 * 32;
+  const size_t smem = static_cast<size_t>(2) * (g.k + 1) * slab * sizeof(float);
+  if (smem > 48 * 1024) return 0;
+  const dim3 grid(C / slab, NB);
+  const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(x0);
+  const __nv_bfloat16* a1 = reinterpret_cast<const __nv_bfloat16*>(x1);
+  __nv_bfloat16* yo = reinterpret_cast<__nv_bfloat16*>(y);
+  if (R <= 4) gn_slab_kernel<4><<<grid, threads, smem, stream>>>(a0, a1, gamma, beta, yo, eps, silu, g);
+  else if (R <= 8) gn_slab_kernel<8><<<grid, threads, smem, stream>>>(a0, a1, gamma, beta, yo, eps, silu, g);
+  else gn_slab_kernel<16><<<grid, threads, smem, stream>>>(a0, a1, gamma, beta, yo, eps, silu, g);
+  return check_launch("gn_slab_kernel") ? -1 : 1;
+}
+
+// workspace: at least NB * 129 * G float2 (per-chunk partials, then {mean, rstd} per image and group). x1 may be null (C1 = 0). y: [NB, HW, C0+C1] bf16.
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                      int NB, int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream) {
   const int C = C0 + C1;
@@ -192,17 +354,30 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
     set_error("groupnorm: unsupported channels C0=%d C1=%d G=%d", C0, C1, G);
     return -1;
   }
+  const int rc = try_groupnorm_slab(x0, x1, y, gamma, beta, NB, HW, C0, C1, G, eps, silu, stream);
+  if (rc != 0) return rc < 0 ? -1 : 0;
   const GnGeom g = gn_geom(NB, HW, C0, C1, G);
   const dim3 grid(g.chunks, NB);
   const size_t smem = static_cast<size_t>(2) * g.k * C * sizeof(float);
+  static unsigned int* counters = nullptr;       // per-image tickets, zero between launches (single stream per process)
+  if (!counters) {
+    if (cudaMalloc(&counters, kGnMaxImages * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(counters, 0, kGnMaxImages * sizeof(unsigned int)) != cudaSuccess) {
+      set_error("groupnorm: cannot allocate ticket counters");
+      counters = nullptr;
+      return -1;
+    }
+  }
+  if (NB > kGnMaxImages) { set_error("groupnorm: NB=%d > %d", NB, kGnMaxImages); return -1; }
+  float2* partial = reinterpret_cast<float2*>(workspace);
+  float2* stats = partial + static_cast<size_t>(NB) * kGnMaxChunks * G;
   gn_stats_kernel<<<grid, g.threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
-                                                     reinterpret_cast<const __nv_bfloat16*>(x1),
-                                                     reinterpret_cast<float2*>(workspace), g);
+                                                     reinterpret_cast<const __nv_bfloat16*>(x1), partial, stats,
+                                                     counters, eps, g);
   if (check_launch("gn_stats_kernel")) return -1;
   gn_apply_kernel<<<grid, g.threads, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
                                                   reinterpret_cast<const __nv_bfloat16*>(x1),
-                                                  reinterpret_cast<const float2*>(workspace), gamma, beta,
-                                                  reinterpret_cast<__nv_bfloat16*>(y), eps, silu, g);
+                                                  stats, gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), silu, g);
   return check_launch("gn_apply_kernel");
 }
 

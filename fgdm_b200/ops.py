@@ -136,7 +136,7 @@ def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):
 
 def _gn_workspace(device, nb, groups):
     # per call (a cached buffer that is later re-allocated would dangle inside captured CUDA graphs)
-    return torch.empty(nb * 128 * groups * 2, device=device, dtype=torch.float32)
+    return torch.empty(nb * 129 * groups * 2, device=device, dtype=torch.float32)
 
 
 def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=None):

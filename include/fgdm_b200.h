@@ -98,7 +98,7 @@ int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int 
                    int d, int tok_pad, float scale, void* stream);
 
 /* GroupNorm32 (+SiLU): util.py:223-225, openaimodel.py:221-224; attention.py:76-77; model.py:33-39.
- * x0/x1 virtual channel concat; workspace >= nb*128*groups*8 bytes. */
+ * x0/x1 virtual channel concat; workspace >= nb*129*groups*8 bytes. */
 int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                    int nb, int hw, int c0, int c1, int groups, float eps, int silu, void* stream);
 
