@@ -35,7 +35,8 @@ struct AttnParams {
   int ld_out;
 };
 
-static constexpr int kAttnThreads = 256;
+static constexpr int kAttnSoftmaxWarps = 8;
+static constexpr int kAttnThreads = 32 * (kAttnSoftmaxWarps + 1);   // + one TMA / MMA-issue warp
 static constexpr float kRescaleThreshold = 8.0f;   // log2 units: P <= 2^8 before a row's reference max is refreshed
 
 // KA: 64-wide K-chunks of the head dim (Q/K tiles are KA swizzle atoms), DV: V^T rows of this CTA's tile (the
@@ -48,17 +49,22 @@ struct AttnCfg {
   static constexpr int kVAtom = DV * 128;              // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kVBytes = (BN / 64) * kVAtom;
   static constexpr int kPBytes = (BN / 64) * 128 * 128;
-  static constexpr int kSmemBytes = kQBytes + 2 * (kKBytes + kVBytes) + kPBytes + 1024 /*align*/ + 1024 /*row max*/ + 128;
+  static constexpr int kSmemBytes = kQBytes + 2 * (kKBytes + kVBytes) + kPBytes + 1024 /*align*/ + 2048 /*row max*/ + 128;
   static constexpr int kTmemCols = (BN + DV <= 128) ? 128 : 256;
 };
 
-// 256 threads: TWO threads per query row (warps w and w+4 own the same 32 TMEM lanes and split the tile's key
-// columns), so each SM sub-partition has 4 warps (2 resident CTAs) to hide MUFU / TMEM latency behind.
-// Flow per KV tile j (thread 0 also drives TMA + MMA):
-//   wait S(j) | tcgen05.ld this thread's half of the S row | half-row max -> smem | barrier A |
-//   thread 0 issues S(j+1) (S is in registers everywhere: its TMEM columns are free) | row max = max of the two
-//   halves | wait PV(j-1) | lazy refresh of the row's reference max (then rescale the O row in TMEM: rare) |
-//   exp2 -> bf16 P tile in swizzled smem | barrier B | warp 0 writes the ones-row of V(j), issues PV(j).
+FGDM_DEVINL void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+// Warp-specialised: 8 softmax warps + 1 TMA/MMA-issue warp, no CTA-wide barrier inside the KV loop.
+// TWO threads per query row (softmax warps w and w+4 own the same 32 TMEM lanes and split the tile's key columns),
+// so each SM sub-partition has 4 softmax warps (2 resident CTAs) to hide MUFU / TMEM latency behind.
+//   softmax thread, tile j:  wait S(j) | tcgen05.ld its half of the S row | arrive s_free | half-row max, exchanged
+//       with the partner warp (64-thread named barrier) | wait PV(j-1) | lazy refresh of the row's reference max
+//       (then rescale the O row in TMEM: rare) | exp2 -> bf16 P tile in swizzled smem | arrive p_ready
+//   issue warp, tile j:      wait s_free(j) -> issue S(j+1) (overlaps the softmax of tile j) |
+//       wait p_ready(j), V(j) -> write the ones-row of V(j) -> issue PV(j) | prefetch K(j+2), V(j+1) by TMA
 // The softmax denominator is NOT accumulated on the CUDA cores: V^T row `dv_real` of every tile is overwritten with
 // 1.0, so O[:, dv_real] = sum_j P[:, j] comes out of the PV tensor-core product (from the same bf16-rounded P as
 // the numerator) and is rescaled together with O.
@@ -78,20 +84,20 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   uint8_t* sK = sQ + Cfg::kQBytes;                  // 2 stages
   uint8_t* sV = sK + 2 * Cfg::kKBytes;              // 2 stages
   uint8_t* sP = sV + 2 * Cfg::kVBytes;
-  float* sMax = reinterpret_cast<float*>(sP + Cfg::kPBytes);   // [2 halves][128 rows]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + 256);
+  float* sMax = reinterpret_cast<float*>(sP + Cfg::kPBytes);   // [2 parities][2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + 512);
   uint64_t* bar_q = bars;
   uint64_t* bar_k = bars + 1;   // [2]
   uint64_t* bar_v = bars + 3;   // [2]
-  uint64_t* bar_s = bars + 5;
-  uint64_t* bar_o = bars + 6;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 7);
+  uint64_t* bar_s = bars + 5;   // S(j) complete            (tcgen05.commit)
+  uint64_t* bar_o = bars + 6;   // PV(j) complete           (tcgen05.commit)
+  uint64_t* bar_sfree = bars + 7;   // S(j) is in registers everywhere (8 warp arrivals)
+  uint64_t* bar_pready = bars + 8;  // P(j) is in smem               (8 warp arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
-  const int half = warp >> 2;                       // which half of the S / O columns this thread owns
-  const int row = tid & 127;                        // query row within the tile == TMEM lane
   const int q0 = blockIdx.x * 128;
   const int bh = blockIdx.y;
   const int v0 = blockIdx.z * p.dv_per;             // first V column of this CTA
@@ -108,9 +114,11 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     mbar_init(&bar_v[1], 1);
     mbar_init(bar_s, 1);
     mbar_init(bar_o, 1);
+    mbar_init(bar_sfree, kAttnSoftmaxWarps);
+    mbar_init(bar_pready, kAttnSoftmaxWarps);
     fence_barrier_init();
   }
-  if (warp == 0) {
+  if (warp == kAttnSoftmaxWarps) {
     tmem_alloc(tmem_ptr, Cfg::kTmemCols);
     tmem_relinquish();
   }
@@ -121,171 +129,77 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   const uint32_t tmem_s = tmem_base;
   const uint32_t tmem_o = tmem_base + BN;
 
-  // K(j) is released as soon as S(j) has completed, V(j) only after PV(j): separate barriers let K run two
-  // tiles ahead and V one and a half.
-  auto load_k = [&](int j) {
-    const int st = j & 1;
-    mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
+  if (warp == kAttnSoftmaxWarps) {
+    // ===================== TMA + MMA issue warp =====================
+    auto load_k = [&](int j) {
+      const int st = j & 1;
+      mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
 #pragma unroll
-    for (int a = 0; a < KA; ++a)
-      tma_load_3d(sK + st * Cfg::kKBytes + a * (BN * 128), &map_k, &bar_k[st], a * 64, j * BN, bh);
-  };
-  auto load_v = [&](int j) {
-    const int st = j & 1;
-    mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
-#pragma unroll
-    for (int a = 0; a < kPA; ++a)
-      tma_load_3d(sV + st * Cfg::kVBytes + a * Cfg::kVAtom, &map_vt, &bar_v[st], j * BN + a * 64, v0, bh);
-  };
-  auto issue_s = [&](int j) {
-    const int st = j & 1;
-    constexpr uint32_t idesc = make_idesc_bf16(128, BN);
-#pragma unroll
-    for (int a = 0; a < KA; ++a) {
-      const uint64_t dq = make_desc_sw128(smem_u32(sQ + a * 16384));
-      const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes + a * (BN * 128)));
-#pragma unroll
-      for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem_s, dq + 2 * k, dk + 2 * k, idesc, (a | k) != 0 ? 1u : 0u);
-    }
-    tc_commit(bar_s);
-  };
-  auto issue_pv = [&](int j) {
-    const int st = j & 1;
-    constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
-#pragma unroll
-    for (int ks = 0; ks < BN / 16; ++ks) {
-      const uint64_t dp = make_desc_sw128(smem_u32(sP + (ks >> 2) * 16384)) + 2 * (ks & 3);
-      const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes + (ks >> 2) * Cfg::kVAtom)) + 2 * (ks & 3);
-      tc_mma_bf16(tmem_o, dp, dv, idesc_pv, (j | ks) != 0 ? 1u : 0u);
-    }
-    tc_commit(bar_o);
-  };
-
-  if (tid == 0) {
-    mbar_expect_tx(bar_q, Cfg::kQBytes);
-#pragma unroll
-    for (int a = 0; a < KA; ++a) tma_load_3d(sQ + a * 16384, &map_q, bar_q, a * 64, q0, bh);
-    load_k(0);
-    load_v(0);
-    if (num_kv > 1) {
-      load_k(1);
-      load_v(1);
-    }
-    mbar_wait(bar_q, 0);
-    mbar_wait(&bar_k[0], 0);
-    tc_fence_after();
-    issue_s(0);
-  }
-
-  const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
-  const uint32_t s_addr = tmem_s + lane_addr + half * HB;
-  const uint32_t o_addr = tmem_o + lane_addr + half * HV;
-  float m_ref = -INFINITY;                            // reference max (scaled, log2 domain) used for exp2
-
-  for (int j = 0; j < num_kv; ++j) {
-    const int valid = p.Nk - j * BN - half * HB;       // keys valid in this thread's half tile (may exceed HB)
-    mbar_wait(bar_s, j & 1);
-    tc_fence_after();
-
-    // ---- this thread's half of the S row -> registers, half-row maximum ----
-    uint32_t s[HB];
-#pragma unroll
-    for (int c = 0; c < HB; c += 32) tmem_ld_32x32(s_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
-    tmem_ld_wait();
-    float hmax;
-    {
-      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-      if (valid >= HB) {
-#pragma unroll
-        for (int i = 0; i < HB; i += 8) {
-#pragma unroll
-          for (int u = 0; u < 4; ++u)
-            mx[u] = fmax3(mx[u], __uint_as_float(s[i + 2 * u]), __uint_as_float(s[i + 2 * u + 1]));
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < HB; i += 8) {
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const int c = i + 2 * u;
-            mx[u] = fmax3(mx[u], (c < valid) ? __uint_as_float(s[c]) : -INFINITY,
-                          (c + 1 < valid) ? __uint_as_float(s[c + 1]) : -INFINITY);
-          }
-        }
-      }
-      hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-    }
-    sMax[half * 128 + row] = hmax;
-    tc_fence_before();
-    __syncthreads();                                   // barrier A: S(j) is in registers, half maxima are in smem
-
-    if (tid == 0) {
-      tc_fence_after();
-      if (j + 2 < num_kv) load_k(j + 2);               // K stage j&1 is free: S(j) has completed
-      if (j + 1 < num_kv) {
-        mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
-        tc_fence_after();
-        issue_s(j + 1);                                // overlaps this tile's softmax
-      }
-    }
-    const float tmax = fmaxf(hmax, sMax[(half ^ 1) * 128 + row]) * p.scale_log2;
-
-    // ---- PV(j-1) must have drained before O is touched or the P tile is overwritten ----
-    if (j > 0) {
-      mbar_wait(bar_o, (j - 1) & 1);
-      tc_fence_after();
-      if (tid == 0 && j + 1 < num_kv) load_v(j + 1);   // V stage (j+1)&1 == (j-1)&1 is free now
-    }
-
-    // ---- lazy rescale: refresh the reference max only when it grew by more than 2^8 ----
-    const bool need = tmax > m_ref + kRescaleThreshold;
-    if (__any_sync(0xffffffffu, need)) {
-      const float m_new = need ? tmax : m_ref;
-      const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
-      m_ref = m_new;
-      if (j > 0) {
-#pragma unroll
-        for (int c = 0; c < HV; c += 8) {
-          uint32_t r[8];
-          tmem_ld_32x8(o_addr + c, r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 8; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st_32x8(o_addr + c, r);
-        }
-        tmem_st_wait();
-      }
-    }
-
-    // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major) ----
-    const float neg_m = -m_ref;
-    const uint32_t sP_row = smem_u32(sP) + row * 128;
-    auto emit = [&](auto masked) {
-#pragma unroll
-      for (int c = 0; c < HB; c += 8) {
-        uint32_t pk[4];
-#pragma unroll
-        for (int i = 0; i < 8; i += 2) {
-          float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
-          float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
-          if constexpr (decltype(masked)::value) {
-            if (c + i >= valid) p0 = 0.0f;
-            if (c + i + 1 >= valid) p1 = 0.0f;
-          }
-          pk[i >> 1] = pack_bf16x2(p0, p1);
-        }
-        const int cc = half * HB + c;                    // column within the tile
-        const int chunk = ((cc & 63) >> 3) ^ (row & 7);
-        st_shared_16(sP_row + (cc >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
-      }
+      for (int a = 0; a < KA; ++a)
+        tma_load_3d(sK + st * Cfg::kKBytes + a * (BN * 128), &map_k, &bar_k[st], a * 64, j * BN, bh);
     };
-    if (valid >= HB) emit(std::false_type{}); else emit(std::true_type{});
+    auto load_v = [&](int j) {
+      const int st = j & 1;
+      mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
+#pragma unroll
+      for (int a = 0; a < kPA; ++a)
+        tma_load_3d(sV + st * Cfg::kVBytes + a * Cfg::kVAtom, &map_vt, &bar_v[st], j * BN + a * 64, v0, bh);
+    };
+    auto issue_s = [&](int j) {
+      const int st = j & 1;
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN);
+#pragma unroll
+      for (int a = 0; a < KA; ++a) {
+        const uint64_t dq = make_desc_sw128(smem_u32(sQ + a * 16384));
+        const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes + a * (BN * 128)));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem_s, dq + 2 * k, dk + 2 * k, idesc, (a | k) != 0 ? 1u : 0u);
+      }
+      tc_commit(bar_s);
+    };
+    auto issue_pv = [&](int j) {
+      const int st = j & 1;
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
+#pragma unroll
+      for (int ks = 0; ks < BN / 16; ++ks) {
+        const uint64_t dp = make_desc_sw128(smem_u32(sP + (ks >> 2) * 16384)) + 2 * (ks & 3);
+        const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes + (ks >> 2) * Cfg::kVAtom)) + 2 * (ks & 3);
+        tc_mma_bf16(tmem_o, dp, dv, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+      }
+      tc_commit(bar_o);
+    };
 
-    fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
-    tc_fence_before();
-    __syncthreads();            // barrier B: the P tile is complete
-
-    if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(bar_q, Cfg::kQBytes);
+#pragma unroll
+      for (int a = 0; a < KA; ++a) tma_load_3d(sQ + a * 16384, &map_q, bar_q, a * 64, q0, bh);
+      load_k(0);
+      load_v(0);
+      if (num_kv > 1) {
+        load_k(1);
+        load_v(1);
+      }
+      mbar_wait(bar_q, 0);
+      mbar_wait(&bar_k[0], 0);
+      tc_fence_after();
+      issue_s(0);
+    }
+    for (int j = 0; j < num_kv; ++j) {
+      if (lane == 0) {
+        if (j + 1 < num_kv) {
+          mbar_wait(bar_sfree, j & 1);                   // S(j) is in registers: its TMEM columns and K stage are free
+          tc_fence_after();
+          if (j + 2 < num_kv) load_k(j + 2);
+          mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
+          tc_fence_after();
+          issue_s(j + 1);                                // overlaps the softmax of tile j
+        }
+        if (j >= 1 && j + 1 < num_kv) {
+          mbar_wait(bar_o, (j - 1) & 1);                 // PV(j-1) done: V stage (j+1)&1 is free
+          load_v(j + 1);
+        }
+      }
+      __syncwarp();
       mbar_wait(&bar_v[j & 1], (j >> 1) & 1);
       // ones-row: V^T row dv_real of every key-atom := 1.0 (a full 128-byte swizzle row, so the swizzle is moot)
       if (lane < kPA * 8) {
@@ -295,44 +209,152 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
+        mbar_wait(bar_pready, j & 1);
         tc_fence_after();
         issue_pv(j);
       }
+      __syncwarp();
     }
-  }
+  } else {
+    // ===================== softmax warps =====================
+    const int half = warp >> 2;                       // which half of the S / O columns this thread owns
+    const int row = tid & 127;                        // query row within the tile == TMEM lane
+    const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t s_addr = tmem_s + lane_addr + half * HB;
+    const uint32_t o_addr = tmem_o + lane_addr + half * HV;
+    const int pair_bar = 1 + (warp & 3);
+    float m_ref = -INFINITY;                            // reference max (scaled, log2 domain) used for exp2
 
-  // ---- normalise and store: out[img, q, head*d + v0 + e]; the denominator is O column dv_real ----
-  mbar_wait(bar_o, (num_kv - 1) & 1);
-  tc_fence_after();
-  const int q = q0 + row;
-  float inv;
-  {
-    uint32_t r1[1];
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1[0]) : "r"(tmem_o + lane_addr + p.dv_real) : "memory");
-    tmem_ld_wait();
-    inv = 1.0f / __uint_as_float(r1[0]);
-  }
-  const int img = bh / p.heads;
-  const int head = bh - img * p.heads;
-  __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0 + half * HV;
+    for (int j = 0; j < num_kv; ++j) {
+      const int valid = p.Nk - j * BN - half * HB;       // keys valid in this thread's half tile (may exceed HB)
+      mbar_wait(bar_s, j & 1);
+      tc_fence_after();
+
+      // ---- this thread's half of the S row -> registers, half-row maximum ----
+      uint32_t s[HB];
 #pragma unroll
-  for (int c = 0; c < HV; c += 8) {
-    uint32_t r[8];
-    tmem_ld_32x8(o_addr + c, r);
-    tmem_ld_wait();
-    const int col = half * HV + c;                       // column within this CTA's V slice
-    if (q < p.Nq && col < p.dv_real && v0 + col < p.d) {
-      *reinterpret_cast<uint4*>(dst + c) =
-          make_uint4(pack_bf16x2(__uint_as_float(r[0]) * inv, __uint_as_float(r[1]) * inv),
-                     pack_bf16x2(__uint_as_float(r[2]) * inv, __uint_as_float(r[3]) * inv),
-                     pack_bf16x2(__uint_as_float(r[4]) * inv, __uint_as_float(r[5]) * inv),
-                     pack_bf16x2(__uint_as_float(r[6]) * inv, __uint_as_float(r[7]) * inv));
+      for (int c = 0; c < HB; c += 32) tmem_ld_32x32(s_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_sfree);
+      float hmax;
+      {
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (valid >= HB) {
+#pragma unroll
+          for (int i = 0; i < HB; i += 8) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              mx[u] = fmax3(mx[u], __uint_as_float(s[i + 2 * u]), __uint_as_float(s[i + 2 * u + 1]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < HB; i += 8) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int c = i + 2 * u;
+              mx[u] = fmax3(mx[u], (c < valid) ? __uint_as_float(s[c]) : -INFINITY,
+                            (c + 1 < valid) ? __uint_as_float(s[c + 1]) : -INFINITY);
+            }
+          }
+        }
+        hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      }
+      float* mx_buf = sMax + (j & 1) * 256;
+      mx_buf[half * 128 + row] = hmax;
+      named_bar_sync(pair_bar, 64);                      // the two warps that share these 32 rows
+      const float tmax = fmaxf(hmax, mx_buf[(half ^ 1) * 128 + row]) * p.scale_log2;
+
+      // ---- PV(j-1) must have drained before O is touched or the P tile is overwritten ----
+      if (j > 0) {
+        mbar_wait(bar_o, (j - 1) & 1);
+        tc_fence_after();
+      }
+
+      // ---- lazy rescale: refresh the reference max only when it grew by more than 2^8 ----
+      const bool need = tmax > m_ref + kRescaleThreshold;
+      if (__any_sync(0xffffffffu, need)) {
+        const float m_new = need ? tmax : m_ref;
+        const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
+        m_ref = m_new;
+        if (j > 0) {
+#pragma unroll
+          for (int c = 0; c < HV; c += 8) {
+            uint32_t r[8];
+            tmem_ld_32x8(o_addr + c, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st_32x8(o_addr + c, r);
+          }
+          tmem_st_wait();
+        }
+      }
+
+      // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major) ----
+      const float neg_m = -m_ref;
+      const uint32_t sP_row = smem_u32(sP) + row * 128;
+      auto emit = [&](auto masked) {
+#pragma unroll
+        for (int c = 0; c < HB; c += 8) {
+          uint32_t pk[4];
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
+            float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
+            if constexpr (decltype(masked)::value) {
+              if (c + i >= valid) p0 = 0.0f;
+              if (c + i + 1 >= valid) p1 = 0.0f;
+            }
+            pk[i >> 1] = pack_bf16x2(p0, p1);
+          }
+          const int cc = half * HB + c;                    // column within the tile
+          const int chunk = ((cc & 63) >> 3) ^ (row & 7);
+          st_shared_16(sP_row + (cc >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
+        }
+      };
+      if (valid >= HB) emit(std::false_type{}); else emit(std::true_type{});
+
+      fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_pready);
+    }
+
+    // ---- normalise and store: out[img, q, head*d + v0 + e]; the denominator is O column dv_real ----
+    mbar_wait(bar_o, (num_kv - 1) & 1);
+    tc_fence_after();
+    const int q = q0 + row;
+    float inv;
+    {
+      uint32_t r1;
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1) : "r"(tmem_o + lane_addr + p.dv_real) : "memory");
+      tmem_ld_wait();
+      inv = 1.0f / __uint_as_float(r1);
+    }
+    const int img = bh / p.heads;
+    const int head = bh - img * p.heads;
+    __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0 + half * HV;
+#pragma unroll
+    for (int c = 0; c < HV; c += 8) {
+      uint32_t r[8];
+      tmem_ld_32x8(o_addr + c, r);
+      tmem_ld_wait();
+      const int col = half * HV + c;                       // column within this CTA's V slice
+      if (q < p.Nq && col < p.dv_real && v0 + col < p.d) {
+        *reinterpret_cast<uint4*>(dst + c) =
+            make_uint4(pack_bf16x2(__uint_as_float(r[0]) * inv, __uint_as_float(r[1]) * inv),
+                       pack_bf16x2(__uint_as_float(r[2]) * inv, __uint_as_float(r[3]) * inv),
+                       pack_bf16x2(__uint_as_float(r[4]) * inv, __uint_as_float(r[5]) * inv),
+                       pack_bf16x2(__uint_as_float(r[6]) * inv, __uint_as_float(r[7]) * inv));
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (warp == kAttnSoftmaxWarps) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
