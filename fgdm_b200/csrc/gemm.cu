@@ -34,7 +34,7 @@ static constexpr int kBK = 64;
 static constexpr int kEpiWarps = 8;                      // two warps per TMEM lane quarter, alternating 32-col panels
 static constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 static constexpr int kStgRow = 80;                       // staging row: 32 bf16 (64 B) + 16 B pad (conflict-free)
-static constexpr int kStgBytes = 32 * kStgRow;           // per epilogue warp
+static constexpr int kStgBytes = 32 * kStgRow + 4 * 128;  // per epilogue warp: 32x32 bf16 panel + 4 bias panels (fp32)
 
 template <int BN>
 struct GemmCfg {
@@ -170,15 +170,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
   } else {
     // ===================== epilogue warps (TMEM -> registers -> global) =====================
-    // Warp w may only touch TMEM lanes 32*(w%4)..+31; warps sharing a lane quarter alternate 32-column panels.
-    // bf16 outputs (and the first residual) go through a per-warp padded smem panel so that every global access
-    // is a run of full 64-byte row segments instead of 32 scattered 16-byte pieces.
+    // Warp w may only touch TMEM lanes 32*(w%4)..+31; the two warps sharing a lane quarter alternate 32-column
+    // panels. Everything that does not depend on the accumulator (residual panels, bias) is fetched BEFORE the
+    // accumulator barrier, so global-memory latency is paid once per tile, not once per panel; TMEM loads are
+    // double-buffered against the math. bf16 outputs and the first residual go through a per-warp padded smem
+    // panel so that every global access is a run of full 64-byte row segments.
     const int ew = warp - 2;
     const int quarter = warp & 3;
     const int half = ew >> 2;
-    const int row = quarter * 32 + lane;
     uint8_t* stg = smem_stg + ew * kStgBytes;
     const uint32_t stg_u32 = smem_u32(stg);
+    const uint32_t sbias_u32 = stg_u32 + 32 * kStgRow;           // [kMaxPanels][32] floats
+    constexpr int kPanels = BN / 32;
+    constexpr int kMaxP = (kPanels + 1) / 2;                     // panels per warp (upper bound)
+    const int np = (kPanels + 1 - half) / 2;                     // this warp's panels: c0 = half*32 + 64*i
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -188,180 +193,235 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       const int m = m_warp + lane;
       const bool row_ok = m < p.M;
       const int img = row_ok ? (m / p.rows_per_img) : 0;
-      mbar_wait(&acc_full[acc], acc_phase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
 
       if (p.out_mode == kOutGeglu) {
         constexpr int kHalf = BN / 2;
-#pragma unroll 1
-        for (int c0 = half * 32; c0 < kHalf; c0 += 64) {
-          uint32_t rx[32], rg[32];
-          tmem_ld_32x32(taddr + c0, rx);
-          tmem_ld_32x32(taddr + kHalf + c0, rg);
-          tmem_ld_wait();
-          const int ocol = n_tile * kHalf + c0;          // output column (value index)
-          const int bcol = n_tile * BN + c0;             // interleaved bias index
-          const bool col_ok = ocol < p.N / 2;            // warp-uniform
-          if (col_ok) {
-            uint32_t packed[16];
+        constexpr int kMaxG = (kHalf / 32 + 1) / 2;              // panel pairs per warp
+        const int ng = (kHalf / 32 + 1 - half) / 2;
+        // bias panels (value | gate) -> smem before the accumulator is ready
+        if (p.bias) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float x0 = __uint_as_float(rx[j]), x1 = __uint_as_float(rx[j + 1]);
-              float g0 = __uint_as_float(rg[j]), g1 = __uint_as_float(rg[j + 1]);
-              if (p.bias) {
-                x0 += __ldg(p.bias + bcol + j);
-                x1 += __ldg(p.bias + bcol + j + 1);
-                g0 += __ldg(p.bias + bcol + kHalf + j);
-                g1 += __ldg(p.bias + bcol + kHalf + j + 1);
+          for (int i = 0; i < kMaxG; ++i) {
+            if (i < ng) {
+              const int c0 = half * 32 + 64 * i;
+              const int bcol = n_tile * BN + c0;
+              float bx = 0.0f, bg = 0.0f;
+              if (n_tile * kHalf + c0 < p.N / 2) {
+                bx = __ldg(p.bias + bcol + lane);
+                bg = __ldg(p.bias + bcol + kHalf + lane);
               }
-              packed[j >> 1] = pack_bf16x2(x0 * gelu_erf_f(g0), x1 * gelu_erf_f(g1));
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (2 * i) * 128 + lane * 4), "f"(bx) : "memory");
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (2 * i + 1) * 128 + lane * 4), "f"(bg) : "memory");
             }
+          }
+        }
+        __syncwarp();
+        mbar_wait(&acc_full[acc], acc_phase);
+        tc_fence_after();
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-              st_shared_16(stg_u32 + lane * kStgRow + q * 16,
-                           make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]));
-            __syncwarp();
-            __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + ocol;
+        for (int i = 0; i < kMaxG; ++i) {
+          if (i < ng) {
+            const int c0 = half * 32 + 64 * i;
+            uint32_t rx[32], rg[32];
+            tmem_ld_32x32(taddr + c0, rx);
+            tmem_ld_32x32(taddr + kHalf + c0, rg);
+            tmem_ld_wait();
+            const int ocol = n_tile * kHalf + c0;          // output column (value index)
+            if (ocol < p.N / 2) {                          // warp-uniform
+              uint32_t packed[16];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int idx = lane + 32 * i, r = idx >> 2, ch = idx & 3;
-              if (m_warp + r < p.M)
-                *reinterpret_cast<uint4*>(obase + static_cast<size_t>(m_warp + r) * p.ldo + ch * 8) =
-                    ld_shared_16(stg_u32 + r * kStgRow + ch * 16);
+              for (int j = 0; j < 32; j += 4) {
+                float4 bx = make_float4(0.f, 0.f, 0.f, 0.f), bg = bx;
+                if (p.bias) {
+                  const uint4 ux = ld_shared_16(sbias_u32 + (2 * i) * 128 + j * 4);
+                  const uint4 ug = ld_shared_16(sbias_u32 + (2 * i + 1) * 128 + j * 4);
+                  bx = make_float4(__uint_as_float(ux.x), __uint_as_float(ux.y), __uint_as_float(ux.z), __uint_as_float(ux.w));
+                  bg = make_float4(__uint_as_float(ug.x), __uint_as_float(ug.y), __uint_as_float(ug.z), __uint_as_float(ug.w));
+                }
+                const float x0 = __uint_as_float(rx[j]) + bx.x, x1 = __uint_as_float(rx[j + 1]) + bx.y;
+                const float x2 = __uint_as_float(rx[j + 2]) + bx.z, x3 = __uint_as_float(rx[j + 3]) + bx.w;
+                const float g0 = __uint_as_float(rg[j]) + bg.x, g1 = __uint_as_float(rg[j + 1]) + bg.y;
+                const float g2 = __uint_as_float(rg[j + 2]) + bg.z, g3 = __uint_as_float(rg[j + 3]) + bg.w;
+                packed[j >> 1] = pack_bf16x2(x0 * gelu_erf_f(g0), x1 * gelu_erf_f(g1));
+                packed[(j >> 1) + 1] = pack_bf16x2(x2 * gelu_erf_f(g2), x3 * gelu_erf_f(g3));
+              }
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+                st_shared_16(stg_u32 + lane * kStgRow + q * 16,
+                             make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]));
+              __syncwarp();
+              __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + ocol;
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const int idx = lane + 32 * q, r = idx >> 2, ch = idx & 3;
+                if (m_warp + r < p.M)
+                  *reinterpret_cast<uint4*>(obase + static_cast<size_t>(m_warp + r) * p.ldo + ch * 8) =
+                      ld_shared_16(stg_u32 + r * kStgRow + ch * 16);
+              }
+              __syncwarp();
             }
-            __syncwarp();
           }
         }
       } else {
         const bool staged = p.out_mode == kOutBf16;
+        const bool pre_res = staged && p.res0 != nullptr;
+        // ---- accumulator-independent prefetch: first residual panel (coalesced layout, registers), bias (smem) ----
+        auto load_res = [&](int i, uint4 (&dst)[4]) {
+          const int col = n_tile * BN + half * 32 + 64 * i;
+          const bool on = i < np && col < p.N;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int idx = lane + 32 * q, rr = idx >> 2, ch = idx & 3;
+            dst[q] = make_uint4(0, 0, 0, 0);
+            if (on && m_warp + rr < p.M)
+              dst[q] = *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m_warp + rr) * p.ld_res0 + col + ch * 8);
+          }
+        };
+        uint4 rres[4];
+        if (pre_res) load_res(0, rres);
+        if (p.bias) {
 #pragma unroll 1
-        for (int c0 = half * 32; c0 < BN; c0 += 64) {
-          uint32_t r[32];
-          tmem_ld_32x32(taddr + c0, r);
-          tmem_ld_wait();
-          const int col = n_tile * BN + c0;
-          if (col >= p.N) continue;                      // warp-uniform
-          if (staged && p.res0) {                        // coalesced load of the residual panel
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int idx = lane + 32 * i, rr = idx >> 2, ch = idx & 3;
-              uint4 u = make_uint4(0, 0, 0, 0);
-              if (m_warp + rr < p.M)
-                u = *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m_warp + rr) * p.ld_res0 + col + ch * 8);
-              st_shared_16(stg_u32 + rr * kStgRow + ch * 16, u);
-            }
-            __syncwarp();
+          for (int i = 0; i < np; ++i) {
+            const int col = n_tile * BN + half * 32 + 64 * i;
+            if (col < p.N)
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + i * 128 + lane * 4), "f"(__ldg(p.bias + col + lane)) : "memory");
           }
-          float v[32];
+        }
+        __syncwarp();
+        mbar_wait(&acc_full[acc], acc_phase);
+        tc_fence_after();
+
+#pragma unroll 1
+        for (int i = 0; i < np; ++i) {
+          {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
+            const int col = n_tile * BN + half * 32 + 64 * i;
+            if (col >= p.N) { tmem_ld_wait(); continue; }    // warp-uniform
+            {
+              if (pre_res) {                                 // residual panel: coalesced registers -> smem
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (p.bias) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
-              v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
-            }
-          }
-          if (p.rowvec) {
-            const float* rv = p.rowvec + static_cast<size_t>(img) * p.ld_rowvec + col;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(rv + j));
-              v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
-            }
-          }
-          if (p.alpha != 1.0f) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
-          }
-          if (p.act == kActRelu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
-          } else if (p.act == kActSilu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = silu_f(v[j]);
-          }
-          if (p.res0) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              uint4 u;
-              if (staged) u = ld_shared_16(stg_u32 + lane * kStgRow + q * 16);
-              else u = row_ok ? *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m) * p.ld_res0 + col + q * 8)
-                              : make_uint4(0, 0, 0, 0);
-              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack_bf16x2(w4[e]);
-                v[q * 8 + e * 2] += f.x;
-                v[q * 8 + e * 2 + 1] += f.y;
+                for (int q = 0; q < 4; ++q) {
+                  const int idx = lane + 32 * q, rr = idx >> 2, ch = idx & 3;
+                  st_shared_16(stg_u32 + rr * kStgRow + ch * 16, rres[q]);
+                }
+                load_res(i + 1, rres);                       // next panel's residual is in flight during this one
+                __syncwarp();
               }
-            }
-          }
-          if (p.res1 && row_ok) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(m) * p.ld_res1 + col);
+              tmem_ld_wait();
+              float v[32];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint4 u = rp[q];
-              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+              for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+              if (p.bias) {
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack_bf16x2(w4[e]);
-                v[q * 8 + e * 2] += f.x;
-                v[q * 8 + e * 2 + 1] += f.y;
+                for (int j = 0; j < 32; j += 4) {
+                  const uint4 u = ld_shared_16(sbias_u32 + i * 128 + j * 4);
+                  v[j] += __uint_as_float(u.x); v[j + 1] += __uint_as_float(u.y);
+                  v[j + 2] += __uint_as_float(u.z); v[j + 3] += __uint_as_float(u.w);
+                }
               }
-            }
-          }
-          if (staged) {
+              if (p.rowvec) {
+                const float* rv = p.rowvec + static_cast<size_t>(img) * p.ld_rowvec + col;
 #pragma unroll
-            for (int q = 0; q < 4; ++q)
-              st_shared_16(stg_u32 + lane * kStgRow + q * 16,
-                           make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                      pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
-            __syncwarp();
-            __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + p.col_off + col;
+                for (int j = 0; j < 32; j += 4) {
+                  const float4 b4 = __ldg(reinterpret_cast<const float4*>(rv + j));
+                  v[j] += b4.x; v[j + 1] += b4.y; v[j + 2] += b4.z; v[j + 3] += b4.w;
+                }
+              }
+              if (p.alpha != 1.0f) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int idx = lane + 32 * i, rr = idx >> 2, ch = idx & 3;
-              if (m_warp + rr < p.M)
-                *reinterpret_cast<uint4*>(obase + static_cast<size_t>(m_warp + rr) * p.ldo + ch * 8) =
-                    ld_shared_16(stg_u32 + rr * kStgRow + ch * 16);
-            }
-            __syncwarp();
-          } else if (!row_ok) {
-            // nothing to store for padding rows
-          } else if (p.out_mode == kOutNchwF32) {
-            // lanes hold consecutive pixels: each channel plane gets a coalesced 128-byte store
-            const int pix = m - img * p.rows_per_img;
-            float* dst = reinterpret_cast<float*>(p.out) + static_cast<size_t>(img) * p.n_store * p.rows_per_img + pix;
+                for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+              }
+              if (p.act == kActRelu) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col + j < p.n_store) dst[static_cast<size_t>(col + j) * p.rows_per_img] = v[j];
-          } else if (p.out_mode == kOutF32) {
-            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
-                                                    static_cast<size_t>(m) * p.ldo + p.col_off + col);
+                for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.0f);
+              } else if (p.act == kActSilu) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
-          } else {  // kOutQkv
-            const int tok = m - img * p.rows_per_img;
+                for (int j = 0; j < 32; ++j) v[j] = silu_f(v[j]);
+              }
+              if (p.res0) {
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              const int cg = col + g * 8;
-              const int sect = cg / p.inner + p.qkv_first;  // 0 q, 1 k, 2 v
-              const int cc = cg % p.inner;
-              const int head = cc / p.dhead;
-              const int e = cc - head * p.dhead;
-              if (sect < 2) {
-                __nv_bfloat16* base = (sect == 0) ? p.q_out : p.k_out;
-                uint4* dst = reinterpret_cast<uint4*>(
-                    base + ((static_cast<size_t>(img) * p.heads + head) * p.rows_per_img + tok) * p.dhead + e);
-                *dst = make_uint4(pack_bf16x2(v[g * 8], v[g * 8 + 1]), pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]),
-                                  pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]));
-              } else {
-                __nv_bfloat16* dst =
-                    p.vt_out + ((static_cast<size_t>(img) * p.heads + head) * p.dhead + e) * p.tok_pad + tok;
+                for (int q = 0; q < 4; ++q) {
+                  uint4 u;
+                  if (staged) u = ld_shared_16(stg_u32 + lane * kStgRow + q * 16);
+                  else u = row_ok ? *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m) * p.ld_res0 + col + q * 8)
+                                  : make_uint4(0, 0, 0, 0);
+                  const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) dst[static_cast<size_t>(j) * p.tok_pad] = __float2bfloat16(v[g * 8 + j]);
+                  for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack_bf16x2(w4[e]);
+                    v[q * 8 + e * 2] += f.x;
+                    v[q * 8 + e * 2 + 1] += f.y;
+                  }
+                }
+              }
+              if (p.res1 && row_ok) {
+                const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(m) * p.ld_res1 + col);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const uint4 u = rp[q];
+                  const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack_bf16x2(w4[e]);
+                    v[q * 8 + e * 2] += f.x;
+                    v[q * 8 + e * 2 + 1] += f.y;
+                  }
+                }
+              }
+              if (staged) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  st_shared_16(stg_u32 + lane * kStgRow + q * 16,
+                               make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                          pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+                __syncwarp();
+                __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + p.col_off + col;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const int idx = lane + 32 * q, rr = idx >> 2, ch = idx & 3;
+                  if (m_warp + rr < p.M)
+                    *reinterpret_cast<uint4*>(obase + static_cast<size_t>(m_warp + rr) * p.ldo + ch * 8) =
+                        ld_shared_16(stg_u32 + rr * kStgRow + ch * 16);
+                }
+                __syncwarp();
+              } else if (!row_ok) {
+                // nothing to store for padding rows
+              } else if (p.out_mode == kOutNchwF32) {
+                // lanes hold consecutive pixels: each channel plane gets a coalesced 128-byte store
+                const int pix = m - img * p.rows_per_img;
+                float* dst = reinterpret_cast<float*>(p.out) + static_cast<size_t>(img) * p.n_store * p.rows_per_img + pix;
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (col + j < p.n_store) dst[static_cast<size_t>(col + j) * p.rows_per_img] = v[j];
+              } else if (p.out_mode == kOutF32) {
+                float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) +
+                                                        static_cast<size_t>(m) * p.ldo + p.col_off + col);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+              } else {  // kOutQkv
+                const int tok = m - img * p.rows_per_img;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                  const int cg = col + g * 8;
+                  const int sect = cg / p.inner + p.qkv_first;  // 0 q, 1 k, 2 v
+                  const int cc = cg % p.inner;
+                  const int head = cc / p.dhead;
+                  const int e = cc - head * p.dhead;
+                  if (sect < 2) {
+                    __nv_bfloat16* base = (sect == 0) ? p.q_out : p.k_out;
+                    uint4* dst = reinterpret_cast<uint4*>(
+                        base + ((static_cast<size_t>(img) * p.heads + head) * p.rows_per_img + tok) * p.dhead + e);
+                    *dst = make_uint4(pack_bf16x2(v[g * 8], v[g * 8 + 1]), pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]),
+                                      pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]));
+                  } else {
+                    __nv_bfloat16* dst =
+                        p.vt_out + ((static_cast<size_t>(img) * p.heads + head) * p.dhead + e) * p.tok_pad + tok;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) dst[static_cast<size_t>(j) * p.tok_pad] = __float2bfloat16(v[g * 8 + j]);
+                  }
+                }
               }
             }
           }
@@ -448,8 +508,8 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   p.M = p.NB * p.H * p.W;
   int BN = bn_hint;
   if (p.out_mode == kOutGeglu) {
-    BN = 128;
-    if (p.N % 128 != 0) { set_error("gemm: GEGLU needs N %% 128 == 0 (N=%d)", p.N); return -1; }
+    BN = 256;
+    if (p.N % 256 != 0) { set_error("gemm: GEGLU needs N %% 256 == 0 (N=%d)", p.N); return -1; }
   } else if (BN == 0) {
     if (p.N % 256 == 0) BN = 256;
     else if (p.N % 160 == 0) BN = 160;

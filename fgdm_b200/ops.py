@@ -299,12 +299,12 @@ def pack_conv_weight(w: torch.Tensor) -> torch.Tensor:
 
 def pack_geglu(w: torch.Tensor, b: torch.Tensor):
     """GEGLU proj [2*inner, dim] (value rows then gate rows, attention.py:40-44) -> rows interleaved
-    per 128-column tile (64 value rows, then the matching 64 gate rows); bias likewise."""
+    per 256-column tile (128 value rows, then the matching 128 gate rows); bias likewise."""
     inner = w.shape[0] // 2
-    assert inner % 64 == 0, "GEGLU inner dim must be a multiple of 64"
-    wx, wg = w[:inner].reshape(inner // 64, 64, -1), w[inner:].reshape(inner // 64, 64, -1)
+    assert inner % 128 == 0, "GEGLU inner dim must be a multiple of 128"
+    wx, wg = w[:inner].reshape(inner // 128, 128, -1), w[inner:].reshape(inner // 128, 128, -1)
     wi = torch.cat([wx, wg], dim=1).reshape(2 * inner, -1)
-    bx, bg = b[:inner].reshape(inner // 64, 64), b[inner:].reshape(inner // 64, 64)
+    bx, bg = b[:inner].reshape(inner // 128, 128), b[inner:].reshape(inner // 128, 128)
     bi = torch.cat([bx, bg], dim=1).reshape(2 * inner)
     return wi.contiguous().to(bf16), bi.contiguous().float()
 

@@ -39,7 +39,7 @@ int fgdm_device_check(void);
 /* Output layout of fgdm_conv_gemm */
 enum {
   FGDM_OUT_BF16 = 0,   /* out[m, col_off + n] bf16, row stride ldo */
-  FGDM_OUT_GEGLU = 1,  /* weights row-interleaved per 128 (64 value rows, 64 gate rows): out = x * gelu(gate) */
+  FGDM_OUT_GEGLU = 1,  /* weights row-interleaved per 256 (128 value rows, 128 gate rows): out = x * gelu(gate) */
   FGDM_OUT_QKV = 2,    /* q/k -> [img, head, tok, d]; v -> transposed [img, head, d, tok_pad] */
   FGDM_OUT_F32 = 3,    /* out[m, n] fp32 */
   FGDM_OUT_NCHW_F32 = 4 /* out[img, c, pix] fp32 for c < n_store: conv_out 320->4 (openaimodel.py:727), 128->3 (model.py:529) */
