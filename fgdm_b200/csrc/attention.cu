@@ -35,70 +35,95 @@ struct AttnParams {
   int ld_out;
 };
 
-static constexpr int kAttnSoftmaxWarps = 8;
-static constexpr int kAttnThreads = 32 * (kAttnSoftmaxWarps + 1);   // + one TMA / MMA-issue warp
+// QTN = 128-row query tiles per CTA (they share every K/V tile): 2 for self-attention (one CTA per SM, P double-
+// buffered), 1 for the 77-key text cross-attention (a single KV tile: two small CTAs per SM overlap each other's
+// prologue and epilogue instead). Warps: 8*QTN softmax, QTN MMA-issue (one per query tile), 1 TMA producer.
+template <int QTN> struct AttnWarps {
+  static constexpr int kSoftmax = 8 * QTN;
+  static constexpr int kIssue0 = kSoftmax;
+  static constexpr int kTma = kSoftmax + QTN;
+  static constexpr int kThreads = 32 * (kTma + 1);
+};
 static constexpr float kRescaleThreshold = 8.0f;   // log2 units: P <= 2^8 before a row's reference max is refreshed
 
 // KA: 64-wide K-chunks of the head dim (Q/K tiles are KA swizzle atoms), DV: V^T rows of this CTA's tile (the
 // real V columns plus the all-ones row that makes the tensor core produce the softmax denominator),
-// BN: keys per tile (128, or 64 when the head dim is large so that two CTAs still fit on an SM).
-template <int KA, int DV, int BN>
+// BN: keys per tile (128, or 64 when the head dim is large).
+template <int KA, int DV, int BN, int QTN>
 struct AttnCfg {
-  static constexpr int kQBytes = KA * 128 * 128;       // KA atoms of [128 rows x 128 B]
+  static constexpr int kAttnQTiles = QTN;
+  static constexpr int kQBytes = KA * 128 * 128;       // per query tile: KA atoms of [128 rows x 128 B]
   static constexpr int kKBytes = KA * BN * 128;        // KA atoms of [BN rows x 128 B]
   static constexpr int kVAtom = DV * 128;              // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kVBytes = (BN / 64) * kVAtom;
   static constexpr int kPBytes = (BN / 64) * 128 * 128;
-  static constexpr int kSmemBytes = kQBytes + 2 * (kKBytes + kVBytes) + kPBytes + 1024 /*align*/ + 2048 /*row max*/ + 128;
-  static constexpr int kTmemCols = (BN + DV <= 128) ? 128 : 256;
+  static constexpr int kFixed = kAttnQTiles * kQBytes + 2 * (kKBytes + kVBytes);
+  static constexpr int kMisc = 1024 /*align*/ + kAttnQTiles * 2048 /*row max*/ + 256 /*barriers*/;
+  // P double-buffered per query tile when it fits: the softmax of tile j+1 never waits for PV(j)
+  static constexpr int kPBufs = (QTN == 2 && kFixed + kAttnQTiles * 2 * kPBytes + kMisc <= 227 * 1024) ? 2 : 1;
+  static constexpr int kSmemBytes = kFixed + kAttnQTiles * kPBufs * kPBytes + kMisc;
+  static constexpr int kTmemStride = 256;              // TMEM columns per query tile: S at +0, O at +BN
+  static constexpr int kTmemCols = 256 * QTN;
+  static constexpr int kMinBlocks = (QTN == 1 && kSmemBytes <= 110 * 1024) ? 2 : 1;
 };
 
 FGDM_DEVINL void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
-// Warp-specialised: 8 softmax warps + 1 TMA/MMA-issue warp, no CTA-wide barrier inside the KV loop.
-// TWO threads per query row (softmax warps w and w+4 own the same 32 TMEM lanes and split the tile's key columns),
-// so each SM sub-partition has 4 softmax warps (2 resident CTAs) to hide MUFU / TMEM latency behind.
+// One CTA per SM, warp-specialised: 16 softmax warps (two 128-row query tiles) + 1 TMA/MMA-issue warp; no CTA-wide
+// barrier inside the KV loop. TWO threads per query row (softmax warps w and w+4 of a tile own the same 32 TMEM lanes
+// and split the key columns), so each SM sub-partition has 4 softmax warps to hide MUFU / TMEM latency behind, and the
+// two query tiles drift apart naturally so that one tile's exp phase covers the other's TMEM/MMA waits.
 //   softmax thread, tile j:  wait S(j) | tcgen05.ld its half of the S row | arrive s_free | half-row max, exchanged
-//       with the partner warp (64-thread named barrier) | wait PV(j-1) | lazy refresh of the row's reference max
-//       (then rescale the O row in TMEM: rare) | exp2 -> bf16 P tile in swizzled smem | arrive p_ready
+//       with the partner warp (64-thread named barrier) | lazy refresh of the row's reference max (then wait PV(j-1)
+//       and rescale the O row in TMEM: rare) | exp2 -> bf16 P(j) in swizzled smem buffer j&1 | observe PV(j-1) |
+//       arrive p_ready
 //   issue warp, tile j:      wait s_free(j) -> issue S(j+1) (overlaps the softmax of tile j) |
 //       wait p_ready(j), V(j) -> write the ones-row of V(j) -> issue PV(j) | prefetch K(j+2), V(j+1) by TMA
 // The softmax denominator is NOT accumulated on the CUDA cores: V^T row `dv_real` of every tile is overwritten with
 // 1.0, so O[:, dv_real] = sum_j P[:, j] comes out of the PV tensor-core product (from the same bf16-rounded P as
 // the numerator) and is rescaled together with O.
-template <int KA, int DV, int BN>
-__global__ void __launch_bounds__(kAttnThreads, 2)
+template <int KA, int DV, int BN, int QTN>
+__global__ void __launch_bounds__(AttnWarps<QTN>::kThreads, AttnCfg<KA, DV, BN, QTN>::kMinBlocks)
 attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
-  using Cfg = AttnCfg<KA, DV, BN>;
+  using Cfg = AttnCfg<KA, DV, BN, QTN>;
+  constexpr int kAttnSoftmaxWarps = AttnWarps<QTN>::kSoftmax;
+  constexpr int kAttnIssueWarp0 = AttnWarps<QTN>::kIssue0;
+  constexpr int kAttnTmaWarp = AttnWarps<QTN>::kTma;
+  (void)kAttnSoftmaxWarps;
   constexpr int kPA = BN / 64;                          // key-atoms per tile
   constexpr int HB = BN / 2;                            // S columns per thread
   constexpr int HV = DV / 2;                            // O columns per thread
+  constexpr int PB = Cfg::kPBufs;
+  constexpr int QT = QTN;
   static_assert(DV % 16 == 0 && HV % 8 == 0, "DV must be a multiple of 16");
+  static_assert(BN + DV <= Cfg::kTmemStride, "TMEM budget");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + Cfg::kQBytes;                  // 2 stages
+  uint8_t* sQ = smem;                               // [QT]
+  uint8_t* sK = sQ + QT * Cfg::kQBytes;             // 2 stages
   uint8_t* sV = sK + 2 * Cfg::kKBytes;              // 2 stages
-  uint8_t* sP = sV + 2 * Cfg::kVBytes;
-  float* sMax = reinterpret_cast<float*>(sP + Cfg::kPBytes);   // [2 parities][2 halves][128 rows]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + 512);
+  uint8_t* sP = sV + 2 * Cfg::kVBytes;              // [QT][PB]
+  float* sMax = reinterpret_cast<float*>(sP + QT * PB * Cfg::kPBytes);   // [QT][2 parities][2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + QT * 512);
   uint64_t* bar_q = bars;
-  uint64_t* bar_k = bars + 1;   // [2]
-  uint64_t* bar_v = bars + 3;   // [2]
-  uint64_t* bar_s = bars + 5;   // S(j) complete            (tcgen05.commit)
-  uint64_t* bar_o = bars + 6;   // PV(j) complete           (tcgen05.commit)
-  uint64_t* bar_sfree = bars + 7;   // S(j) is in registers everywhere (8 warp arrivals)
-  uint64_t* bar_pready = bars + 8;  // P(j) is in smem               (8 warp arrivals)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* bar_k = bars + 1;        // [2]
+  uint64_t* bar_v = bars + 3;        // [2]
+  uint64_t* bar_s = bars + 5;        // [QT] S(j) complete            (tcgen05.commit)
+  uint64_t* bar_o = bars + 7;        // [QT] PV(j) complete           (tcgen05.commit)
+  uint64_t* bar_sfree = bars + 9;    // [QT] S(j) is in registers everywhere (8 warp arrivals)
+  uint64_t* bar_pready = bars + 11;  // [QT] P(j) is in smem               (8 warp arrivals)
+  uint64_t* k_empty = bars + 13;     // [2] both tiles' S(j) have read K stage j&1   (2 tcgen05.commit arrivals)
+  uint64_t* v_empty = bars + 15;     // [2] both tiles' PV(j) have read V stage j&1  (2 tcgen05.commit arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
   const int lane = tid & 31;
-  const int q0 = blockIdx.x * 128;
+  const int q0 = blockIdx.x * (128 * QT);
   const int bh = blockIdx.y;
   const int v0 = blockIdx.z * p.dv_per;             // first V column of this CTA
   const int num_kv = (p.Nk + BN - 1) / BN;
@@ -108,17 +133,21 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     tma_prefetch_desc(&map_k);
     tma_prefetch_desc(&map_vt);
     mbar_init(bar_q, 1);
-    mbar_init(&bar_k[0], 1);
-    mbar_init(&bar_k[1], 1);
-    mbar_init(&bar_v[0], 1);
-    mbar_init(&bar_v[1], 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
-    mbar_init(bar_sfree, kAttnSoftmaxWarps);
-    mbar_init(bar_pready, kAttnSoftmaxWarps);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_k[i], 1);
+      mbar_init(&bar_v[i], 1);
+      mbar_init(&k_empty[i], QT);
+      mbar_init(&v_empty[i], QT);
+    }
+    for (int t = 0; t < QT; ++t) {
+      mbar_init(&bar_s[t], 1);
+      mbar_init(&bar_o[t], 1);
+      mbar_init(&bar_sfree[t], 8);
+      mbar_init(&bar_pready[t], 8);
+    }
     fence_barrier_init();
   }
-  if (warp == kAttnSoftmaxWarps) {
+  if (warp == kAttnTmaWarp) {
     tmem_alloc(tmem_ptr, Cfg::kTmemCols);
     tmem_relinquish();
   }
@@ -126,82 +155,85 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
-  const uint32_t tmem_s = tmem_base;
-  const uint32_t tmem_o = tmem_base + BN;
 
-  if (warp == kAttnSoftmaxWarps) {
-    // ===================== TMA + MMA issue warp =====================
-    auto load_k = [&](int j) {
-      const int st = j & 1;
-      mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
+  if (warp == kAttnTmaWarp) {
+    // ===================== TMA producer warp: Q once, then a 2-stage K ring and a 2-stage V ring =====================
+    if (lane == 0) {
+      auto load_k = [&](int j) {
+        const int st = j & 1;
+        mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
 #pragma unroll
-      for (int a = 0; a < KA; ++a)
-        tma_load_3d(sK + st * Cfg::kKBytes + a * (BN * 128), &map_k, &bar_k[st], a * 64, j * BN, bh);
-    };
-    auto load_v = [&](int j) {
-      const int st = j & 1;
-      mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
+        for (int a = 0; a < KA; ++a)
+          tma_load_3d(sK + st * Cfg::kKBytes + a * (BN * 128), &map_k, &bar_k[st], a * 64, j * BN, bh);
+      };
+      auto load_v = [&](int j) {
+        const int st = j & 1;
+        mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
 #pragma unroll
-      for (int a = 0; a < kPA; ++a)
-        tma_load_3d(sV + st * Cfg::kVBytes + a * Cfg::kVAtom, &map_vt, &bar_v[st], j * BN + a * 64, v0, bh);
-    };
+        for (int a = 0; a < kPA; ++a)
+          tma_load_3d(sV + st * Cfg::kVBytes + a * Cfg::kVAtom, &map_vt, &bar_v[st], j * BN + a * 64, v0, bh);
+      };
+      mbar_expect_tx(bar_q, QT * Cfg::kQBytes);
+#pragma unroll
+      for (int t = 0; t < QT; ++t)
+#pragma unroll
+        for (int a = 0; a < KA; ++a)
+          tma_load_3d(sQ + t * Cfg::kQBytes + a * 16384, &map_q, bar_q, a * 64, q0 + t * 128, bh);
+      for (int j = 0; j < num_kv; ++j) {
+        if (j >= 2) mbar_wait(&k_empty[j & 1], ((j - 2) >> 1) & 1);
+        load_k(j);
+        if (j >= 2) mbar_wait(&v_empty[j & 1], ((j - 2) >> 1) & 1);
+        load_v(j);
+      }
+    }
+  } else if (warp >= kAttnIssueWarp0) {
+    // ===================== MMA issue warp of query tile t =====================
+    const int t = warp - kAttnIssueWarp0;
     auto issue_s = [&](int j) {
       const int st = j & 1;
       constexpr uint32_t idesc = make_idesc_bf16(128, BN);
 #pragma unroll
       for (int a = 0; a < KA; ++a) {
-        const uint64_t dq = make_desc_sw128(smem_u32(sQ + a * 16384));
+        const uint64_t dq = make_desc_sw128(smem_u32(sQ + t * Cfg::kQBytes + a * 16384));
         const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes + a * (BN * 128)));
 #pragma unroll
-        for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem_s, dq + 2 * k, dk + 2 * k, idesc, (a | k) != 0 ? 1u : 0u);
+        for (int k = 0; k < 4; ++k)
+          tc_mma_bf16(tmem_base + t * Cfg::kTmemStride, dq + 2 * k, dk + 2 * k, idesc, (a | k) != 0 ? 1u : 0u);
       }
-      tc_commit(bar_s);
+      tc_commit(&bar_s[t]);
+      tc_commit(&k_empty[st]);
     };
     auto issue_pv = [&](int j) {
       const int st = j & 1;
       constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
+      const uint8_t* pbuf = sP + (t * PB + (PB == 2 ? (j & 1) : 0)) * Cfg::kPBytes;
 #pragma unroll
       for (int ks = 0; ks < BN / 16; ++ks) {
-        const uint64_t dp = make_desc_sw128(smem_u32(sP + (ks >> 2) * 16384)) + 2 * (ks & 3);
+        const uint64_t dp = make_desc_sw128(smem_u32(pbuf + (ks >> 2) * 16384)) + 2 * (ks & 3);
         const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes + (ks >> 2) * Cfg::kVAtom)) + 2 * (ks & 3);
-        tc_mma_bf16(tmem_o, dp, dv, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+        tc_mma_bf16(tmem_base + t * Cfg::kTmemStride + BN, dp, dv, idesc_pv, (j | ks) != 0 ? 1u : 0u);
       }
-      tc_commit(bar_o);
+      tc_commit(&bar_o[t]);
+      tc_commit(&v_empty[st]);
     };
 
     if (lane == 0) {
-      mbar_expect_tx(bar_q, Cfg::kQBytes);
-#pragma unroll
-      for (int a = 0; a < KA; ++a) tma_load_3d(sQ + a * 16384, &map_q, bar_q, a * 64, q0, bh);
-      load_k(0);
-      load_v(0);
-      if (num_kv > 1) {
-        load_k(1);
-        load_v(1);
-      }
       mbar_wait(bar_q, 0);
       mbar_wait(&bar_k[0], 0);
       tc_fence_after();
       issue_s(0);
     }
     for (int j = 0; j < num_kv; ++j) {
-      if (lane == 0) {
-        if (j + 1 < num_kv) {
-          mbar_wait(bar_sfree, j & 1);                   // S(j) is in registers: its TMEM columns and K stage are free
-          tc_fence_after();
-          if (j + 2 < num_kv) load_k(j + 2);
-          mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
-          tc_fence_after();
-          issue_s(j + 1);                                // overlaps the softmax of tile j
-        }
-        if (j >= 1 && j + 1 < num_kv) {
-          mbar_wait(bar_o, (j - 1) & 1);                 // PV(j-1) done: V stage (j+1)&1 is free
-          load_v(j + 1);
-        }
+      if (lane == 0 && j + 1 < num_kv) {
+        mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
+        mbar_wait(&bar_sfree[t], j & 1);               // S(j) is in registers: its TMEM columns are free
+        tc_fence_after();
+        issue_s(j + 1);                                // overlaps the softmax of tile j
       }
       __syncwarp();
       mbar_wait(&bar_v[j & 1], (j >> 1) & 1);
-      // ones-row: V^T row dv_real of every key-atom := 1.0 (a full 128-byte swizzle row, so the swizzle is moot)
+      // ones-row: V^T row dv_real of every key-atom := 1.0 (a full 128-byte swizzle row, so the swizzle is moot).
+      // Both issue warps write the same bytes; whichever comes second rewrites identical values.
       if (lane < kPA * 8) {
         const uint32_t a = smem_u32(sV + (j & 1) * Cfg::kVBytes + (lane >> 3) * Cfg::kVAtom) + p.dv_real * 128 + (lane & 7) * 16;
         st_shared_16(a, make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u));
@@ -209,7 +241,7 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        mbar_wait(bar_pready, j & 1);
+        mbar_wait(&bar_pready[t], j & 1);
         tc_fence_after();
         issue_pv(j);
       }
@@ -217,17 +249,21 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     }
   } else {
     // ===================== softmax warps =====================
-    const int half = warp >> 2;                       // which half of the S / O columns this thread owns
-    const int row = tid & 127;                        // query row within the tile == TMEM lane
+    const int t = warp >> 3;                          // query tile
+    const int half = (warp >> 2) & 1;                 // which half of the S / O columns this thread owns
+    const int row = (warp & 3) * 32 + lane;           // query row within the tile == TMEM lane
     const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t s_addr = tmem_s + lane_addr + half * HB;
-    const uint32_t o_addr = tmem_o + lane_addr + half * HV;
-    const int pair_bar = 1 + (warp & 3);
+    const uint32_t s_addr = tmem_base + t * Cfg::kTmemStride + lane_addr + half * HB;
+    const uint32_t o_base = tmem_base + t * Cfg::kTmemStride + BN + lane_addr;
+    const uint32_t o_addr = o_base + half * HV;
+    const int pair_bar = 1 + t * 4 + (warp & 3);
+    uint64_t* my_bar_o = &bar_o[t];
+    float* my_max = sMax + t * 512;
     float m_ref = -INFINITY;                            // reference max (scaled, log2 domain) used for exp2
 
     for (int j = 0; j < num_kv; ++j) {
       const int valid = p.Nk - j * BN - half * HB;       // keys valid in this thread's half tile (may exceed HB)
-      mbar_wait(bar_s, j & 1);
+      mbar_wait(&bar_s[t], j & 1);
       tc_fence_after();
 
       // ---- this thread's half of the S row -> registers, half-row maximum ----
@@ -237,7 +273,7 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_sfree);
+      if (lane == 0) mbar_arrive(&bar_sfree[t]);
       float hmax;
       {
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -261,14 +297,14 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
         }
         hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       }
-      float* mx_buf = sMax + (j & 1) * 256;
+      float* mx_buf = my_max + (j & 1) * 256;
       mx_buf[half * 128 + row] = hmax;
       named_bar_sync(pair_bar, 64);                      // the two warps that share these 32 rows
       const float tmax = fmaxf(hmax, mx_buf[(half ^ 1) * 128 + row]) * p.scale_log2;
 
-      // ---- PV(j-1) must have drained before O is touched or the P tile is overwritten ----
-      if (j > 0) {
-        mbar_wait(bar_o, (j - 1) & 1);
+      // ---- single P buffer: PV(j-1) must have drained before the P tile is overwritten ----
+      if (PB == 1 && j > 0) {
+        mbar_wait(my_bar_o, (j - 1) & 1);
         tc_fence_after();
       }
 
@@ -279,6 +315,10 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
         const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
         m_ref = m_new;
         if (j > 0) {
+          if (PB == 2) {                                  // O may only be touched once PV(j-1) has drained
+            mbar_wait(my_bar_o, (j - 1) & 1);
+            tc_fence_after();
+          }
 #pragma unroll
           for (int c = 0; c < HV; c += 8) {
             uint32_t r[8];
@@ -294,7 +334,7 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 
       // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major) ----
       const float neg_m = -m_ref;
-      const uint32_t sP_row = smem_u32(sP) + row * 128;
+      const uint32_t sP_row = smem_u32(sP + (t * PB + (PB == 2 ? (j & 1) : 0)) * Cfg::kPBytes) + row * 128;
       auto emit = [&](auto masked) {
 #pragma unroll
         for (int c = 0; c < HB; c += 8) {
@@ -317,19 +357,22 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
       if (valid >= HB) emit(std::false_type{}); else emit(std::true_type{});
 
       fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+      // Observe PV(j-1) BEFORE enabling PV(j): every bar_o phase is seen in order (no parity aliasing), and it makes
+      // buffer (j+1)&1 provably free for the next tile. PV(j-1) was issued a whole exp phase ago: this never stalls.
+      if (PB == 2 && j > 0) mbar_wait(my_bar_o, (j - 1) & 1);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_pready);
+      if (lane == 0) mbar_arrive(&bar_pready[t]);
     }
 
     // ---- normalise and store: out[img, q, head*d + v0 + e]; the denominator is O column dv_real ----
-    mbar_wait(bar_o, (num_kv - 1) & 1);
+    mbar_wait(my_bar_o, (num_kv - 1) & 1);
     tc_fence_after();
-    const int q = q0 + row;
+    const int q = q0 + t * 128 + row;
     float inv;
     {
       uint32_t r1;
-      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1) : "r"(tmem_o + lane_addr + p.dv_real) : "memory");
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1) : "r"(o_base + p.dv_real) : "memory");
       tmem_ld_wait();
       inv = 1.0f / __uint_as_float(r1);
     }
@@ -354,19 +397,19 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
-  if (warp == kAttnSoftmaxWarps) {
+  if (warp == kAttnTmaWarp) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
-template <int KA, int DV, int BN>
-static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
-                       int nsplit, cudaStream_t stream) {
-  using Cfg = AttnCfg<KA, DV, BN>;
+template <int KA, int DV, int BN, int QTN>
+static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
+                         int nsplit, cudaStream_t stream) {
+  using Cfg = AttnCfg<KA, DV, BN, QTN>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention_kernel<KA, DV, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(attention_kernel<KA, DV, BN, QTN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("attention: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -374,9 +417,17 @@ static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUten
     }
     configured = true;
   }
-  dim3 grid((p.Nq + 127) / 128, p.BH, nsplit);
-  attention_kernel<KA, DV, BN><<<grid, kAttnThreads, Cfg::kSmemBytes, stream>>>(mq, mk, mv, p);
+  dim3 grid((p.Nq + 128 * QTN - 1) / (128 * QTN), p.BH, nsplit);
+  attention_kernel<KA, DV, BN, QTN><<<grid, AttnWarps<QTN>::kThreads, Cfg::kSmemBytes, stream>>>(mq, mk, mv, p);
   return check_launch("attention_kernel");
+}
+
+template <int KA, int DV, int BN>
+static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
+                       int nsplit, cudaStream_t stream) {
+  // short KV (text cross-attention) or a single query tile: the one-tile CTA; otherwise two query tiles per CTA
+  if (p.Nk <= 2 * BN || p.Nq <= 128) return launch_attn_q<KA, DV, BN, 1>(mq, mk, mv, p, nsplit, stream);
+  return launch_attn_q<KA, DV, BN, 2>(mq, mk, mv, p, nsplit, stream);
 }
 
 // q: [images, heads, Nq, d], k: [images, heads, Nk, d], vt: [images, heads, d, tok_pad] (keys contiguous),
