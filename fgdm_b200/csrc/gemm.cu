@@ -23,6 +23,7 @@
 //    the attention kernel.
 #include "gemm.cuh"
 #include <stdio.h>
+#include <stdlib.h>
 
 namespace fgdm {
 
@@ -47,6 +48,44 @@ struct GemmCfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kStgBytes + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+// Work iterator shared by the three warp roles: classic mode hands out whole tiles round-robin; range mode walks this
+// CTA's contiguous slice of the (tile, K-chunk) space segment by segment.
+struct WorkIter {
+  int range, num_tiles, num_k, T, cur, end;
+  FGDM_DEVINL WorkIter(const GemmParams& p, int num_tiles_, int num_k_) {
+    range = p.range_ctas; num_tiles = num_tiles_; num_k = num_k_; T = num_tiles_ * num_k_;
+    if (range) {
+      cur = static_cast<int>(static_cast<long long>(blockIdx.x) * T / range);
+      end = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * T / range);
+    } else {
+      cur = blockIdx.x; end = num_tiles_;
+    }
+  }
+  FGDM_DEVINL bool next(int& tile, int& kb, int& ke) {
+    if (cur >= end) return false;
+    if (range) {
+      tile = cur / num_k;
+      kb = cur - tile * num_k;
+      ke = min(num_k, kb + (end - cur));
+      cur += ke - kb;
+    } else {
+      tile = cur; kb = 0; ke = num_k;
+      cur += gridDim.x;
+    }
+    return true;
+  }
+  FGDM_DEVINL int range_begin(int cta) const { return static_cast<int>(static_cast<long long>(cta) * T / range); }
+  FGDM_DEVINL int owner(int c) const {     // the CTA whose range contains chunk index c
+    int i = static_cast<int>(static_cast<long long>(c) * range / T);
+    while (range_begin(i + 1) <= c) ++i;
+    while (range_begin(i) > c) --i;
+    return i;
+  }
+};
+
+// the 8 epilogue warps only (barrier 0 is the CTA-wide one used at start-up and tear-down)
+FGDM_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
+
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
@@ -65,6 +104,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   uint64_t* acc_full = bars + 2 * kStages;
   uint64_t* acc_empty = bars + 2 * kStages + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  volatile uint32_t* split_flag = tmem_ptr + 1;    // epilogue warps: "this CTA finishes the tile"
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -102,7 +142,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      WorkIter it(p, num_tiles, num_k);
+      int tile, kc_begin, kc_end;
+      while (it.next(tile, kc_begin, kc_end)) {
         const int m_tile = tile / p.num_n_tiles;
         const int n_tile = tile - m_tile * p.num_n_tiles;
         const int m0 = m_tile * kBM;
@@ -110,7 +152,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         const int hw = m0 / p.W;
         const int h0 = hw % p.H;
         const int n0 = hw / p.H;
-        for (int kc = 0; kc < num_k; ++kc) {
+        for (int kc = kc_begin; kc < kc_end; ++kc) {
           const int tap = kc / chunks_per_tap;
           const int c = (kc - tap * chunks_per_tap) * kBK;
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -141,11 +183,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      WorkIter it(p, num_tiles, num_k);
+      int tile, kc_begin, kc_end;
+      while (it.next(tile, kc_begin, kc_end)) {
         mbar_wait(&acc_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * Cfg::kAccStride;
-        for (int kc = 0; kc < num_k; ++kc) {
+        for (int kc = kc_begin; kc < kc_end; ++kc) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint64_t da = make_desc_sw128(smem_u32(smem_a + stage * Cfg::kABytes));
@@ -153,7 +197,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {
             // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in (addr>>4)
-            tc_mma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc | k) != 0 ? 1u : 0u);
+            tc_mma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
           }
           tc_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
           if (++stage == kStages) {
@@ -186,7 +230,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     const int np = (kPanels + 1 - half) / 2;                     // this warp's panels: c0 = half*32 + 64*i
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    WorkIter it(p, num_tiles, num_k);
+    int tile, kc_begin, kc_end;
+    bool first_seg = true;
+    while (it.next(tile, kc_begin, kc_end)) {
+      const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
+      const int my_slot = first_seg ? 0 : 1;
+      first_seg = false;
       const int m_tile = tile / p.num_n_tiles;
       const int n_tile = tile - m_tile * p.num_n_tiles;
       const int m_warp = m_tile * kBM + quarter * 32;   // first row of this warp
@@ -292,12 +342,79 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         mbar_wait(&acc_full[acc], acc_phase);
         tc_fence_after();
 
+        bool finish = true;
+        int c_first = 0, c_last = 0;
+        if (partial) {
+          // dump this segment's fp32 partial, take a ticket; only the last contributor of the tile goes on
+          c_first = it.owner(tile * num_k);
+          c_last = it.owner(tile * num_k + num_k - 1);
+          // scratch layout [tile][split][panel][q][row][4 floats]: for a fixed 16-byte column group q the 32 lanes of
+          // a warp (consecutive rows) touch 512 contiguous bytes, in the dump and in the ordered reduce alike
+          float4* ws = reinterpret_cast<float4*>(p.split_ws + (static_cast<size_t>(blockIdx.x) * 2 + my_slot) * (kBM * BN)) +
+                       quarter * 32 + lane;
 #pragma unroll 1
-        for (int i = 0; i < np; ++i) {
-          {
+          for (int i = 0; i < np; ++i) {
             uint32_t r[32];
             tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
+            tmem_ld_wait();
+            float4* dst = ws + static_cast<size_t>(half + 2 * i) * 8 * kBM;
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              dst[q * kBM] = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                         __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+          }
+          __threadfence();
+          epi_bar_sync();
+          if (ew == 0 && lane == 0) {
+            const unsigned int t = atomicAdd(&p.split_tickets[tile], 1u);
+            const bool last = t == static_cast<unsigned int>(c_last - c_first);
+            if (last) p.split_tickets[tile] = 0;             // ready for the next launch on this stream
+            *split_flag = last ? 1u : 0u;
+          }
+          epi_bar_sync();
+          finish = *split_flag != 0;
+          if (finish) __threadfence();
+        }
+
+#pragma unroll 1
+        for (int i = 0; finish && i < np; ++i) {
+          {
+            uint32_t r[32];
             const int col = n_tile * BN + half * 32 + 64 * i;
+            if (partial) {
+              // fixed contributor order (own partial included): bit-identical whichever CTA finishes last
+              float a32[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) a32[j] = 0.0f;
+              const size_t poff = static_cast<size_t>(half + 2 * i) * 8 * kBM + quarter * 32 + lane;
+              auto slot_ptr = [&](int cta) {
+                // a CTA's first segment lives in slot 0, a later one in slot 1
+                const int sl = (it.range_begin(cta) / num_k == tile) ? 0 : 1;
+                return reinterpret_cast<const float4*>(p.split_ws + (static_cast<size_t>(cta) * 2 + sl) * (kBM * BN)) + poff;
+              };
+              for (int cta = c_first; cta <= c_last; cta += 2) {   // two partials (16 x 16 B) in flight per thread
+                const bool two = cta + 1 <= c_last;
+                const float4* s4 = slot_ptr(cta);
+                const float4* t4 = slot_ptr(two ? cta + 1 : cta);
+                float4 f0[8], f1[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) f0[q] = __ldcg(s4 + q * kBM);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) f1[q] = two ? __ldcg(t4 + q * kBM) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                  a32[4 * q] += f0[q].x; a32[4 * q + 1] += f0[q].y; a32[4 * q + 2] += f0[q].z; a32[4 * q + 3] += f0[q].w;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                  a32[4 * q] += f1[q].x; a32[4 * q + 1] += f1[q].y; a32[4 * q + 2] += f1[q].z; a32[4 * q + 3] += f1[q].w;
+                }
+              }
+#pragma unroll
+              for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(a32[j]);
+            } else {
+              tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
+            }
             if (col >= p.N) { tmem_ld_wait(); continue; }    // warp-uniform
             {
               if (pre_res) {                                 // residual panel: coalesced registers -> smem
@@ -460,9 +577,34 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
     configured = true;
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
+  const int grid = p.range_ctas ? p.range_ctas : (tiles < num_sms() ? tiles : num_sms());
   gemm_tc_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ma0, ma1, mb, p);
   return check_launch("gemm_tc_kernel");
+}
+
+// split-K scratch owned by the library: allocated on first use (the eager warm-up pass, never inside a graph capture)
+static constexpr size_t kSplitWsBytes = static_cast<size_t>(2) * 160 * 128 * 256 * 4;   // 160 CTAs x 2 slots x (128 x 256) fp32 = 42 MB
+static constexpr int kSplitMaxTiles = 16384;
+static float* g_split_ws = nullptr;
+static unsigned int* g_split_tickets = nullptr;
+static bool split_buffers_ready() {
+  static int state = 0;   // 0 untried, 1 ready, -1 unavailable (then split-K is simply not used)
+  if (state == 0) {
+    const char* e = getenv("FGDM_SPLITK");
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (e && e[0] == '0') {
+      state = -1;
+    } else if (cudaMalloc(&g_split_ws, kSplitWsBytes) == cudaSuccess &&
+               cudaMalloc(&g_split_tickets, kSplitMaxTiles * sizeof(unsigned int)) == cudaSuccess &&
+               cudaMemset(g_split_tickets, 0, kSplitMaxTiles * sizeof(unsigned int)) == cudaSuccess) {
+      state = 1;
+    } else {
+      (void)cudaGetLastError();
+      state = -1;
+    }
+    (void)cs;
+  }
+  return state == 1;
 }
 
 // Box geometry of one 128-row A tile in the [NB, H, W, C] image view.
@@ -507,15 +649,57 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   }
   p.M = p.NB * p.H * p.W;
   int BN = bn_hint;
+  p.range_ctas = 0;
+  const int m_tiles = (p.M + kBM - 1) / kBM;
+  const int num_k_chunks = p.taps * ((p.C0 + p.C1) / kBK);
   if (p.out_mode == kOutGeglu) {
     BN = 256;
     if (p.N % 256 != 0) { set_error("gemm: GEGLU needs N %% 256 == 0 (N=%d)", p.N); return -1; }
   } else if (BN == 0) {
-    if (p.N % 256 == 0) BN = 256;
-    else if (p.N % 160 == 0) BN = 160;
-    else if (p.N % 128 == 0) BN = 128;
-    else if (p.N <= 64) BN = 64;
+    if (p.N % 32 == 0 && p.N >= 128 && (p.N % 256 == 0 || p.N % 160 == 0 || p.N % 128 == 0)) {
+      // Tile width and K partitioning by a wave model. Classic: rounds over the SMs x (K chunks per tile x measured
+      // time per chunk + per-tile fill/drain). Range mode (split-K when the tiles cannot fill the SMs, stream-K when
+      // they fill a round and a bit): (tiles x chunks / CTAs) x time per chunk + dump/ticket/ordered-reduce
+      // (measured ~10 us). Time per 64-deep chunk from the measured sustained rates of each tile width
+      // (256: ~1450, 160: ~1050, 128: ~900 TFLOP/s chip-wide).
+      static const int kBn[3] = {256, 160, 128};
+      static const float kChunkNs[3] = {428.f, 369.f, 345.f};
+      float best = 1e30f;
+      const int sms = num_sms();
+      const bool can_range = p.out_mode == kOutBf16 && split_buffers_ready();
+      for (int c = 0; c < 3; ++c) {
+        if (p.N % kBn[c] != 0) continue;
+        const int tiles = m_tiles * (p.N / kBn[c]);
+        {
+          const int rounds = (tiles + sms - 1) / sms;
+          const float cost = rounds * (num_k_chunks * kChunkNs[c] + 1000.f);
+          if (cost < best) { best = cost; BN = kBn[c]; p.range_ctas = 0; }
+        }
+        if (!can_range || tiles > kSplitMaxTiles || num_k_chunks < 48) continue;
+        for (int g = 0; g < 4; ++g) {
+          // candidates: split-K by 2, 3, 4 (tiles * S <= SMs) or one range per SM
+          const int ctas = g < 3 ? tiles * (g + 2) : sms;
+          if (ctas > sms || (g == 3 && (tiles <= sms || tiles > 2 * sms))) continue;
+          const float per_cta = static_cast<float>(tiles) * num_k_chunks / ctas;
+          if (per_cta < 24.f) continue;
+          const float cost = per_cta * kChunkNs[c] + 2000.f + 9000.f;
+          if (cost < best) { best = cost; BN = kBn[c]; p.range_ctas = ctas; }
+        }
+      }
+    } else if (p.N <= 64) BN = 64;
     else BN = 128;
+  }
+  {
+    static int force = -1;
+    if (force < 0) { const char* e = getenv("FGDM_RANGE_FORCE"); force = e ? atoi(e) : 0; }
+    if (force > 0 && p.out_mode == kOutBf16 && bn_hint == 0 && split_buffers_ready() && BN >= 128) p.range_ctas = force;
+    if (getenv("FGDM_GEMM_DEBUG"))
+      fprintf(stderr, "gemm M=%d N=%d chunks=%d -> BN=%d range_ctas=%d\n", p.M, p.N, num_k_chunks, BN, p.range_ctas);
+  }
+  if (p.range_ctas) {
+    if (static_cast<size_t>(p.range_ctas) * 2 * kBM * BN * 4 > kSplitWsBytes) { set_error("gemm: range scratch too small"); return -1; }
+    p.split_ws = g_split_ws;
+    p.split_tickets = g_split_tickets;
   }
   p.num_m_tiles = (p.M + kBM - 1) / kBM;
   p.num_n_tiles = (p.N + BN - 1) / BN;

@@ -50,6 +50,13 @@ struct GemmParams {
   int inner;            // heads * dhead
   int heads, dhead;
   int tok_pad;          // row stride of the transposed V (>= tokens per image, multiple of 8)
+  // K-range partitioning (split-K / stream-K) for layers whose output tiles do not fill the 148 SMs evenly: the
+  // tiles x K-chunks index space is cut into `range_ctas` equal contiguous ranges, one per CTA. A CTA whose range
+  // covers only part of a tile's K dumps its fp32 partial into its own scratch slot; the LAST contributor of a tile
+  // to finish (ticket) sums the partials in CTA order (bit-reproducible) and runs the epilogue. 0 = classic loop.
+  int range_ctas;
+  float* split_ws;              // [cta][2 slots: first / later segment][128 x BN] fp32, library-owned
+  unsigned int* split_tickets;  // [tile], zero between launches
 };
 
 }  // namespace fgdm

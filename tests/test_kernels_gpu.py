@@ -80,6 +80,24 @@ def test_conv3x3(nb, h, w, cin, cout):
     assert relerr(nchw(y), ref) < 1e-2
 
 
+@pytest.mark.parametrize("nb,h,w,cin,cout", [(16, 8, 8, 1280, 1280), (16, 16, 16, 640, 1280), (4, 8, 8, 2560, 1280),
+                                             (16, 16, 16, 1280, 1280), (20, 16, 16, 320, 640)])
+def test_conv3x3_split_k(nb, h, w, cin, cout):
+    """Small-M / deep-K layers (the UNet's 8x8 and 16x16 levels) take the split-K path: partial tiles are summed in
+    fixed split order by the last unit to finish, so results are correct AND bit-identical run to run."""
+    x = torch.randn(nb, cin, h, w, device=DEV)
+    wt = torch.randn(cout, cin, 3, 3, device=DEV) / math.sqrt(9 * cin)
+    b = torch.randn(cout, device=DEV)
+    res = torch.randn(nb, h, w, cout, device=DEV).to(torch.bfloat16)
+    xb, wp = nhwc(x), ops.pack_conv_weight(wt)
+    y = ops.conv_gemm(xb, wp, cout, conv=ops.CONV_3X3, bias=b, res0=res.view(-1, cout)).view(nb, h, w, cout)
+    ref = F.conv2d(nchw(xb), wt.to(torch.bfloat16).float(), b, padding=1) + nchw(res)
+    assert relerr(nchw(y), ref) < 1e-2
+    for _ in range(3):
+        y2 = ops.conv_gemm(xb, wp, cout, conv=ops.CONV_3X3, bias=b, res0=res.view(-1, cout)).view(nb, h, w, cout)
+        assert torch.equal(y, y2)
+
+
 def test_conv3x3_concat_and_temb():
     nb, h, w, c0, c1, cout = 2, 16, 16, 128, 64, 128
     x0 = torch.randn(nb, c0, h, w, device=DEV)

@@ -122,10 +122,10 @@ def test_controlldm_apply_model_vs_reference_golden(control):
     assert relmax(ctrl[0].float().permute(0, 3, 1, 2), g["ctrl0"]) < EPS_TOL
     # ctrl[12] is an INTERNAL bf16 tensor (deepest 2x2 map behind 8 bf16 ResBlock/transformer stages), not the
     # north_star's eps: its max-abs error is an extreme-value statistic that moves +-15 % with the summation order of
-    # any kernel, so it is held to 3e-2 on the max and 1e-2 on the RMS; eps itself stays at EPS_TOL above and below.
+    # any kernel, so it is held to 3e-2 on the max and EPS_TOL on the RMS; eps itself stays at EPS_TOL above and below.
     c12, g12 = ctrl[12].float().permute(0, 3, 1, 2), torch.as_tensor(g["ctrl12"]).to(DEV)
     assert relmax(c12, g["ctrl12"]) < 3e-2
-    assert float((c12 - g12).pow(2).mean().sqrt() / g12.pow(2).mean().sqrt()) < 1e-2
+    assert float((c12 - g12).pow(2).mean().sqrt() / g12.pow(2).mean().sqrt()) < EPS_TOL
     model.control_scales = list(gc.CONTROL_SCALES_VARIANT)
     try:
         assert relmax(model.apply_model(x, t, cond), g["eps_scaled"]) < EPS_TOL
