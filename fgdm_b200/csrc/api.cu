@@ -1,4 +1,5 @@
 // fgdm_b200 — C ABI (include/fgdm_b200.h): error plumbing, TMA descriptor encoding, thin wrappers.
+#include <stdlib.h>
 #include "../../include/fgdm_b200.h"
 #include "gemm.cuh"
 #include <cudaTypedefs.h>
@@ -26,6 +27,12 @@ int check_launch(const char* what) {
   }
   ++g_launches;
   return 0;
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("FGDM_PDL"); on = (e && e[0] == '1') ? 1 : 0; }   // measured: no gain under CUDA-graph replay, so off unless FGDM_PDL=1
+  return on == 1;
 }
 
 int num_sms() {

@@ -155,6 +155,8 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_launch_dependents();
 
   if (warp == kAttnTmaWarp) {
     // ===================== TMA producer warp: Q once, then a 2-stage K ring and a 2-stage V ring =====================
@@ -418,7 +420,9 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
     configured = true;
   }
   dim3 grid((p.Nq + 128 * QTN - 1) / (128 * QTN), p.BH, nsplit);
-  attention_kernel<KA, DV, BN, QTN><<<grid, AttnWarps<QTN>::kThreads, Cfg::kSmemBytes, stream>>>(mq, mk, mv, p);
+  cudaError_t e = launch_pdl(attention_kernel<KA, DV, BN, QTN>, grid, dim3(AttnWarps<QTN>::kThreads), Cfg::kSmemBytes, stream,
+                             mq, mk, mv, p);
+  if (e != cudaSuccess) { set_error("attention_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("attention_kernel");
 }
 

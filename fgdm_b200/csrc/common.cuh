@@ -20,6 +20,33 @@ static constexpr int kNumSMsDefault = 148;
 int num_sms();
 
 // ----------------------------------------------------------------------------------------------
+// Programmatic dependent launch: a kernel launched through launch_pdl() may start while its predecessor in the
+// stream is still draining; it runs its prologue (barrier init, TMEM allocation, descriptor prefetch), then
+// pdl_wait() blocks until the predecessor grid has completed and its memory is visible. EVERY kernel launched through
+// launch_pdl() must call pdl_wait() before its first global-memory access. pdl_launch_dependents() lets the successor
+// begin as soon as all CTAs of this grid are running. Captured by CUDA graphs as programmatic edges.
+// ----------------------------------------------------------------------------------------------
+FGDM_DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+FGDM_DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();   // api.cu: FGDM_PDL=0 disables (plain stream order)
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+// ----------------------------------------------------------------------------------------------
 // small utilities
 // ----------------------------------------------------------------------------------------------
 FGDM_DEVINL uint32_t smem_u32(const void* p) {

@@ -42,7 +42,7 @@ struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;                // 16 KB
   static constexpr int kBBytes = BN * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4;
+  static constexpr int kStages = (BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4;   // 224: 4 x 44 KB, 256: 4 x 48 KB
   static constexpr int kAccStride = (BN <= 64) ? 64 : (BN <= 128) ? 128 : 256;  // TMEM columns
   static constexpr int kTmemCols = 2 * kAccStride;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kStgBytes + 1024 /*align*/ + 256 /*barriers*/;
@@ -131,6 +131,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();                  // everything above overlapped the previous kernel's tail
+  pdl_launch_dependents();
 
   const int ctot = p.C0 + p.C1;
   const int chunks_per_tap = ctot / kBK;
@@ -578,7 +580,8 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = p.range_ctas ? p.range_ctas : (tiles < num_sms() ? tiles : num_sms());
-  gemm_tc_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ma0, ma1, mb, p);
+  cudaError_t e = launch_pdl(gemm_tc_kernel<BN>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, ma0, ma1, mb, p);
+  if (e != cudaSuccess) { set_error("gemm_tc_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("gemm_tc_kernel");
 }
 
@@ -656,20 +659,21 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     BN = 256;
     if (p.N % 256 != 0) { set_error("gemm: GEGLU needs N %% 256 == 0 (N=%d)", p.N); return -1; }
   } else if (BN == 0) {
-    if (p.N % 32 == 0 && p.N >= 128 && (p.N % 256 == 0 || p.N % 160 == 0 || p.N % 128 == 0)) {
+    if (p.N % 32 == 0 && p.N >= 128 && (p.N % 256 == 0 || p.N % 160 == 0 || p.N % 128 == 0 || p.N > 224)) {
       // Tile width and K partitioning by a wave model. Classic: rounds over the SMs x (K chunks per tile x measured
       // time per chunk + per-tile fill/drain). Range mode (split-K when the tiles cannot fill the SMs, stream-K when
       // they fill a round and a bit): (tiles x chunks / CTAs) x time per chunk + dump/ticket/ordered-reduce
       // (measured ~10 us). Time per 64-deep chunk from the measured sustained rates of each tile width
       // (256: ~1450, 160: ~1050, 128: ~900 TFLOP/s chip-wide).
-      static const int kBn[3] = {256, 160, 128};
-      static const float kChunkNs[3] = {428.f, 369.f, 345.f};
+      // 224 (7 panels) serves N = 640 as 3 tiles at 95 % fill: a 256-class tile instead of four 160-wide ones
+      static const int kBn[4] = {256, 224, 160, 128};
+      static const float kChunkNs[4] = {428.f, 385.f, 369.f, 345.f};
       float best = 1e30f;
       const int sms = num_sms();
       const bool can_range = p.out_mode == kOutBf16 && split_buffers_ready();
-      for (int c = 0; c < 3; ++c) {
-        if (p.N % kBn[c] != 0) continue;
-        const int tiles = m_tiles * (p.N / kBn[c]);
+      for (int c = 0; c < 4; ++c) {
+        if (p.N % kBn[c] != 0 && !(kBn[c] == 224 && p.N > 224)) continue;
+        const int tiles = m_tiles * ((p.N + kBn[c] - 1) / kBn[c]);
         {
           const int rounds = (tiles + sms - 1) / sms;
           const float cost = rounds * (num_k_chunks * kChunkNs[c] + 1000.f);
@@ -735,6 +739,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     case 64: return launch_bn<64>(ma0, ma1, mb, p, stream);
     case 128: return launch_bn<128>(ma0, ma1, mb, p, stream);
     case 160: return launch_bn<160>(ma0, ma1, mb, p, stream);
+    case 224: return launch_bn<224>(ma0, ma1, mb, p, stream);
     case 256: return launch_bn<256>(ma0, ma1, mb, p, stream);
     default: set_error("gemm: unsupported BN=%d", BN); return -1;
   }

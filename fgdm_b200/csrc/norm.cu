@@ -61,6 +61,8 @@ __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
                                 float2* partial, float2* __restrict__ stats, unsigned int* counters, float eps,
                                 GnGeom g) {
   extern __shared__ float sm[];  // [k][C] sums, then [k][C] sumsq
+  pdl_wait();
+  pdl_launch_dependents();
   const int C = g.C0 + g.C1;
   const int v = threadIdx.x % g.V;
   const int pl = threadIdx.x / g.V;
@@ -149,6 +151,8 @@ __global__ void gn_stats_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
 __global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __restrict__ x1,
                                 const float2* __restrict__ stats, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, __nv_bfloat16* __restrict__ y, int silu, GnGeom g) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int C = g.C0 + g.C1;
   const int cpg = C / g.G;
   const int img = blockIdx.y;
@@ -217,6 +221,8 @@ gn_slab_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __rest
                float eps, int silu, GnSlabGeom g) {
   extern __shared__ float sm[];            // [k][SC] sums, then [k][SC] sums of squares (SC = slab channels)
   __shared__ float s_mean[16], s_rstd[16];
+  pdl_wait();
+  pdl_launch_dependents();
   const int C = g.C0 + g.C1;
   const int SC = g.SV * 8;
   const int sv = threadIdx.x % g.SV;
@@ -340,9 +346,9 @@ static int try_groupnorm_slab(const void* x0, const void* x1, void* y, const flo
   const __nv_bfloat16* a0 = reinterpret_cast<const __nv_bfloat16*>(x0);
   const __nv_bfloat16* a1 = reinterpret_cast<const __nv_bfloat16*>(x1);
   __nv_bfloat16* yo = reinterpret_cast<__nv_bfloat16*>(y);
-  if (R <= 4) gn_slab_kernel<4><<<grid, threads, smem, stream>>>(a0, a1, gamma, beta, yo, eps, silu, g);
-  else if (R <= 8) gn_slab_kernel<8><<<grid, threads, smem, stream>>>(a0, a1, gamma, beta, yo, eps, silu, g);
-  else gn_slab_kernel<16><<<grid, threads, smem, stream>>>(a0, a1, gamma, beta, yo, eps, silu, g);
+  if (R <= 4) launch_pdl(gn_slab_kernel<4>, grid, dim3(threads), smem, stream, a0, a1, gamma, beta, yo, eps, silu, g);
+  else if (R <= 8) launch_pdl(gn_slab_kernel<8>, grid, dim3(threads), smem, stream, a0, a1, gamma, beta, yo, eps, silu, g);
+  else launch_pdl(gn_slab_kernel<16>, grid, dim3(threads), smem, stream, a0, a1, gamma, beta, yo, eps, silu, g);
   return check_launch("gn_slab_kernel") ? -1 : 1;
 }
 
@@ -371,13 +377,12 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
   if (NB > kGnMaxImages) { set_error("groupnorm: NB=%d > %d", NB, kGnMaxImages); return -1; }
   float2* partial = reinterpret_cast<float2*>(workspace);
   float2* stats = partial + static_cast<size_t>(NB) * kGnMaxChunks * G;
-  gn_stats_kernel<<<grid, g.threads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
-                                                     reinterpret_cast<const __nv_bfloat16*>(x1), partial, stats,
-                                                     counters, eps, g);
+  launch_pdl(gn_stats_kernel, grid, dim3(g.threads), smem, stream, reinterpret_cast<const __nv_bfloat16*>(x0),
+             reinterpret_cast<const __nv_bfloat16*>(x1), partial, stats, counters, eps, g);
   if (check_launch("gn_stats_kernel")) return -1;
-  gn_apply_kernel<<<grid, g.threads, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x0),
-                                                  reinterpret_cast<const __nv_bfloat16*>(x1),
-                                                  stats, gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), silu, g);
+  launch_pdl(gn_apply_kernel, grid, dim3(g.threads), 0, stream, reinterpret_cast<const __nv_bfloat16*>(x0),
+             reinterpret_cast<const __nv_bfloat16*>(x1), static_cast<const float2*>(stats), gamma, beta,
+             reinterpret_cast<__nv_bfloat16*>(y), silu, g);
   return check_launch("gn_apply_kernel");
 }
 
@@ -390,6 +395,8 @@ __global__ void layernorm_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloa
                                  float eps) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_launch_dependents();
   if (warp >= rows) return;
   const int V = C / 8;
   const __nv_bfloat16* xr = x + static_cast<size_t>(warp) * C;
@@ -455,9 +462,9 @@ int launch_layernorm(const void* x, void* y, const float* gamma, const float* be
   const int V = C / 8;
   const __nv_bfloat16* xi = reinterpret_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* yo = reinterpret_cast<__nv_bfloat16*>(y);
-  if (V <= 64) layernorm_kernel<2><<<blocks, threads, 0, stream>>>(xi, yo, gamma, beta, rows, C, eps);
-  else if (V <= 160) layernorm_kernel<5><<<blocks, threads, 0, stream>>>(xi, yo, gamma, beta, rows, C, eps);
-  else layernorm_kernel<8><<<blocks, threads, 0, stream>>>(xi, yo, gamma, beta, rows, C, eps);
+  if (V <= 64) launch_pdl(layernorm_kernel<2>, dim3(blocks), dim3(threads), 0, stream, xi, yo, gamma, beta, rows, C, eps);
+  else if (V <= 160) launch_pdl(layernorm_kernel<5>, dim3(blocks), dim3(threads), 0, stream, xi, yo, gamma, beta, rows, C, eps);
+  else launch_pdl(layernorm_kernel<8>, dim3(blocks), dim3(threads), 0, stream, xi, yo, gamma, beta, rows, C, eps);
   return check_launch("layernorm_kernel");
 }
 

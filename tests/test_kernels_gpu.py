@@ -38,7 +38,8 @@ def _dev():
 
 
 @pytest.mark.parametrize("m,k,n,bn", [(128, 64, 64, 0), (256, 128, 128, 0), (1232, 768, 640, 0), (4096, 320, 320, 0),
-                                      (8192, 1280, 1280, 0), (512, 640, 2560, 128), (300, 192, 96, 0)])
+                                      (8192, 1280, 1280, 0), (512, 640, 2560, 128), (300, 192, 96, 0), (2048, 256, 640, 224),
+                                      (16384, 640, 640, 0), (1000, 128, 320, 224)])
 def test_linear(m, k, n, bn):
     x = torch.randn(m, k, device=DEV)
     w = torch.randn(n, k, device=DEV) / math.sqrt(k)
