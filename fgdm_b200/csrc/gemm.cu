@@ -37,12 +37,15 @@ static constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 static constexpr int kStgRow = 80;                       // staging row: 32 bf16 (64 B) + 16 B pad (conflict-free)
 static constexpr int kStgBytes = 32 * kStgRow + 4 * 128;  // per epilogue warp: 32x32 bf16 panel + 4 bias panels (fp32)
 
-template <int BN>
+// CTAS = 2: a CTA pair (2-cluster, cta_group::2) computes a 256 x BN tile; each CTA stages its own 128 rows of A and
+// HALF of the B tile (BN/2 rows), so per-SM operand traffic (TMA writes + MMA reads) drops by the B half.
+template <int BN, int CTAS = 1>
 struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;                // 16 KB
-  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kBBytes = (BN / CTAS) * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4;   // 224: 4 x 44 KB, 256: 4 x 48 KB
+  static constexpr int kStages1 = (BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4;   // 224: 4 x 44 KB, 256: 4 x 48 KB
+  static constexpr int kStages = CTAS == 1 ? kStages1 : 6;     // pair: 6 x (16 + <= 16) KB
   static constexpr int kAccStride = (BN <= 64) ? 64 : (BN <= 128) ? 128 : 256;  // TMEM columns
   static constexpr int kTmemCols = 2 * kAccStride;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kStgBytes + 1024 /*align*/ + 256 /*barriers*/;
@@ -51,15 +54,16 @@ struct GemmCfg {
 // Work iterator shared by the three warp roles: classic mode hands out whole tiles round-robin; range mode walks this
 // CTA's contiguous slice of the (tile, K-chunk) space segment by segment.
 struct WorkIter {
-  int range, num_tiles, num_k, T, cur, end;
-  FGDM_DEVINL WorkIter(const GemmParams& p, int num_tiles_, int num_k_) {
+  int range, num_tiles, num_k, T, cur, end, stride;
+  FGDM_DEVINL WorkIter(const GemmParams& p, int num_tiles_, int num_k_, int ctas = 1) {
     range = p.range_ctas; num_tiles = num_tiles_; num_k = num_k_; T = num_tiles_ * num_k_;
     if (range) {
       cur = static_cast<int>(static_cast<long long>(blockIdx.x) * T / range);
       end = static_cast<int>(static_cast<long long>(blockIdx.x + 1) * T / range);
     } else {
-      cur = blockIdx.x; end = num_tiles_;
+      cur = blockIdx.x / ctas; end = num_tiles_;
     }
+    stride = gridDim.x / ctas;
   }
   FGDM_DEVINL bool next(int& tile, int& kb, int& ke) {
     if (cur >= end) return false;
@@ -70,7 +74,7 @@ struct WorkIter {
       cur += ke - kb;
     } else {
       tile = cur; kb = 0; ke = num_k;
-      cur += gridDim.x;
+      cur += stride;
     }
     return true;
   }
@@ -86,12 +90,13 @@ struct WorkIter {
 // the 8 epilogue warps only (barrier 0 is the CTA-wide one used at start-up and tear-down)
 FGDM_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
 
-template <int BN>
+template <int BN, int CTAS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
                const __grid_constant__ CUtensorMap map_b, const __grid_constant__ GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CTAS>;
   constexpr int kStages = Cfg::kStages;
+  const uint32_t cta_rank = CTAS == 2 ? cluster_ctarank() : 0;   // 0 = leader (issues the pair MMAs)
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -119,16 +124,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
-      mbar_init(&acc_empty[i], kEpiWarps);
+      mbar_init(&acc_empty[i], kEpiWarps * CTAS);    // pair: the peer's epilogue warps arrive remotely on the leader
     }
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_ptr, Cfg::kTmemCols);
-    tmem_relinquish();
+    if (CTAS == 2) {
+      tmem_alloc_pair(tmem_ptr, Cfg::kTmemCols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_ptr, Cfg::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();               // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   pdl_wait();                  // everything above overlapped the previous kernel's tail
@@ -137,18 +148,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   const int ctot = p.C0 + p.C1;
   const int chunks_per_tap = ctot / kBK;
   const int num_k = p.taps * chunks_per_tap;
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  // pair mode walks 256-row tile pairs: this CTA owns m_tile = 2 * pair + rank
+  const int num_tiles = ((p.num_m_tiles + CTAS - 1) / CTAS) * p.num_n_tiles;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      WorkIter it(p, num_tiles, num_k);
+      WorkIter it(p, num_tiles, num_k, CTAS);
       int tile, kc_begin, kc_end;
       while (it.next(tile, kc_begin, kc_end)) {
-        const int m_tile = tile / p.num_n_tiles;
-        const int n_tile = tile - m_tile * p.num_n_tiles;
+        const int m_tile = (tile / p.num_n_tiles) * CTAS + cta_rank;
+        const int n_tile = tile % p.num_n_tiles;
         const int m0 = m_tile * kBM;
         const int w0 = m0 % p.W;
         const int hw = m0 / p.W;
@@ -158,18 +170,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
           const int tap = kc / chunks_per_tap;
           const int c = (kc - tap * chunks_per_tap) * kBK;
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           void* dst_a = smem_a + stage * Cfg::kABytes;
           void* dst_b = smem_b + stage * Cfg::kBBytes;
           const int cw = w0 + p.tap_dw[tap];
           const int ch = h0 + p.tap_dh[tap];
           const int cn = n0 + p.tap_dn[tap];
-          if (c < p.C0) {
-            tma_load_4d(dst_a, &map_a0, &full_bar[stage], c, cw, ch, cn);
+          if (CTAS == 2) {
+            // both CTAs' bytes are credited to the LEADER's barrier, which expects the whole pair stage
+            const uint32_t bar = mapa_shared(smem_u32(&full_bar[stage]), 0);
+            if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
+            if (c < p.C0) tma_load_4d_pair(dst_a, &map_a0, bar, c, cw, ch, cn);
+            else tma_load_4d_pair(dst_a, &map_a1, bar, c - p.C0, cw, ch, cn);
+            tma_load_2d_pair(dst_b, &map_b, bar, kc * kBK, n_tile * BN + static_cast<int>(cta_rank) * (BN / 2));
           } else {
-            tma_load_4d(dst_a, &map_a1, &full_bar[stage], c - p.C0, cw, ch, cn);
+            mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+            if (c < p.C0) {
+              tma_load_4d(dst_a, &map_a0, &full_bar[stage], c, cw, ch, cn);
+            } else {
+              tma_load_4d(dst_a, &map_a1, &full_bar[stage], c - p.C0, cw, ch, cn);
+            }
+            tma_load_2d(dst_b, &map_b, &full_bar[stage], kc * kBK, n_tile * BN);
           }
-          tma_load_2d(dst_b, &map_b, &full_bar[stage], kc * kBK, n_tile * BN);
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -179,13 +200,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(kBM, BN);
+    if (lane == 0 && cta_rank == 0) {                     // pair mode: the leader CTA issues for both
+      constexpr uint32_t idesc = make_idesc_bf16(kBM * CTAS, BN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      WorkIter it(p, num_tiles, num_k);
+      WorkIter it(p, num_tiles, num_k, CTAS);
       int tile, kc_begin, kc_end;
       while (it.next(tile, kc_begin, kc_end)) {
         mbar_wait(&acc_empty[acc], acc_phase ^ 1);
@@ -199,15 +220,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k) {
             // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in (addr>>4)
-            tc_mma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
+            if (CTAS == 2) tc_mma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
+            else tc_mma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
           }
-          tc_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+          // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+          if (CTAS == 2) tc_commit_pair(&empty_bar[stage]); else tc_commit(&empty_bar[stage]);
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        tc_commit(&acc_full[acc]);  // accumulator complete -> epilogue
+        if (CTAS == 2) tc_commit_pair(&acc_full[acc]); else tc_commit(&acc_full[acc]);  // accumulator complete -> epilogue
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -232,15 +255,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     const int np = (kPanels + 1 - half) / 2;                     // this warp's panels: c0 = half*32 + 64*i
     int acc = 0;
     uint32_t acc_phase = 0;
-    WorkIter it(p, num_tiles, num_k);
+    WorkIter it(p, num_tiles, num_k, CTAS);
     int tile, kc_begin, kc_end;
     bool first_seg = true;
     while (it.next(tile, kc_begin, kc_end)) {
       const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
       const int my_slot = first_seg ? 0 : 1;
       first_seg = false;
-      const int m_tile = tile / p.num_n_tiles;
-      const int n_tile = tile - m_tile * p.num_n_tiles;
+      const int m_tile = (tile / p.num_n_tiles) * CTAS + cta_rank;
+      const int n_tile = tile % p.num_n_tiles;
       const int m_warp = m_tile * kBM + quarter * 32;   // first row of this warp
       const int m = m_warp + lane;
       const bool row_ok = m < p.M;
@@ -548,7 +571,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      if (lane == 0) {
+        if (CTAS == 2) mbar_arrive_cluster(mapa_shared(smem_u32(&acc_empty[acc]), 0));   // the leader's MMA thread waits
+        else mbar_arrive(&acc_empty[acc]);
+      }
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
@@ -558,19 +584,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 
   tc_fence_before();
   __syncthreads();
+  if (CTAS == 2) cluster_sync_all();   // the peer may still be signalling this CTA's barriers / reading its smem
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    if (CTAS == 2) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+    else tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
-template <int BN>
+template <int BN, int CTAS>
 static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUtensorMap& mb, const GemmParams& p,
                      cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CTAS>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("gemm: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -578,9 +606,23 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
     }
     configured = true;
   }
-  const int tiles = p.num_m_tiles * p.num_n_tiles;
-  const int grid = p.range_ctas ? p.range_ctas : (tiles < num_sms() ? tiles : num_sms());
-  cudaError_t e = launch_pdl(gemm_tc_kernel<BN>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, ma0, ma1, mb, p);
+  const int tiles = ((p.num_m_tiles + CTAS - 1) / CTAS) * p.num_n_tiles;
+  int grid = p.range_ctas ? p.range_ctas : (tiles * CTAS < num_sms() ? tiles * CTAS : num_sms() / CTAS * CTAS);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = CTAS;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = CTAS == 2 ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS>, ma0, ma1, mb, p);
   if (e != cudaSuccess) { set_error("gemm_tc_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("gemm_tc_kernel");
 }
@@ -651,6 +693,8 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     return -1;
   }
   p.M = p.NB * p.H * p.W;
+  const bool force_pair = bn_hint >= 1000;        // bn_hint = 1000 + BN: CTA-pair (cta_group::2) kernel with that tile width
+  if (force_pair) bn_hint -= 1000;
   int BN = bn_hint;
   p.range_ctas = 0;
   const int m_tiles = (p.M + kBM - 1) / kBM;
@@ -700,6 +744,13 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     if (getenv("FGDM_GEMM_DEBUG"))
       fprintf(stderr, "gemm M=%d N=%d chunks=%d -> BN=%d range_ctas=%d\n", p.M, p.N, num_k_chunks, BN, p.range_ctas);
   }
+  // CTA pairs (cta_group::2): a 2-cluster runs one 256-row MMA, each CTA staging half of the B tile. Measured on B200
+  // (tools/bench_bn.py, m=65536 k=2880 n=1280): +3.5 % at BN=256 (1308 -> 1353 TFLOP/s), +2 % at 160/224, and -5 % on
+  // the short-K linears (cluster launch), i.e. operand traffic is not what bounds these tiles; the path is kept,
+  // tested (bn_hint = 1000 + BN) and opt-in (FGDM_PAIR=1) rather than default.
+  static int pair_mode = -1;
+  if (pair_mode < 0) { const char* e = getenv("FGDM_PAIR"); pair_mode = e ? atoi(e) : 0; }
+  const int ctas = ((pair_mode || force_pair) && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
   if (p.range_ctas) {
     if (static_cast<size_t>(p.range_ctas) * 2 * kBM * BN * 4 > kSplitWsBytes) { set_error("gemm: range scratch too small"); return -1; }
     p.split_ws = g_split_ws;
@@ -732,15 +783,23 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   {
     uint64_t dims[2] = {K, static_cast<uint64_t>(p.N)};
     uint64_t strides[1] = {K * 2};
-    uint32_t box[2] = {kBK, static_cast<uint32_t>(BN)};
+    uint32_t box[2] = {kBK, static_cast<uint32_t>(BN / ctas)};   // pair mode: each CTA fetches its half of the B tile
     if (encode_tmap(&mb, w, 2, dims, strides, box)) return -1;
   }
+  if (ctas == 2) {
+    switch (BN) {
+      case 160: return launch_bn<160, 2>(ma0, ma1, mb, p, stream);
+      case 224: return launch_bn<224, 2>(ma0, ma1, mb, p, stream);
+      case 256: return launch_bn<256, 2>(ma0, ma1, mb, p, stream);
+      default: set_error("gemm: unsupported pair BN=%d", BN); return -1;
+    }
+  }
   switch (BN) {
-    case 64: return launch_bn<64>(ma0, ma1, mb, p, stream);
-    case 128: return launch_bn<128>(ma0, ma1, mb, p, stream);
-    case 160: return launch_bn<160>(ma0, ma1, mb, p, stream);
-    case 224: return launch_bn<224>(ma0, ma1, mb, p, stream);
-    case 256: return launch_bn<256>(ma0, ma1, mb, p, stream);
+    case 64: return launch_bn<64, 1>(ma0, ma1, mb, p, stream);
+    case 128: return launch_bn<128, 1>(ma0, ma1, mb, p, stream);
+    case 160: return launch_bn<160, 1>(ma0, ma1, mb, p, stream);
+    case 224: return launch_bn<224, 1>(ma0, ma1, mb, p, stream);
+    case 256: return launch_bn<256, 1>(ma0, ma1, mb, p, stream);
     default: set_error("gemm: unsupported BN=%d", BN); return -1;
   }
 }

@@ -84,7 +84,7 @@ typedef struct {
   int qkv_first;           /* 0: weight rows are [q|k|v]; 1: [k|v] */
   int heads, dhead;
   int tok_pad;
-  int bn_hint;             /* N tile (0 = auto; 64/128/160/224/256) */
+  int bn_hint;             /* N tile (0 = auto; 64/128/160/224/256; 1000 + {160,224,256} = CTA-pair kernel) */
   int n_store;             /* FGDM_OUT_NCHW_F32: real output channels (weights zero-padded to n) */
 } fgdm_gemm_args;
 

@@ -51,6 +51,19 @@ def test_linear(m, k, n, bn):
     assert relerr(y, ref) < 1e-2
 
 
+@pytest.mark.parametrize("m,k,n,bn", [(4096, 1280, 1280, 1256), (1536, 640, 640, 1160), (65536, 320, 640, 1224)])
+def test_linear_cta_pair(m, k, n, bn):
+    """bn_hint = 1000 + BN selects the cta_group::2 kernel: a 2-CTA cluster issues one 256-row tcgen05.mma, each CTA
+    stages its 128 rows of A and half of the B tile, the leader's barriers cover both (include/fgdm_b200.h)."""
+    x = torch.randn(m, k, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(n, k, device=DEV) / math.sqrt(k)).to(torch.bfloat16)
+    b = torch.randn(n, device=DEV)
+    r0 = torch.randn(m, n, device=DEV).to(torch.bfloat16)
+    y = ops.conv_gemm(x, w, n, bias=b, res0=r0, bn_hint=bn)
+    ref = x.float() @ w.float().t() + b + r0.float()
+    assert relerr(y, ref) < 1e-2
+
+
 def test_linear_epilogues():
     m, k, n = 512, 256, 320
     x = torch.randn(m, k, device=DEV).to(torch.bfloat16)

@@ -34,7 +34,7 @@ cases = [("conv", 16, 8, 8, 1280, 1280, True), ("conv", 16, 8, 8, 2560, 1280, Tr
          ("conv", 16, 32, 32, 640, 640, True), ("conv", 16, 64, 64, 320, 320, True), ("conv", 16, 64, 64, 640, 320, True),
          ("lin", 16, 64, 64, 320, 320, True), ("lin", 16, 32, 32, 640, 640, True), ("lin", 16, 16, 16, 1280, 1280, True),
          ("lin", 16, 8, 8, 1280, 1280, True), ("lin", 16, 64, 64, 1280, 320, True), ("lin", 16, 16, 16, 5120, 1280, True)]
-for kind, nb, h, w, cin, cout, res in cases:
+for kind, nb, h, w, cin, cout, res in (cases if __name__ == "__main__" else []):
     m = nb * h * w
     x = torch.randn(nb, h, w, cin, device="cuda").to(bf)
     b = torch.randn(cout, device="cuda")
