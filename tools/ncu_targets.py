@@ -1,0 +1,59 @@
+"""One eager launch of each hot kernel at its dominant UNet shape (for `ncu --set full`; run under gpurun)."""
+import os
+import sys
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from fgdm_b200 import ops  # noqa: E402
+
+bf = torch.bfloat16
+torch.manual_seed(0)
+
+
+def conv(nb, h, w, cin, cout):
+    x = torch.randn(nb, h, w, cin, device="cuda").to(bf)
+    wt = (torch.randn(cout, 9 * cin, device="cuda") / (9 * cin) ** 0.5).to(bf)
+    b = torch.randn(cout, device="cuda")
+    r = torch.randn(nb * h * w, cout, device="cuda").to(bf)
+    return lambda: ops.conv_gemm(x, wt, cout, conv=ops.CONV_3X3, bias=b, res0=r)
+
+
+def lin(m, k, n):
+    x = torch.randn(m, k, device="cuda").to(bf)
+    wt = (torch.randn(n, k, device="cuda") / k ** 0.5).to(bf)
+    b = torch.randn(n, device="cuda")
+    r = torch.randn(m, n, device="cuda").to(bf)
+    return lambda: ops.conv_gemm(x, wt, n, bias=b, res0=r)
+
+
+def attn(images, heads, nq, nk, d):
+    q = torch.randn(images, heads, nq, d, device="cuda").to(bf)
+    k = torch.randn(images, heads, nk, d, device="cuda").to(bf)
+    tp = (nk + 7) // 8 * 8
+    vt = torch.randn(images, heads, d, tp, device="cuda").to(bf)
+    out = torch.empty(images, nq, heads * d, device="cuda", dtype=bf)
+    return lambda: ops.attention(q, k, vt, out, images, heads, nq, nk, d, tp)
+
+
+def gn(nb, hw, c):
+    s = int(hw ** 0.5)
+    x = torch.randn(nb, s, s, c, device="cuda").to(bf)
+    g, b = torch.randn(c, device="cuda"), torch.randn(c, device="cuda")
+    out = torch.empty_like(x)
+    return lambda: ops.groupnorm(x, g, b, silu=True, out=out)
+
+
+def ln(rows, c):
+    x = torch.randn(rows, c, device="cuda").to(bf)
+    g, b = torch.randn(c, device="cuda"), torch.randn(c, device="cuda")
+    return lambda: ops.layernorm(x, g, b)
+
+
+targets = [conv(16, 64, 64, 320, 320), conv(16, 32, 32, 640, 640), conv(16, 16, 16, 1280, 1280), conv(16, 8, 8, 1280, 1280),
+           lin(65536, 320, 320), lin(4096, 1280, 1280), attn(16, 8, 4096, 4096, 40), attn(16, 8, 1024, 1024, 80),
+           attn(16, 8, 4096, 77, 40), gn(16, 4096, 320), gn(16, 1024, 640), gn(16, 64, 1280), ln(65536, 320)]
+for rep in range(2):      # pass 0 warms (function attributes, scratch allocation); profile pass 1 (ncu -s <n>)
+    for t in targets:
+        t()
+    torch.cuda.synchronize()
