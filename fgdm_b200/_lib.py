@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfgdm_b200.so")
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32, OUT_NCHW_F32 = 0, 1, 2, 3, 4
 ACT_NONE, ACT_SILU, ACT_RELU = 0, 1, 2
@@ -32,6 +32,7 @@ class GemmArgs(C.Structure):
         ("out", vp), ("ldo", C.c_int), ("col_off", C.c_int),
         ("q_out", vp), ("k_out", vp), ("vt_out", vp), ("qkv_first", C.c_int),
         ("heads", C.c_int), ("dhead", C.c_int), ("tok_pad", C.c_int), ("bn_hint", C.c_int), ("n_store", C.c_int),
+        ("res1_rows", C.c_int),
     ]
 
 

@@ -204,6 +204,7 @@ int fgdm_conv_gemm(const fgdm_gemm_args* a, void* stream) {
   p.ld_res0 = a->ld_res0;
   p.res1 = reinterpret_cast<const __nv_bfloat16*>(a->res1);
   p.ld_res1 = a->ld_res1;
+  p.res1_rows = a->res1_rows;
   p.alpha = a->alpha;
   p.act = a->act;
   p.out_mode = a->out_mode;

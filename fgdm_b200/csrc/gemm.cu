@@ -499,7 +499,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                 }
               }
               if (p.res1 && row_ok) {
-                const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(m) * p.ld_res1 + col);
+                const int m1 = p.res1_rows > 0 ? m % p.res1_rows : m;
+                const uint4* rp = reinterpret_cast<const uint4*>(p.res1 + static_cast<size_t>(m1) * p.ld_res1 + col);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                   const uint4 u = rp[q];

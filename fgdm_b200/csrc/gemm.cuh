@@ -35,6 +35,7 @@ struct GemmParams {
   int ld_res0;
   const __nv_bfloat16* res1;
   int ld_res1;
+  int res1_rows;        // > 0: res1 row = m % res1_rows (shared adapter features of the two CFG halves)
   float alpha;
   int act;
   int out_mode;

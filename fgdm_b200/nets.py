@@ -275,7 +275,9 @@ class UNetModel(_UNetBase):
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
         emb_all = self._emb(timesteps)
-        fa = self.adapter.forward(x, rows) if self.adapter is not None else None   # prompt = h, :836-844
+        # prompt = h (:836-844): the adapter sees only the latent, so its features are identical for the cond and
+        # uncond CFG rows -> computed once per unique latent, added modulo by the GEMM epilogue (res1_rows)
+        fa = self.adapter.forward(x, x.shape[0]) if self.adapter is not None else None
         h, hs = self._encode(x, rows, emb_all, kvs, fa)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
         return self._decode(h, hs, emb_all, kvs)

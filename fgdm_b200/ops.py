@@ -77,7 +77,7 @@ def count_launches(n: int) -> None:
 
 def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None, bias=None, rowvec=None,
               rows_per_img=0, res0=None, res1=None, alpha=1.0, act=ACT_NONE, out_mode=OUT_BF16, out=None,
-              ldo=None, col_off=0, qkv=None, bn_hint=0, n_store=0):
+              ldo=None, col_off=0, qkv=None, bn_hint=0, n_store=0, res1_rows=0):
     """Implicit-GEMM conv / Linear. a0 (and a1) are NHWC bf16 `[nb, h, w, c]` or token `[rows, c]` tensors.
 
     For CONV_3X3_S2, a0 is the phase-split tensor `[4, nb, h, w, c]` (see resample(mode=2)) and
@@ -102,6 +102,12 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
     args.res1, args.ld_res1 = _p(res1), (res1.stride(-2) if res1 is not None else 0)
     args.alpha, args.act, args.out_mode = alpha, act, out_mode
     args.bn_hint = bn_hint
+    if res1 is not None and res1_rows == 0:
+        r1 = res1.numel() // res1.shape[-1]
+        if r1 < m:                       # shared by several images (adapter features of the CFG halves): modulo rows
+            assert m % r1 == 0, (m, r1)
+            res1_rows = r1
+    args.res1_rows = res1_rows
     if out_mode == OUT_QKV:
         q, k, vt, first, heads, dhead, tok_pad = qkv
         args.q_out, args.k_out, args.vt_out = _p(q), _p(k), _p(vt)

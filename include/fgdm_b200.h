@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define FGDM_ABI_VERSION 2
+#define FGDM_ABI_VERSION 3
 
 const char* fgdm_last_error(void);
 int fgdm_abi_version(void);
@@ -86,6 +86,8 @@ typedef struct {
   int tok_pad;
   int bn_hint;             /* N tile (0 = auto; 64/128/160/224/256; 1000 + {160,224,256} = CTA-pair kernel) */
   int n_store;             /* FGDM_OUT_NCHW_F32: real output channels (weights zero-padded to n) */
+  int res1_rows;           /* > 0: res1 has only this many rows and row m reads res1[m % res1_rows] (the FG-DM adapter
+                            * features are identical for the cond and uncond CFG halves, openaimodel.py:836-857) */
 } fgdm_gemm_args;
 
 /* nn.Conv2d / nn.Linear call sites: openaimodel.py:224,250,261,112,164-166; attention.py:40,60,
