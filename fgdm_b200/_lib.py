@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfgdm_b200.so")
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32, OUT_NCHW_F32 = 0, 1, 2, 3, 4
 ACT_NONE, ACT_SILU, ACT_RELU = 0, 1, 2
@@ -33,6 +33,8 @@ class GemmArgs(C.Structure):
         ("q_out", vp), ("k_out", vp), ("vt_out", vp), ("qkv_first", C.c_int),
         ("heads", C.c_int), ("dhead", C.c_int), ("tok_pad", C.c_int), ("bn_hint", C.c_int), ("n_store", C.c_int),
         ("res1_rows", C.c_int),
+        ("row_stats", vp), ("ln_stats", vp), ("ln_slots", C.c_int), ("ln_s", vp), ("ln_channels", C.c_int),
+        ("ln_eps", C.c_float),
     ]
 
 
@@ -41,6 +43,7 @@ SIGNATURES = {
     "fgdm_abi_version": [],
     "fgdm_device_check": [],
     "fgdm_conv_gemm": [C.POINTER(GemmArgs), vp],
+    "fgdm_gemm_stats_slots": [C.POINTER(GemmArgs)],
     "fgdm_attention": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp],
     "fgdm_groupnorm": [vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp],
     "fgdm_layernorm": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp],

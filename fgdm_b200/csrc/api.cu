@@ -98,7 +98,7 @@ int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dim
 
 // launchers implemented in the other translation units
 int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, const void* w, int bn_hint,
-                cudaStream_t stream);
+                cudaStream_t stream, int* stats_slots_out = nullptr);
 int launch_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int Nq, int Nk,
                      int d, int tok_pad, float scale, cudaStream_t stream);
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
@@ -166,7 +166,7 @@ int fgdm_device_check(void) {
   return get_encode() ? 0 : -1;
 }
 
-int fgdm_conv_gemm(const fgdm_gemm_args* a, void* stream) {
+static int conv_gemm_impl(const fgdm_gemm_args* a, void* stream, int* stats_slots_out) {
   FGDM_NONNULL(a, "args");
   FGDM_NONNULL(a->a0, "a0");
   FGDM_NONNULL(a->weight, "weight");
@@ -239,7 +239,33 @@ int fgdm_conv_gemm(const fgdm_gemm_args* a, void* stream) {
       return -2;
     }
   }
-  return launch_gemm(p, a->a0, a->a1, a_images, a->weight, a->bn_hint, reinterpret_cast<cudaStream_t>(stream));
+  p.row_stats = reinterpret_cast<float2*>(a->row_stats);
+  p.ln_stats = reinterpret_cast<const float2*>(a->ln_stats);
+  p.ln_slots = a->ln_slots;
+  p.ln_s = a->ln_s;
+  p.ln_eps = a->ln_eps;
+  if (p.ln_stats) {
+    if (a->ln_slots <= 0 || (a->ln_slots & 1) || (reinterpret_cast<uintptr_t>(a->ln_stats) & 15) || a->ln_channels <= 0 ||
+        !a->ln_s || !a->bias) {
+      set_error("fgdm_conv_gemm: folded LayerNorm needs ln_slots, ln_channels, ln_s and bias");
+      return -2;
+    }
+    p.ln_inv_c = 1.0f / static_cast<float>(a->ln_channels);
+  }
+  if (p.row_stats && a->out_mode != FGDM_OUT_BF16) {
+    set_error("fgdm_conv_gemm: row_stats needs FGDM_OUT_BF16");
+    return -2;
+  }
+  return launch_gemm(p, a->a0, a->a1, a_images, a->weight, a->bn_hint, reinterpret_cast<cudaStream_t>(stream),
+                     stats_slots_out);
+}
+
+int fgdm_conv_gemm(const fgdm_gemm_args* a, void* stream) { return conv_gemm_impl(a, stream, nullptr); }
+
+int fgdm_gemm_stats_slots(const fgdm_gemm_args* a) {
+  int slots = 0;
+  const int rc = conv_gemm_impl(a, nullptr, &slots);
+  return rc < 0 ? rc : slots;
 }
 
 int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int nq, int nk,

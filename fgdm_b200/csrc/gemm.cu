@@ -35,7 +35,7 @@ static constexpr int kBK = 64;
 static constexpr int kEpiWarps = 8;                      // two warps per TMEM lane quarter, alternating 32-col panels
 static constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 static constexpr int kStgRow = 80;                       // staging row: 32 bf16 (64 B) + 16 B pad (conflict-free)
-static constexpr int kStgBytes = 32 * kStgRow + 4 * 128;  // per epilogue warp: 32x32 bf16 panel + 4 bias panels (fp32)
+static constexpr int kStgBytes = 32 * kStgRow + 8 * 128;  // per epilogue warp: 32x32 bf16 panel + 4 bias + 4 LN-fold panels (fp32)
 
 // CTAS = 2: a CTA pair (2-cluster, cta_group::2) computes a 256 x BN tile; each CTA stages its own 128 rows of A and
 // HALF of the B tile (BN/2 rows), so per-SM operand traffic (TMA writes + MMA reads) drops by the B half.
@@ -269,6 +269,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       const bool row_ok = m < p.M;
       const int img = row_ok ? (m / p.rows_per_img) : 0;
       const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
+      // folded LayerNorm: this row's mean / rstd from the producer GEMM's partial sums (fixed slot order)
+      float ln_rstd = 1.0f, ln_rm = 0.0f;                      // rstd and rstd * mean
+      if (p.ln_stats) {
+        float s1 = 0.0f, s2 = 0.0f;
+        if (row_ok) {
+          // slots come in pairs (one per column half of a producer tile): 16-byte loads, four in flight
+          const float4* st = reinterpret_cast<const float4*>(p.ln_stats + static_cast<size_t>(m) * p.ln_slots);
+          const int nq = p.ln_slots >> 1;
+          for (int q0 = 0; q0 < nq; q0 += 4) {
+            float4 f[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) f[q] = q0 + q < nq ? __ldg(st + q0 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { s1 += f[q].x; s1 += f[q].z; s2 += f[q].y; s2 += f[q].w; }
+          }
+        }
+        const float mean = s1 * p.ln_inv_c;
+        const float var = fmaxf(s2 * p.ln_inv_c - mean * mean, 0.0f);
+        ln_rstd = rsqrtf(var + p.ln_eps);
+        ln_rm = ln_rstd * mean;
+      }
 
       if (p.out_mode == kOutGeglu) {
         constexpr int kHalf = BN / 2;
@@ -288,6 +309,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               }
               asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (2 * i) * 128 + lane * 4), "f"(bx) : "memory");
               asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (2 * i + 1) * 128 + lane * 4), "f"(bg) : "memory");
+              if (p.ln_stats) {
+                float sx = 0.0f, sg = 0.0f;
+                if (n_tile * kHalf + c0 < p.N / 2) {
+                  sx = __ldg(p.ln_s + bcol + lane);
+                  sg = __ldg(p.ln_s + bcol + kHalf + lane);
+                }
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (4 + 2 * i) * 128 + lane * 4), "f"(sx) : "memory");
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (5 + 2 * i) * 128 + lane * 4), "f"(sg) : "memory");
+              }
             }
           }
         }
@@ -314,10 +344,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                   bx = make_float4(__uint_as_float(ux.x), __uint_as_float(ux.y), __uint_as_float(ux.z), __uint_as_float(ux.w));
                   bg = make_float4(__uint_as_float(ug.x), __uint_as_float(ug.y), __uint_as_float(ug.z), __uint_as_float(ug.w));
                 }
-                const float x0 = __uint_as_float(rx[j]) + bx.x, x1 = __uint_as_float(rx[j + 1]) + bx.y;
-                const float x2 = __uint_as_float(rx[j + 2]) + bx.z, x3 = __uint_as_float(rx[j + 3]) + bx.w;
-                const float g0 = __uint_as_float(rg[j]) + bg.x, g1 = __uint_as_float(rg[j + 1]) + bg.y;
-                const float g2 = __uint_as_float(rg[j + 2]) + bg.z, g3 = __uint_as_float(rg[j + 3]) + bg.w;
+                if (p.ln_stats) {                                 // bias' = bias - rstd * mean * ln_s
+                  const uint4 vx = ld_shared_16(sbias_u32 + (4 + 2 * i) * 128 + j * 4);
+                  const uint4 vg = ld_shared_16(sbias_u32 + (5 + 2 * i) * 128 + j * 4);
+                  bx.x = fmaf(-ln_rm, __uint_as_float(vx.x), bx.x); bx.y = fmaf(-ln_rm, __uint_as_float(vx.y), bx.y);
+                  bx.z = fmaf(-ln_rm, __uint_as_float(vx.z), bx.z); bx.w = fmaf(-ln_rm, __uint_as_float(vx.w), bx.w);
+                  bg.x = fmaf(-ln_rm, __uint_as_float(vg.x), bg.x); bg.y = fmaf(-ln_rm, __uint_as_float(vg.y), bg.y);
+                  bg.z = fmaf(-ln_rm, __uint_as_float(vg.z), bg.z); bg.w = fmaf(-ln_rm, __uint_as_float(vg.w), bg.w);
+                }
+                const float x0 = fmaf(__uint_as_float(rx[j]), ln_rstd, bx.x), x1 = fmaf(__uint_as_float(rx[j + 1]), ln_rstd, bx.y);
+                const float x2 = fmaf(__uint_as_float(rx[j + 2]), ln_rstd, bx.z), x3 = fmaf(__uint_as_float(rx[j + 3]), ln_rstd, bx.w);
+                const float g0 = fmaf(__uint_as_float(rg[j]), ln_rstd, bg.x), g1 = fmaf(__uint_as_float(rg[j + 1]), ln_rstd, bg.y);
+                const float g2 = fmaf(__uint_as_float(rg[j + 2]), ln_rstd, bg.z), g3 = fmaf(__uint_as_float(rg[j + 3]), ln_rstd, bg.w);
                 packed[j >> 1] = pack_bf16x2(x0 * gelu_erf_f(g0), x1 * gelu_erf_f(g1));
                 packed[(j >> 1) + 1] = pack_bf16x2(x2 * gelu_erf_f(g2), x3 * gelu_erf_f(g3));
               }
@@ -355,14 +393,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         };
         uint4 rres[4];
         if (pre_res) load_res(0, rres);
-        if (p.bias) {
-#pragma unroll 1
-          for (int i = 0; i < np; ++i) {
+        if (p.bias) {     // bias (and folded-LN column sums): all loads first, then the smem stores
+          float bv[kMaxP], sv[kMaxP];
+#pragma unroll
+          for (int i = 0; i < kMaxP; ++i) {
             const int col = n_tile * BN + half * 32 + 64 * i;
-            if (col < p.N)
-              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + i * 128 + lane * 4), "f"(__ldg(p.bias + col + lane)) : "memory");
+            const bool on = i < np && col < p.N;
+            bv[i] = on ? __ldg(p.bias + col + lane) : 0.0f;
+            sv[i] = on && p.ln_stats ? __ldg(p.ln_s + col + lane) : 0.0f;
+          }
+#pragma unroll
+          for (int i = 0; i < kMaxP; ++i) {
+            if (i < np) {
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + i * 128 + lane * 4), "f"(bv[i]) : "memory");
+              if (p.ln_stats)
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (4 + i) * 128 + lane * 4), "f"(sv[i]) : "memory");
+            }
           }
         }
+        float rs_sum = 0.0f, rs_sq = 0.0f;                       // producer side: this row's partial statistics
         __syncwarp();
         mbar_wait(&acc_full[acc], acc_phase);
         tc_fence_after();
@@ -455,6 +504,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               float v[32];
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+              if (p.ln_stats) {                                // folded LayerNorm: rstd * (acc - mean * s[n]) (+ bias below)
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                  const uint4 u = ld_shared_16(sbias_u32 + (4 + i) * 128 + j * 4);
+                  v[j] = fmaf(v[j], ln_rstd, -ln_rm * __uint_as_float(u.x));
+                  v[j + 1] = fmaf(v[j + 1], ln_rstd, -ln_rm * __uint_as_float(u.y));
+                  v[j + 2] = fmaf(v[j + 2], ln_rstd, -ln_rm * __uint_as_float(u.z));
+                  v[j + 3] = fmaf(v[j + 3], ln_rstd, -ln_rm * __uint_as_float(u.w));
+                }
+              }
               if (p.bias) {
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) {
@@ -514,11 +573,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                 }
               }
               if (staged) {
+                uint32_t pk[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                if (p.row_stats) {   // statistics of the ROUNDED values: exactly what the consuming GEMM multiplies
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) {
+                    const float2 f = unpack_bf16x2(pk[j]);
+                    rs_sum += f.x + f.y;
+                    rs_sq = fmaf(f.x, f.x, fmaf(f.y, f.y, rs_sq));
+                  }
+                }
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
-                  st_shared_16(stg_u32 + lane * kStgRow + q * 16,
-                               make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                          pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+                  st_shared_16(stg_u32 + lane * kStgRow + q * 16, make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]));
                 __syncwarp();
                 __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + p.col_off + col;
 #pragma unroll
@@ -569,6 +637,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
             }
           }
         }
+        // producer side of the folded LayerNorm: one {sum, sumsq} slot per (n_tile, panel half) and row
+        if (p.row_stats && finish && row_ok)
+          p.row_stats[static_cast<size_t>(m) * (2 * p.num_n_tiles) + 2 * n_tile + half] = make_float2(rs_sum, rs_sq);
       }
       tc_fence_before();
       __syncwarp();
@@ -681,7 +752,7 @@ static bool tile_box(int NB, int H, int W, int* bn, int* bh, int* bw) {
 // a0/a1: NHWC bf16 sources with a0_NB images (a stride-2 conv passes the phase-split tensor with
 // 4*NB images). w: [N, taps*(C0+C1)] bf16. `bn_hint` selects the N tile (0 = automatic).
 int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, const void* w, int bn_hint,
-                cudaStream_t stream) {
+                cudaStream_t stream, int* stats_slots_out) {
   if (p.C0 <= 0 || p.C0 % kBK != 0 || p.C1 % kBK != 0) {
     set_error("gemm: channel counts must be positive multiples of 64 (C0=%d C1=%d)", p.C0, p.C1);
     return -1;
@@ -759,6 +830,10 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   }
   p.num_m_tiles = (p.M + kBM - 1) / kBM;
   p.num_n_tiles = (p.N + BN - 1) / BN;
+  if (stats_slots_out) {             // dry run: how many row_stats slots per row this launch would write
+    *stats_slots_out = 2 * p.num_n_tiles;
+    return 0;
+  }
   const int ctot = p.C0 + p.C1;
   const uint64_t K = static_cast<uint64_t>(p.taps) * ctot;
 

@@ -51,6 +51,18 @@ struct GemmParams {
   int inner;            // heads * dhead
   int heads, dhead;
   int tok_pad;          // row stride of the transposed V (>= tokens per image, multiple of 8)
+  // LayerNorm folded into the GEMM (attention.py:226-240: every nn.LayerNorm feeds a Linear). PRODUCER side: a GEMM
+  // whose bf16 output is the residual stream also writes per-row partial {sum, sum of squares} of its output columns,
+  // one slot per (n_tile, panel half): row_stats[m * stats_slots + slot]. CONSUMER side: the Linear runs on the RAW
+  // tokens with weights pre-multiplied by gamma; the epilogue applies v = rstd * (acc - mean * ln_s[n]) + bias[n],
+  // ln_s[n] = sum_k gamma[k] W[n,k], bias[n] = sum_k beta[k] W[n,k] + b[n], mean/rstd from the producer's slots
+  // summed in slot order (bit-reproducible). No LayerNorm kernel, no normalised copy of the tokens in HBM.
+  float2* row_stats;            // producer: [M, stats_slots] or NULL
+  const float2* ln_stats;       // consumer: [M, ln_slots] or NULL
+  int ln_slots;
+  const float* ln_s;            // consumer: [N] fp32
+  float ln_inv_c;               // 1 / channels of the normalised axis
+  float ln_eps;
   // K-range partitioning (split-K / stream-K) for layers whose output tiles do not fill the 148 SMs evenly: the
   // tiles x K-chunks index space is cut into `range_ctas` equal contiguous ranges, one per CTA. A CTA whose range
   // covers only part of a tile's K dumps its fp32 partial into its own scratch slot; the LAST contributor of a tile

@@ -8,6 +8,8 @@ layouts are ours. No layer falls back to torch arithmetic.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
@@ -93,6 +95,8 @@ class Conv2d(Layer):
         nb, h, w, _ = x.shape
         if self.k == 1:
             y = ops.conv_gemm(x, self.w, self.cout, a1=x1, bias=self.b, nb=1, h=1, w=nb * h * w, **kw)
+            if kw.get("want_stats"):
+                return y[0].view(nb, h, w, -1), y[1]
             return y.view(nb, h, w, -1) if y is not None else None
         if self.stride == 2:
             ph = ops.resample(x, 2)
@@ -134,6 +138,21 @@ class Norm(Layer):
     def _load(self, sd, prefix, dev):
         self.g = self._get(sd, prefix + "weight", (self.c,)).to(dev, torch.float32).contiguous()
         self.b = self._get(sd, prefix + "bias", (self.c,)).to(dev, torch.float32).contiguous()
+
+
+LN_EPS = 1e-5   # nn.LayerNorm default (attention.py:226-228)
+
+
+def fold_layernorm(w32, bias, norm):
+    """LayerNorm folded into the Linear that consumes it: y = LN(x) W^T + b
+         = rstd * (x (W*gamma)^T - mean * s) + t,  s[n] = sum_k (W*gamma)[n,k],  t[n] = sum_k beta[k] W[n,k] + b[n].
+    Returns (W*gamma as bf16, s from the bf16-rounded weights (what the tensor core multiplies), t), fp32 vectors."""
+    wf = (w32 * norm.g[None, :]).to(bf16).contiguous()
+    s = wf.float().sum(1).contiguous()
+    t = w32 @ norm.b
+    if bias is not None:
+        t = t + bias
+    return wf, s, t.contiguous()
 
 
 class Seq(Layer):
@@ -194,13 +213,21 @@ class CrossAttention(Layer):
         self.to_v = self.add("to_v", Linear(cdim, inner, bias=False))
         self.to_out = self.add("to_out", Seq({0: Linear(inner, query_dim)}))
 
+    ln = None         # the nn.LayerNorm in front of this attention (set by BasicTransformerBlock before load)
+    ln_fold = False   # True: the LayerNorm is folded into the q / qkv projection (fold_layernorm)
+
     def load(self, sd, prefix, dev):
         super().load(sd, prefix, dev)
         q, k, v = self.to_q.w32, self.to_k.w32, self.to_v.w32
-        if self.is_self:
-            self.w_qkv = torch.cat([q, k, v], 0).to(bf16).contiguous()
+        wq = torch.cat([q, k, v], 0) if self.is_self else q           # K/V of cross-attention project the text context
+        if self.ln_fold:
+            wq, self.ln_s, self.ln_t = fold_layernorm(wq, None, self.ln)
         else:
-            self.w_q = q.to(bf16).contiguous()
+            wq, self.ln_s, self.ln_t = wq.to(bf16).contiguous(), None, None
+        if self.is_self:
+            self.w_qkv = wq
+        else:
+            self.w_q = wq
             self.w_kv = torch.cat([k, v], 0).to(bf16).contiguous()
         self.to_q.w32 = self.to_k.w32 = self.to_v.w32 = None
         self.to_out[0].pack()
@@ -215,26 +242,33 @@ class CrossAttention(Layer):
                       qkv=(None, k, vt, 1, self.heads, self.d, lp))
         return k, vt, L
 
-    def forward(self, xn, resid, nimg, ntok, kv=None):
-        """xn: normalised tokens [nimg*ntok, C]; resid: tokens added after to_out. kv: projected context."""
-        dev = xn.device
+    def forward(self, x, stats, nimg, ntok, kv=None, want_stats=False):
+        """x + to_out(attention(LayerNorm(x))). x: RAW tokens [nimg*ntok, C]; with ln_fold the LayerNorm happens inside
+        the q/k/v projection from `stats` (per-row partial sums written by the GEMM that produced x), otherwise in the
+        LayerNorm kernel. want_stats: also return the statistics of the result for the next folded LayerNorm."""
+        dev = x.device
+        if self.ln_fold:
+            xn, kw = x, dict(bias=self.ln_t, ln=(stats, self.ln_s, x.shape[-1], LN_EPS))
+        else:
+            xn, kw = ops.layernorm(x, self.ln.g, self.ln.b), {}
         q = torch.empty((nimg, self.heads, ntok, self.d), device=dev, dtype=bf16)
         if self.is_self:
             tp = (ntok + 7) // 8 * 8
             k = torch.empty((nimg, self.heads, ntok, self.d), device=dev, dtype=bf16)
             vt = torch.empty((nimg, self.heads, self.d, tp), device=dev, dtype=bf16)
             ops.conv_gemm(xn, self.w_qkv, 3 * self.inner, out_mode=OUT_QKV, rows_per_img=ntok,
-                          qkv=(q, k, vt, 0, self.heads, self.d, tp))
+                          qkv=(q, k, vt, 0, self.heads, self.d, tp), **kw)
             nk = ntok
         else:
             k, vt, nk = kv
             tp = vt.shape[-1]
             ops.conv_gemm(xn, self.w_q, self.inner, out_mode=OUT_QKV, rows_per_img=ntok,
-                          qkv=(q, q, q, 0, self.heads, self.d, tp))
+                          qkv=(q, q, q, 0, self.heads, self.d, tp), **kw)
         a = torch.empty((nimg * ntok, self.inner), device=dev, dtype=bf16)
         ops.attention(q, k, vt, a, nimg, self.heads, ntok, nk, self.d, tp)
         o = self.to_out[0]
-        return ops.conv_gemm(a, o.w, o.cout, bias=o.b, res0=resid)
+        y = ops.conv_gemm(a, o.w, o.cout, bias=o.b, res0=x, want_stats=want_stats)
+        return y if want_stats else (y, None)
 
 
 class GEGLU(Layer):
@@ -243,9 +277,18 @@ class GEGLU(Layer):
         self.inner = inner
         self.proj = self.add("proj", Linear(dim, 2 * inner))
 
+    ln = None         # norm3 of the owning BasicTransformerBlock
+    ln_fold = False   # True: norm3 is folded into the projection
+
     def load(self, sd, prefix, dev):
         super().load(sd, prefix, dev)
-        self.w, self.b = ops.pack_geglu(self.proj.w32, self.proj.b)
+        w, b = self.proj.w32, self.proj.b
+        self.ln_s = None
+        if self.ln_fold:
+            wg = w * self.ln.g[None, :]
+            _, self.ln_s = ops.pack_geglu(wg, wg.to(bf16).float().sum(1))    # row sums of the bf16 weights, interleaved alike
+            w, b = wg, w @ self.ln.b + b                                      # gamma-folded weights, bias = beta.W^T + b
+        self.w, self.b = ops.pack_geglu(w, b)
         self.proj.w32 = None
 
 
@@ -259,11 +302,15 @@ class FeedForward(Layer):
         super().load(sd, prefix, dev)
         self.net[2].pack()
 
-    def forward(self, xn, resid):
+    def forward(self, x, stats):
+        """x + net(LayerNorm(x)); the LayerNorm (norm3) is folded into the GEGLU projection or a kernel of its own."""
         g = self.net[0]
-        h = ops.conv_gemm(xn, g.w, 2 * g.inner, bias=g.b, out_mode=OUT_GEGLU)      # x * gelu(gate)
+        if g.ln_fold:
+            h = ops.conv_gemm(x, g.w, 2 * g.inner, bias=g.b, out_mode=OUT_GEGLU, ln=(stats, g.ln_s, x.shape[-1], LN_EPS))
+        else:
+            h = ops.conv_gemm(ops.layernorm(x, g.ln.g, g.ln.b), g.w, 2 * g.inner, bias=g.b, out_mode=OUT_GEGLU)
         o = self.net[2]
-        return ops.conv_gemm(h, o.w, o.cout, bias=o.b, res0=resid)
+        return ops.conv_gemm(h, o.w, o.cout, bias=o.b, res0=x)
 
 
 class BasicTransformerBlock(Layer):
@@ -276,11 +323,32 @@ class BasicTransformerBlock(Layer):
         self.norm2 = self.add("norm2", Norm(dim))
         self.norm3 = self.add("norm3", Norm(dim))
 
-    def forward(self, t, nimg, ntok, kv):
-        """BasicTransformerBlock._forward, attention.py:234-240."""
-        t = self.attn1.forward(ops.layernorm(t, self.norm1.g, self.norm1.b), t, nimg, ntok)
-        t = self.attn2.forward(ops.layernorm(t, self.norm2.g, self.norm2.b), t, nimg, ntok, kv)
-        return self.ff.forward(ops.layernorm(t, self.norm3.g, self.norm3.b), t)
+    # Which LayerNorms are folded into the GEMM that consumes them (fold_layernorm). The fold moves work into GEMM
+    # epilogues; the K = 320 projections of the 64x64 level are epilogue-bound already, and there the fold into the wide
+    # q/k/v and GEGLU projections costs more than the LayerNorm kernel it removes (tools/bench_lnfold.py).
+    FOLD_MIN_DIM = int(os.environ.get("FGDM_LN_FOLD_MIN", "640"))
+
+    def load(self, sd, prefix, dev):
+        for n in ("norm1", "norm2", "norm3"):
+            self.children[n].load(sd, prefix + n + ".", dev)
+        wide = self.norm1.c >= self.FOLD_MIN_DIM
+        for consumer, norm, fold in ((self.attn1, self.norm1, wide), (self.attn2, self.norm2, True),
+                                     (self.ff.net[0], self.norm3, wide)):
+            consumer.ln, consumer.ln_fold = norm, fold
+        for n in ("attn1", "ff", "attn2"):
+            self.children[n].load(sd, prefix + n + ".", dev)
+
+    @property
+    def wants_stats(self):
+        """Does the GEMM that produces this block's input have to write LayerNorm statistics?"""
+        return self.attn1.ln_fold
+
+    def forward(self, t, stats, nimg, ntok, kv):
+        """BasicTransformerBlock._forward, attention.py:234-240. `stats`: per-row {sum, sumsq} partials of t written by
+        the GEMM that produced it; each residual GEMM hands the next folded LayerNorm its statistics the same way."""
+        t, stats = self.attn1.forward(t, stats, nimg, ntok, want_stats=self.attn2.ln_fold)
+        t, stats = self.attn2.forward(t, stats, nimg, ntok, kv, want_stats=self.ff.net[0].ln_fold)
+        return self.ff.forward(t, stats)
 
 
 class SpatialTransformer(Layer):
@@ -301,8 +369,9 @@ class SpatialTransformer(Layer):
         """SpatialTransformer.forward attention.py:275-292; GroupNorm eps 1e-6 (attention.py:76-77)."""
         nb, h, w, c = x.shape
         xn = ops.groupnorm(x, self.norm.g, self.norm.b, eps=1e-6, silu=False)
-        t = self.proj_in.gemm(xn).view(nb * h * w, -1)
-        t = self.blocks[0].forward(t, nb, h * w, kvs[self.kv_slot])
+        blk = self.blocks[0]
+        t, stats = self.proj_in.gemm(xn, want_stats=True) if blk.wants_stats else (self.proj_in.gemm(xn), None)
+        t = blk.forward(t.view(nb * h * w, -1), stats, nb, h * w, kvs[self.kv_slot])
         return self.proj_out.gemm(t.view(nb, h, w, -1), res0=x, res1=res1)
 
 

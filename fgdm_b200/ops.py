@@ -77,11 +77,15 @@ def count_launches(n: int) -> None:
 
 def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None, bias=None, rowvec=None,
               rows_per_img=0, res0=None, res1=None, alpha=1.0, act=ACT_NONE, out_mode=OUT_BF16, out=None,
-              ldo=None, col_off=0, qkv=None, bn_hint=0, n_store=0, res1_rows=0):
+              ldo=None, col_off=0, qkv=None, bn_hint=0, n_store=0, res1_rows=0, want_stats=False, ln=None):
     """Implicit-GEMM conv / Linear. a0 (and a1) are NHWC bf16 `[nb, h, w, c]` or token `[rows, c]` tensors.
 
     For CONV_3X3_S2, a0 is the phase-split tensor `[4, nb, h, w, c]` (see resample(mode=2)) and
     (nb, h, w) describe the OUTPUT. Returns the output tensor (or None in QKV mode).
+
+    Folded LayerNorm (see include/fgdm_b200.h): `want_stats=True` makes a bf16-output GEMM also return the per-row
+    partial statistics of its output, `(out, stats[m, slots, 2] fp32)`; a consumer passes
+    `ln=(stats, ln_s[n] fp32, channels, eps)` together with gamma-folded weights and `bias = beta.W^T + b`.
     """
     c0 = a0.shape[-1]
     c1 = a1.shape[-1] if a1 is not None else 0
@@ -126,11 +130,22 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
         elif ldo is None:
             ldo = out.shape[-1]
         args.out, args.ldo, args.col_off = _p(out), ldo, col_off
+    if ln is not None:
+        st, ln_s, ln_c, ln_eps = ln
+        args.ln_stats, args.ln_slots, args.ln_s = _p(st), st.shape[1], _p(ln_s)
+        args.ln_channels, args.ln_eps = ln_c, ln_eps
+    stats = None
+    if want_stats:
+        slots = _lib.load().fgdm_gemm_stats_slots(C.byref(args))
+        if slots <= 0:
+            raise RuntimeError("fgdm_gemm_stats_slots: " + _lib.last_error())
+        stats = torch.empty((m, slots, 2), device=a0.device, dtype=torch.float32)
+        args.row_stats = _p(stats)
     kdim = (9 if conv != CONV_1X1 else 1) * (c0 + c1)
     nres = (res0 is not None) + (res1 is not None)
     _call("fgdm_conv_gemm", ("gemm taps=%d m=%d k=%d n=%d" % (9 if conv != CONV_1X1 else 1, m, kdim, n), 2.0 * m * n * kdim,
                              2.0 * (m * (c0 + c1) + n * kdim + m * n * (1 + nres))), C.byref(args), _stream())
-    return out
+    return (out, stats) if want_stats else out
 
 
 def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):

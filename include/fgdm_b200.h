@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define FGDM_ABI_VERSION 3
+#define FGDM_ABI_VERSION 4
 
 const char* fgdm_last_error(void);
 int fgdm_abi_version(void);
@@ -88,11 +88,23 @@ typedef struct {
   int n_store;             /* FGDM_OUT_NCHW_F32: real output channels (weights zero-padded to n) */
   int res1_rows;           /* > 0: res1 has only this many rows and row m reads res1[m % res1_rows] (the FG-DM adapter
                             * features are identical for the cond and uncond CFG halves, openaimodel.py:836-857) */
+  /* LayerNorm folded into the Linear that consumes it (attention.py:226-240). Producer: row_stats != NULL makes a
+   * bf16-output GEMM also write per-row partial {sum, sumsq} of its output: [M, stats_slots] float2 with
+   * stats_slots = fgdm_gemm_stats_slots(M, N, ...) = 2 * n_tiles. Consumer: ln_stats/ln_slots/ln_s turn the epilogue
+   * into v = rstd*(acc - mean*ln_s[n]) + bias[n] (weights pre-multiplied by gamma, bias = beta.W^T + b). */
+  void* row_stats;
+  const void* ln_stats;
+  int ln_slots;
+  const float* ln_s;
+  int ln_channels;
+  float ln_eps;
 } fgdm_gemm_args;
 
 /* nn.Conv2d / nn.Linear call sites: openaimodel.py:224,250,261,112,164-166; attention.py:40,60,
  * 161-168,258-273; adapter.py:285-293; cldm.py:789-790; model.py:92-119. tcgen05 implicit GEMM. */
 int fgdm_conv_gemm(const fgdm_gemm_args* args, void* stream);
+/* number of row_stats slots per row that fgdm_conv_gemm will write for these args (2 x the number of N tiles it picks) */
+int fgdm_gemm_stats_slots(const fgdm_gemm_args* args);
 
 /* CrossAttention core (attention.py:189-202; controlnet/ldm/modules/attention.py:171-190).
  * q [images, heads, nq, d], k [images, heads, nk, d], vt [images, heads, d, tok_pad], out [images, nq, heads*d]. */

@@ -151,6 +151,61 @@ def test_geglu():
     assert relerr(y, a * F.gelu(g)) < 1e-2
 
 
+@pytest.mark.parametrize("m,k0,c", [(4096, 320, 320), (1024, 640, 640), (256, 1280, 1280), (200, 3072, 1280), (1000, 64, 320)])
+def test_layernorm_folded_into_gemm(m, k0, c):
+    """LayerNorm -> Linear as one GEMM: the producing GEMM writes per-row {sum, sumsq} partials, the consumer applies
+    rstd * (acc - mean * s[n]) + t[n] with gamma folded into its weights (BasicTransformerBlock, attention.py:234-240)."""
+    from types import SimpleNamespace
+    from fgdm_b200.layers import fold_layernorm, LN_EPS
+    heads, d = 8, c // 8
+    x0 = torch.randn(m, k0, device=DEV).to(torch.bfloat16)
+    w0 = (torch.randn(c, k0, device=DEV) / math.sqrt(k0)).to(torch.bfloat16)
+    b0 = torch.randn(c, device=DEV) + 1.5                      # DC offset: mean comparable to the spread
+    res = torch.randn(m, c, device=DEV).to(torch.bfloat16)
+    t, stats = ops.conv_gemm(x0, w0, c, bias=b0, res0=res, want_stats=True)
+    tref = x0.float() @ w0.float().t() + b0 + res.float()
+    assert relerr(t, tref) < 1e-2
+    tot = stats.sum(1)
+    assert torch.allclose(tot[:, 0], t.float().sum(1), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(tot[:, 1], (t.float() ** 2).sum(1), rtol=1e-4, atol=1e-2)
+
+    norm = SimpleNamespace(g=torch.randn(c, device=DEV) * 0.3 + 1.0, b=torch.randn(c, device=DEV) * 0.2)
+    xn = F.layer_norm(t.float(), (c,), norm.g, norm.b, LN_EPS)
+    ln = lambda s: (stats, s, c, LN_EPS)
+
+    # plain Linear with bias
+    w = torch.randn(c, c, device=DEV) / math.sqrt(c)
+    b = torch.randn(c, device=DEV)
+    wf, s, tb = fold_layernorm(w, b, norm)
+    y = ops.conv_gemm(t, wf, c, bias=tb, ln=ln(s))
+    assert relerr(y, xn @ w.t() + b) < 1.5e-2
+
+    # q/k/v projection (head-major layouts), no bias in the reference layer
+    if m % 16 == 0:
+        images, n = 2, m // 2
+        w = torch.randn(3 * c, c, device=DEV) / math.sqrt(c)
+        wf, s, tb = fold_layernorm(w, None, norm)
+        q = torch.empty(images, heads, n, d, device=DEV, dtype=torch.bfloat16)
+        k = torch.empty_like(q)
+        vt = torch.empty(images, heads, d, n, device=DEV, dtype=torch.bfloat16)
+        ops.conv_gemm(t, wf, 3 * c, bias=tb, rows_per_img=n, out_mode=ops.OUT_QKV, qkv=(q, k, vt, 0, heads, d, n), ln=ln(s))
+        ref = (xn @ w.t()).view(images, n, 3, heads, d)
+        assert relerr(q, ref[:, :, 0].permute(0, 2, 1, 3)) < 1.5e-2
+        assert relerr(k, ref[:, :, 1].permute(0, 2, 1, 3)) < 1.5e-2
+        assert relerr(vt, ref[:, :, 2].permute(0, 2, 3, 1)) < 1.5e-2
+
+    # GEGLU
+    inner = 4 * c
+    w = torch.randn(2 * inner, c, device=DEV) / math.sqrt(c)
+    b = torch.randn(2 * inner, device=DEV)
+    wg = w * norm.g[None, :]
+    wi, bi = ops.pack_geglu(wg, w @ norm.b + b)
+    _, si = ops.pack_geglu(wg, wg.to(torch.bfloat16).float().sum(1))
+    y = ops.conv_gemm(t, wi, 2 * inner, bias=bi, out_mode=ops.OUT_GEGLU, ln=ln(si))
+    a, g = (xn @ w.t() + b).chunk(2, dim=-1)
+    assert relerr(y, a * F.gelu(g)) < 1.5e-2
+
+
 def _attn_ref(q, k, v, scale):
     s = torch.einsum("bhid,bhjd->bhij", q.float(), k.float()) * scale
     return torch.einsum("bhij,bhjd->bhid", s.softmax(-1), v.float())
