@@ -153,54 +153,66 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      WorkIter it(p, num_tiles, num_k, CTAS);
-      int tile, kc_begin, kc_end;
-      while (it.next(tile, kc_begin, kc_end)) {
-        const int m_tile = (tile / p.num_n_tiles) * CTAS + cta_rank;
-        const int n_tile = tile % p.num_n_tiles;
-        const int m0 = m_tile * kBM;
-        const int w0 = m0 % p.W;
-        const int hw = m0 / p.W;
-        const int h0 = hw % p.H;
-        const int n0 = hw / p.H;
-        for (int kc = kc_begin; kc < kc_end; ++kc) {
-          const int tap = kc / chunks_per_tap;
-          const int c = (kc - tap * chunks_per_tap) * kBK;
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+    // This loop is the pacing instruction stream of every tile narrower than 224 columns (ncu: the warp is busy, never
+    // waiting, while the MMA thread waits for data), so it is kept lean: the whole warp runs it converged, so that the
+    // loop state lives in uniform registers, one elected lane issues, and tap / channel advance incrementally (no
+    // division per chunk).
+    int stage = 0;
+    uint32_t phase = 0;
+    WorkIter it(p, num_tiles, num_k, CTAS);
+    int tile, kc_begin, kc_end;
+    const uint32_t full0 = smem_u32(&full_bar[0]);
+    const uint32_t leader_full0 = CTAS == 2 ? mapa_shared(full0, 0) : full0;
+    while (it.next(tile, kc_begin, kc_end)) {
+      const int m_tile = (tile / p.num_n_tiles) * CTAS + cta_rank;
+      const int n_tile = tile % p.num_n_tiles;
+      const int m0 = m_tile * kBM;
+      const int w0 = m0 % p.W;
+      const int hw = m0 / p.W;
+      const int h0 = hw % p.H;
+      const int n0 = hw / p.H;
+      const int brow = n_tile * BN + (CTAS == 2 ? static_cast<int>(cta_rank) * (BN / 2) : 0);
+      int tap = kc_begin / chunks_per_tap;
+      int c = (kc_begin - tap * chunks_per_tap) * kBK;       // channel offset inside the tap
+      int kcol = kc_begin * kBK;                             // column of the weight matrix
+      int cw = w0 + p.tap_dw[tap], ch = h0 + p.tap_dh[tap], cn = n0 + p.tap_dn[tap];
+      for (int kc = kc_begin; kc < kc_end; ++kc) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
           void* dst_a = smem_a + stage * Cfg::kABytes;
           void* dst_b = smem_b + stage * Cfg::kBBytes;
-          const int cw = w0 + p.tap_dw[tap];
-          const int ch = h0 + p.tap_dh[tap];
-          const int cn = n0 + p.tap_dn[tap];
+          const bool second = c >= p.C0;                     // virtual concat: channels past C0 come from the 2nd tensor
+          const CUtensorMap* ma = second ? &map_a1 : &map_a0;
+          const int ca = second ? c - p.C0 : c;
           if (CTAS == 2) {
             // both CTAs' bytes are credited to the LEADER's barrier, which expects the whole pair stage
-            const uint32_t bar = mapa_shared(smem_u32(&full_bar[stage]), 0);
+            const uint32_t bar = leader_full0 + stage * 8;
             if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
-            if (c < p.C0) tma_load_4d_pair(dst_a, &map_a0, bar, c, cw, ch, cn);
-            else tma_load_4d_pair(dst_a, &map_a1, bar, c - p.C0, cw, ch, cn);
-            tma_load_2d_pair(dst_b, &map_b, bar, kc * kBK, n_tile * BN + static_cast<int>(cta_rank) * (BN / 2));
+            tma_load_4d_pair(dst_a, ma, bar, ca, cw, ch, cn);
+            tma_load_2d_pair(dst_b, &map_b, bar, kcol, brow);
           } else {
             mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-            if (c < p.C0) {
-              tma_load_4d(dst_a, &map_a0, &full_bar[stage], c, cw, ch, cn);
-            } else {
-              tma_load_4d(dst_a, &map_a1, &full_bar[stage], c - p.C0, cw, ch, cn);
-            }
-            tma_load_2d(dst_b, &map_b, &full_bar[stage], kc * kBK, n_tile * BN);
+            tma_load_4d(dst_a, ma, &full_bar[stage], ca, cw, ch, cn);
+            tma_load_2d(dst_b, &map_b, &full_bar[stage], kcol, brow);
           }
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1;
-          }
+        }
+        __syncwarp();
+        kcol += kBK;
+        c += kBK;
+        if (c == ctot && kc + 1 < kc_end) {                  // next tap
+          c = 0;
+          ++tap;
+          cw = w0 + p.tap_dw[tap]; ch = h0 + p.tap_dh[tap]; cn = n0 + p.tap_dn[tap];
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0 && cta_rank == 0) {                     // pair mode: the leader CTA issues for both
+    // ===================== MMA issuer (warp-converged loop, one elected lane issues) =====================
+    if (cta_rank == 0) {                                  // pair mode: the leader CTA issues for both
       constexpr uint32_t idesc = make_idesc_bf16(kBM * CTAS, BN);
       int stage = 0;
       uint32_t phase = 0;
@@ -208,6 +220,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       uint32_t acc_phase = 0;
       WorkIter it(p, num_tiles, num_k, CTAS);
       int tile, kc_begin, kc_end;
+      const uint64_t da0 = make_desc_sw128(smem_u32(smem_a));
+      const uint64_t db0 = make_desc_sw128(smem_u32(smem_b));
       while (it.next(tile, kc_begin, kc_end)) {
         mbar_wait(&acc_empty[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -215,22 +229,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         for (int kc = kc_begin; kc < kc_end; ++kc) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint64_t da = make_desc_sw128(smem_u32(smem_a + stage * Cfg::kABytes));
-          const uint64_t db = make_desc_sw128(smem_u32(smem_b + stage * Cfg::kBBytes));
+          if (elect_one()) {
+            // descriptors address smem in 16-byte units: stage s is +s*bytes/16, 16 bf16 along K (32 B) is +2
+            const uint64_t da = da0 + static_cast<uint64_t>(stage * (Cfg::kABytes >> 4));
+            const uint64_t db = db0 + static_cast<uint64_t>(stage * (Cfg::kBBytes >> 4));
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in (addr>>4)
-            if (CTAS == 2) tc_mma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
-            else tc_mma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
+            for (int k = 0; k < kBK / 16; ++k) {
+              if (CTAS == 2) tc_mma_bf16_pair(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
+              else tc_mma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kc > kc_begin || k != 0) ? 1u : 0u);
+            }
+            // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+            if (CTAS == 2) tc_commit_pair(&empty_bar[stage]); else tc_commit(&empty_bar[stage]);
+            if (kc + 1 == kc_end) {                       // accumulator complete -> epilogue
+              if (CTAS == 2) tc_commit_pair(&acc_full[acc]); else tc_commit(&acc_full[acc]);
+            }
           }
-          // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
-          if (CTAS == 2) tc_commit_pair(&empty_bar[stage]); else tc_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        if (CTAS == 2) tc_commit_pair(&acc_full[acc]); else tc_commit(&acc_full[acc]);  // accumulator complete -> epilogue
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -390,6 +409,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
             if (on && m_warp + rr < p.M)
               dst[q] = *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m_warp + rr) * p.ld_res0 + col + ch * 8);
           }
+          if ((p.dbg & 1) && i + 1 < np && col + 64 < p.N && m_warp + lane < p.M)     // panel after that one: pull its rows into L1
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(p.res0 + static_cast<size_t>(m_warp + lane) * p.ld_res0 + col + 64));
         };
         uint4 rres[4];
         if (pre_res) load_res(0, rres);
@@ -813,6 +834,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     static int force = -1;
     if (force < 0) { const char* e = getenv("FGDM_RANGE_FORCE"); force = e ? atoi(e) : 0; }
     if (force > 0 && p.out_mode == kOutBf16 && bn_hint == 0 && split_buffers_ready() && BN >= 128) p.range_ctas = force;
+    { const char* e = getenv("FGDM_DBG"); p.dbg = e ? atoi(e) : 0; }
     if (getenv("FGDM_GEMM_DEBUG"))
       fprintf(stderr, "gemm M=%d N=%d chunks=%d -> BN=%d range_ctas=%d\n", p.M, p.N, num_k_chunks, BN, p.range_ctas);
   }
