@@ -409,8 +409,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
             if (on && m_warp + rr < p.M)
               dst[q] = *reinterpret_cast<const uint4*>(p.res0 + static_cast<size_t>(m_warp + rr) * p.ld_res0 + col + ch * 8);
           }
-          if ((p.dbg & 1) && i + 1 < np && col + 64 < p.N && m_warp + lane < p.M)     // panel after that one: pull its rows into L1
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(p.res0 + static_cast<size_t>(m_warp + lane) * p.ld_res0 + col + 64));
         };
         uint4 rres[4];
         if (pre_res) load_res(0, rres);
@@ -804,7 +802,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
       // (256: ~1450, 160: ~1050, 128: ~900 TFLOP/s chip-wide).
       // 224 (7 panels) serves N = 640 as 3 tiles at 95 % fill: a 256-class tile instead of four 160-wide ones
       static const int kBn[4] = {256, 224, 160, 128};
-      static const float kChunkNs[4] = {428.f, 385.f, 369.f, 345.f};
+      static const float kChunkNs[4] = {448.f, 393.f, 322.f, 287.f};   // tools/bench_bn.py: 1386 / 1380 / 1205 / 1083 TFLOP/s
       float best = 1e30f;
       const int sms = num_sms();
       const bool can_range = p.out_mode == kOutBf16 && split_buffers_ready();
@@ -834,17 +832,19 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     static int force = -1;
     if (force < 0) { const char* e = getenv("FGDM_RANGE_FORCE"); force = e ? atoi(e) : 0; }
     if (force > 0 && p.out_mode == kOutBf16 && bn_hint == 0 && split_buffers_ready() && BN >= 128) p.range_ctas = force;
-    { const char* e = getenv("FGDM_DBG"); p.dbg = e ? atoi(e) : 0; }
     if (getenv("FGDM_GEMM_DEBUG"))
       fprintf(stderr, "gemm M=%d N=%d chunks=%d -> BN=%d range_ctas=%d\n", p.M, p.N, num_k_chunks, BN, p.range_ctas);
   }
-  // CTA pairs (cta_group::2): a 2-cluster runs one 256-row MMA, each CTA staging half of the B tile. Measured on B200
-  // (tools/bench_bn.py, m=65536 k=2880 n=1280): +3.5 % at BN=256 (1308 -> 1353 TFLOP/s), +2 % at 160/224, and -5 % on
-  // the short-K linears (cluster launch), i.e. operand traffic is not what bounds these tiles; the path is kept,
-  // tested (bn_hint = 1000 + BN) and opt-in (FGDM_PAIR=1) rather than default.
-  static int pair_mode = -1;
-  if (pair_mode < 0) { const char* e = getenv("FGDM_PAIR"); pair_mode = e ? atoi(e) : 0; }
-  const int ctas = ((pair_mode || force_pair) && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
+  // CTA pairs (cta_group::2): a 2-cluster runs one 256-row MMA, each CTA staging half of the B tile, which cuts the
+  // L2->SM operand traffic per FLOP - the bound of this kernel once the producer loop is lean (every tile width moves
+  // ~110 GB/s per SM). Measured on B200 (tools/bench_bn.py, m=65536 k=2880 n=1280): BN=160 1198 -> 1328, 224 1291 ->
+  // 1391, 256 1360 -> 1450 TFLOP/s; in the UNet the 3x3 convs gain 7-19 %, K = 1920/2560 linears 10-13 %, K = 1280 is a
+  // wash and K <= 960 loses 6-16 % (cluster launch + pair hand-offs on a short K loop). Hence: pairs from 30 K chunks up.
+  // FGDM_PAIR=0 never, FGDM_PAIR=1 wherever the kernel allows it; bn_hint = 1000 + BN forces it (tests).
+  static int pair_mode = -2;
+  if (pair_mode == -2) { const char* e = getenv("FGDM_PAIR"); pair_mode = e ? atoi(e) : -1; }
+  const bool want_pair = force_pair || pair_mode == 1 || (pair_mode == -1 && num_k_chunks >= 30);
+  const int ctas = (want_pair && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
   if (p.range_ctas) {
     if (static_cast<size_t>(p.range_ctas) * 2 * kBM * BN * 4 > kSplitWsBytes) { set_error("gemm: range scratch too small"); return -1; }
     p.split_ws = g_split_ws;

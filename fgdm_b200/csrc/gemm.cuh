@@ -63,7 +63,6 @@ struct GemmParams {
   const float* ln_s;            // consumer: [N] fp32
   float ln_inv_c;               // 1 / channels of the normalised axis
   float ln_eps;
-  int dbg;                 // TEMP experiment switches (FGDM_DBG)
   // K-range partitioning (split-K / stream-K) for layers whose output tiles do not fill the 148 SMs evenly: the
   // tiles x K-chunks index space is cut into `range_ctas` equal contiguous ranges, one per CTA. A CTA whose range
   // covers only part of a tile's K dumps its fp32 partial into its own scratch slot; the LAST contributor of a tile

@@ -14,8 +14,8 @@ m, k = 65536, 2880 // 64 * 64
 for n in (1280, 2240):
     x = torch.randn(m, k, device="cuda").to(bf)
     w = (torch.randn(n, k, device="cuda") / k ** 0.5).to(bf)
-    for bn in (64, 128, 160, 224, 256):
-        if n % bn and not (bn == 224):
+    for bn in (64, 128, 160, 224, 256, 1160, 1224, 1256):     # 1000 + BN: CTA-pair kernel
+        if n % (bn % 1000) and not (bn % 1000 == 224):
             continue
         us = timeit(lambda: ops.conv_gemm(x, w, n, bn_hint=bn), n=5)
         print(f"lin m={m} k={k} n={n} BN={bn}: {us:8.1f} us {2.0 * m * k * n / us / 1e6:7.0f} TFLOP/s")
