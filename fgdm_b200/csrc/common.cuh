@@ -101,9 +101,8 @@ FGDM_DEVINL uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-FGDM_DEVINL float2 unpack_bf16x2(uint32_t u) {
-  __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
-  return __bfloat1622float2(v);
+FGDM_DEVINL float2 unpack_bf16x2(uint32_t u) {     // bf16 -> fp32 is a 16-bit shift: one SHL and one LOP per pair
+  return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
 }
 
 // ----------------------------------------------------------------------------------------------

@@ -78,6 +78,10 @@ struct WorkIter {
     }
     return true;
   }
+  FGDM_DEVINL int peek_tile() const {      // the tile the following next() will return (-1: none)
+    if (cur >= end) return -1;
+    return range ? cur / num_k : cur;
+  }
   FGDM_DEVINL int range_begin(int cta) const { return static_cast<int>(static_cast<long long>(cta) * T / range); }
   FGDM_DEVINL int owner(int c) const {     // the CTA whose range contains chunk index c
     int i = static_cast<int>(static_cast<long long>(c) * range / T);
@@ -277,6 +281,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     WorkIter it(p, num_tiles, num_k, CTAS);
     int tile, kc_begin, kc_end;
     bool first_seg = true;
+    float bias_pf[kMaxP];                                        // bias panels of the next tile (prefetched)
+    int bias_pf_ntile = -1;
+#pragma unroll
+    for (int i = 0; i < kMaxP; ++i) bias_pf[i] = 0.0f;
     while (it.next(tile, kc_begin, kc_end)) {
       const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
       const int my_slot = first_seg ? 0 : 1;
@@ -286,7 +294,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       const int m_warp = m_tile * kBM + quarter * 32;   // first row of this warp
       const int m = m_warp + lane;
       const bool row_ok = m < p.M;
-      const int img = row_ok ? (m / p.rows_per_img) : 0;
+      int img = 0;                                             // image of this row: only some epilogues need the division
+      if (row_ok && (p.rowvec || p.out_mode == kOutQkv || p.out_mode == kOutNchwF32)) img = m / p.rows_per_img;
       const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
       // folded LayerNorm: this row's mean / rstd from the producer GEMM's partial sums (fixed slot order)
       float ln_rstd = 1.0f, ln_rm = 0.0f;                      // rstd and rstd * mean
@@ -412,13 +421,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         };
         uint4 rres[4];
         if (pre_res) load_res(0, rres);
-        if (p.bias) {     // bias (and folded-LN column sums): all loads first, then the smem stores
+        if (p.bias) {
+          // bias panels -> smem. The loads for this CTA's NEXT tile are issued here and land while this tile is
+          // processed (4 registers): an epilogue-bound GEMM otherwise pays this latency on every tile.
           float bv[kMaxP], sv[kMaxP];
+          const bool have = bias_pf_ntile == n_tile;
 #pragma unroll
           for (int i = 0; i < kMaxP; ++i) {
             const int col = n_tile * BN + half * 32 + 64 * i;
             const bool on = i < np && col < p.N;
-            bv[i] = on ? __ldg(p.bias + col + lane) : 0.0f;
+            bv[i] = have ? bias_pf[i] : (on ? __ldg(p.bias + col + lane) : 0.0f);
             sv[i] = on && p.ln_stats ? __ldg(p.ln_s + col + lane) : 0.0f;
           }
 #pragma unroll
@@ -427,6 +439,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + i * 128 + lane * 4), "f"(bv[i]) : "memory");
               if (p.ln_stats)
                 asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + (4 + i) * 128 + lane * 4), "f"(sv[i]) : "memory");
+            }
+          }
+          const int nxt = it.peek_tile();
+          bias_pf_ntile = nxt < 0 ? -1 : nxt % p.num_n_tiles;
+          if (nxt >= 0) {
+#pragma unroll
+            for (int i = 0; i < kMaxP; ++i) {
+              const int col = bias_pf_ntile * BN + half * 32 + 64 * i;
+              bias_pf[i] = (i < np && col < p.N) ? __ldg(p.bias + col + lane) : 0.0f;
             }
           }
         }
