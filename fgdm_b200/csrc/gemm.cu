@@ -653,13 +653,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                 for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
               } else {  // kOutQkv
                 const int tok = m - img * p.rows_per_img;
+                // (section, head, channel) of the panel's first column by division, then advanced 8 columns at a time
+                // (dhead % 8 == 0: a group of 8 never straddles a head)
+                int sect = col / p.inner;                       // 0 q, 1 k, 2 v (after qkv_first)
+                int head = (col - sect * p.inner) / p.dhead;
+                int e = col - sect * p.inner - head * p.dhead;
+                sect += p.qkv_first;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                  const int cg = col + g * 8;
-                  const int sect = cg / p.inner + p.qkv_first;  // 0 q, 1 k, 2 v
-                  const int cc = cg % p.inner;
-                  const int head = cc / p.dhead;
-                  const int e = cc - head * p.dhead;
+                  if (g > 0) {
+                    e += 8;
+                    if (e >= p.dhead) {
+                      e = 0;
+                      if (++head == p.heads) { head = 0; ++sect; }
+                    }
+                  }
                   if (sect < 2) {
                     __nv_bfloat16* base = (sect == 0) ? p.q_out : p.k_out;
                     uint4* dst = reinterpret_cast<uint4*>(
