@@ -46,7 +46,7 @@ def make_ddim_sampling_parameters(alphacums, ddim_timesteps, eta, verbose=True):
 class _StepGraph:
     """One captured DDIM step for fixed (model, B, latent shape, context length, CFG on/off)."""
 
-    def __init__(self, model, B, shape, ctx_len, cfg, S_max=1000):
+    def __init__(self, model, B, shape, ctx_len, cfg, S_max=1000, pcond_rows=0):
         dev = model.device
         self.model, self.B, self.cfg = model, B, cfg
         self.R = 2 * B if cfg else B
@@ -70,6 +70,10 @@ class _StepGraph:
             self.guided = torch.zeros((B, H, W, model.control_model.model_channels), device=dev,
                                       dtype=torch.bfloat16)
             self.control_sig = (tuple(model.control_scales), model.only_mid_control)
+        # joint FG-DM factor: adapter features of the pcond latent, step-invariant (openaimodel.py:836-844)
+        self.fa = None
+        if pcond_rows:
+            self.fa = unet.encode_prompt(torch.zeros((pcond_rows, C, H, W), device=dev, dtype=torch.float32))
         self.graph = None
         self.launches_per_step = 0
 
@@ -78,9 +82,12 @@ class _StepGraph:
             k.copy_(k2)
             vt.copy_(vt2)
 
-    def set_conditioning(self, cond_ctx, uncond_ctx, hint=None):
+    def set_conditioning(self, cond_ctx, uncond_ctx, hint=None, pcond=None):
         """Hoisted, step-invariant work (once per sample call): attention.py:162-163 K/V projections of the
-        text context for every cross-attention; cldm.py:796 hint stem."""
+        text context for every cross-attention; cldm.py:796 hint stem; adapter features of a pcond latent."""
+        if self.fa is not None:
+            for dst, src in zip(self.fa, self.model.model.diffusion_model.encode_prompt(pcond.to(self.x.device))):
+                dst.copy_(src)
         if self.cfg:
             self.ctx[:self.B].copy_(uncond_ctx)          # rows [0,B) uncond, [B,2B) cond: ddim.py:226
             self.ctx[self.B:].copy_(cond_ctx)
@@ -98,7 +105,8 @@ class _StepGraph:
         if self.is_control:
             eps = m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R)
         else:
-            eps = m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R)
+            eps = m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R,
+                                                  adapter_features=self.fa)
         e_u = eps[:self.B]
         e_c = eps[self.B:] if self.cfg else None
         ops.cfg_ddim_step(e_u, e_c, self.x, self.coef, 0, self.scale, index_ptr=self.index, x_prev=self.x,
@@ -201,7 +209,8 @@ class DDIMSampler(object):
         return self.ddim_sampling(conditioning, size, callback=callback, img_callback=img_callback,
                                   temperature=temperature, x_T=x_T, log_every_t=log_every_t,
                                   unconditional_guidance_scale=unconditional_guidance_scale,
-                                  unconditional_conditioning=unconditional_conditioning, eta=eta)
+                                  unconditional_conditioning=unconditional_conditioning, eta=eta,
+                                  pcond=kwargs.get("pcond"))
 
     @staticmethod
     def _split_cond(c):
@@ -222,7 +231,9 @@ class DDIMSampler(object):
     @torch.no_grad()
     def ddim_sampling(self, cond, shape, x_T=None, callback=None, img_callback=None, log_every_t=100,
                       temperature=1., unconditional_guidance_scale=1., unconditional_conditioning=None, eta=0.,
-                      **kwargs):
+                      pcond=None, **kwargs):
+        """pcond: latent [P,4,h,w] of another factor for the adapter (ddpm.py:1536-1542 passes it down to
+        UNetModel.forward through apply_model's kwargs)."""
         model = self.model
         device = model.device
         b = shape[0]
@@ -238,12 +249,16 @@ class DDIMSampler(object):
                 and (hint_u is None or hint_u is hint_c or (hint_u.shape == hint_c.shape and torch.equal(hint_u, hint_c)))
                 and (not isinstance(model, ControlLDM) or hint_c is not None))
         if fast:
+            if pcond is not None and isinstance(model, ControlLDM):
+                raise NotImplementedError("pcond belongs to the FG-DM UNet (adapter), not to the ControlNet factor")
             key = (b, tuple(shape[1:]), ctx_c.shape[1], cfg,
-                   (tuple(model.control_scales), model.only_mid_control) if isinstance(model, ControlLDM) else None)
+                   (tuple(model.control_scales), model.only_mid_control) if isinstance(model, ControlLDM) else None,
+                   0 if pcond is None else pcond.shape[0])
             g = self._graphs.get(key)
             if g is None:
-                g = self._graphs[key] = _StepGraph(model, b, shape[1:], ctx_c.shape[1], cfg)
-            g.set_conditioning(ctx_c, ctx_u, hint_c)
+                g = self._graphs[key] = _StepGraph(model, b, shape[1:], ctx_c.shape[1], cfg,
+                                                   pcond_rows=0 if pcond is None else pcond.shape[0])
+            g.set_conditioning(ctx_c, ctx_u, hint_c, pcond)
             for i in g.run(img, time_range, self.coef_table, unconditional_guidance_scale if cfg else 1.0):
                 index = total_steps - i - 1
                 if callback:
@@ -262,7 +277,8 @@ class DDIMSampler(object):
             ts = torch.full((b,), int(step), device=device, dtype=torch.long)
             img, pred_x0 = self.p_sample_ddim(img, cond, ts, index=index, temperature=temperature,
                                               unconditional_guidance_scale=unconditional_guidance_scale,
-                                              unconditional_conditioning=unconditional_conditioning, coef=coef)
+                                              unconditional_conditioning=unconditional_conditioning, coef=coef,
+                                              **({} if pcond is None else {"pcond": pcond}))
             if callback:
                 callback(i)
             if img_callback:
@@ -282,16 +298,17 @@ class DDIMSampler(object):
         b = x.shape[0]
         if coef is None:
             coef = self.coef_table.to(x.device)
+        mk = {"pcond": kwargs["pcond"]} if kwargs.get("pcond") is not None else {}   # forwarded like ddim.py:192,241
         if unconditional_conditioning is None or unconditional_guidance_scale == 1.:
-            e_u, e_c = self.model.apply_model(x, t, c), None
+            e_u, e_c = self.model.apply_model(x, t, c, **mk), None
         elif isinstance(c, dict):                         # ddim_hacked.py:190-191: two sequential calls
-            e_c = self.model.apply_model(x, t, c)
-            e_u = self.model.apply_model(x, t, unconditional_conditioning)
+            e_c = self.model.apply_model(x, t, c, **mk)
+            e_u = self.model.apply_model(x, t, unconditional_conditioning, **mk)
         else:                                             # ddim.py:222-242: one batched call
             x_in = torch.cat([x] * 2)
             t_in = torch.cat([t] * 2)
             c_in = torch.cat([unconditional_conditioning, c])
-            e_u, e_c = self.model.apply_model(x_in, t_in, c_in).chunk(2)
+            e_u, e_c = self.model.apply_model(x_in, t_in, c_in, **mk).chunk(2)
         sigma = float(coef[index, 4])
         noise = torch.randn_like(x) if sigma != 0. else None     # ddim.py:265 (sigma = 0 when eta = 0)
         x_prev, pred_x0 = ops.cfg_ddim_step(e_u.float().contiguous(), None if e_c is None else e_c.float().contiguous(),

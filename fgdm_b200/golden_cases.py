@@ -70,6 +70,13 @@ def unet_case():
                 ctx=synth.randn((2, 77, 768), 22))
 
 
+def pcond_case():
+    """FG-DM joint ("pcond") factor: the adapter is fed by another factor's clean latent instead of the noisy latent
+    (openaimodel.py:836-844). One prompt, its two CFG rows: the reference's `h + fa[k]` broadcasts a 1-row feature."""
+    return dict(x=synth.randn((2, 4, 16, 16), 23), t=torch.tensor([621, 621], dtype=torch.int64),
+                ctx=synth.randn((2, 77, 768), 24), pcond=synth.randn((1, 4, 16, 16), 25))
+
+
 def ddim_case():
     return dict(S=5, B=1, shape=(4, 16, 16), scale=7.5, x_T=synth.randn((1, 4, 16, 16), 31),
                 c=synth.randn((1, 77, 768), 32), uc=synth.randn((1, 77, 768), 33))

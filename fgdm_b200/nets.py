@@ -265,19 +265,35 @@ class UNetModel(_UNetBase):
         else:
             self.adapter = None
 
-    def forward(self, x, timesteps=None, context=None, y=None, pcond=None, kv=None, rows=None, **kwargs):
+    def encode_prompt(self, pcond):
+        """Adapter features of a `pcond` latent (openaimodel.py:836-844: `prompt = pcond`): step-invariant, so the
+        sampler computes them once per sample call and hands them back through `adapter_features`."""
+        if self.adapter is None:
+            raise NotImplementedError("pcond needs the FG-DM adapter (no_prompting=False)")
+        pc = pcond.float().contiguous()
+        return self.adapter.forward(pc, pc.shape[0])
+
+    def forward(self, x, timesteps=None, context=None, y=None, pcond=None, kv=None, rows=None, adapter_features=None,
+                **kwargs):
         """x: fp32 [nb_in, 4, h, w]; rows >= nb_in output rows (row r reads x[r % nb_in] — lets the sampler
         feed ONE copy of x for the cond and uncond halves instead of the reference's torch.cat([x]*2),
-        ddim.py:222). timesteps: int64 [rows]; context [rows, L, 768] or kv = project_context(context)."""
-        if y is not None or pcond is not None:
-            raise NotImplementedError("class labels / pcond are outside the FG-DM sampling path")
+        ddim.py:222). timesteps: int64 [rows]; context [rows, L, 768] or kv = project_context(context).
+        pcond: fp32 [P, 4, h, w] latent of another factor fed to the adapter instead of x (the joint FG-DM factor);
+        row r takes the features of pcond[r % P] (P = 1 is the reference's broadcast of `h + fa[k]`)."""
+        if y is not None:
+            raise NotImplementedError("class labels are outside the FG-DM sampling path")
         x = x.float().contiguous()
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
         emb_all = self._emb(timesteps)
         # prompt = h (:836-844): the adapter sees only the latent, so its features are identical for the cond and
         # uncond CFG rows -> computed once per unique latent, added modulo by the GEMM epilogue (res1_rows)
-        fa = self.adapter.forward(x, x.shape[0]) if self.adapter is not None else None
+        if adapter_features is not None:
+            fa = adapter_features
+        elif self.adapter is not None:
+            fa = self.encode_prompt(pcond) if pcond is not None else self.adapter.forward(x, x.shape[0])
+        else:
+            fa = None
         h, hs = self._encode(x, rows, emb_all, kvs, fa)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
         return self._decode(h, hs, emb_all, kvs)

@@ -197,9 +197,10 @@ DEFAULT_UNET_CFG = dict(in_channels=4, out_channels=4, model_channels=320, atten
                         num_res_blocks=2, channel_mult=[1, 2, 4, 4], num_heads=8, context_dim=768)
 
 
-def unet_forward(sd, x, t, context, cfg=None, prefix="", adapter=True):
+def unet_forward(sd, x, t, context, cfg=None, prefix="", adapter=True, pcond=None):
     """FG-DM UNetModel.forward, openaimodel.py:808-884 (pcond=None => the adapter sees the noisy
-    latent itself, :836-844; features added after input blocks 2,5,8,11, :855-857).
+    latent itself, :836-844; pcond given => the adapter sees that tensor (another factor's latent) and its features
+    broadcast over the rows of h exactly as `h + fa[k]` does; features added after input blocks 2,5,8,11, :855-857).
     adapter=False restates forward_original (:753-806), the plain SD UNet."""
     cfg = cfg or DEFAULT_UNET_CFG
     p = prefix
@@ -207,7 +208,7 @@ def unet_forward(sd, x, t, context, cfg=None, prefix="", adapter=True):
     inputs, middle, outputs = unet_layout(cfg)
     emb = time_embed(sd, p, t, cfg["model_channels"])
     h = x.float()
-    fa = adapter_forward(sd, p + "adapter", h) if adapter else None
+    fa = adapter_forward(sd, p + "adapter", h if pcond is None else pcond.float()) if adapter else None
     hs = []
     k = 0
     for idx, kinds in enumerate(inputs):

@@ -6,7 +6,7 @@
 3. writes the reference's outputs as golden fixtures to tests/golden/*.npz (inputs are re-derived from
    the seeds stored alongside, weights from the weight seed).
 
-Usage: python oracle/make_golden.py [--only fgdm|control|misc]
+Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond]
 """
 from __future__ import annotations
 
@@ -84,6 +84,7 @@ def golden_fgdm():
         am = model.apply_model(case["x"], case["t"], case["ctx"], num=1)
         assert torch.equal(am, eps_ref)
         save("unet_fgdm", eps=eps_ref, weight_seed=gc.FGDM_WEIGHT_SEED)
+        golden_pcond(model, sd)
         # --- DDIM loop with CFG through the reference sampler
         from ldm.models.diffusion.ddim import DDIMSampler
         case = gc.ddim_case()
@@ -137,6 +138,23 @@ def golden_fgdm():
         img_orc = orc.vae_decode(sd, case["z"])
         check("decode_first_stage", img_orc, img_ref)
         save("vae_decode", img=img_ref)
+
+
+def golden_pcond(model=None, sd=None):
+    """UNetModel.forward(pcond=...) (openaimodel.py:836-844): the joint FG-DM factor's adapter input."""
+    if model is None:
+        model = rh.build_fgdm()
+        sd = load_weights(model, gc.fgdm_param_shapes(), gc.FGDM_WEIGHT_SEED)
+    unet = model.model.diffusion_model
+    with torch.no_grad():
+        case = gc.pcond_case()
+        eps_ref = unet(case["x"], case["t"], context=case["ctx"], pcond=case["pcond"])
+        eps_orc = orc.unet_forward(sd, case["x"], case["t"], case["ctx"], prefix="model.diffusion_model.",
+                                   pcond=case["pcond"])
+        check("UNetModel.forward(pcond)", eps_orc, eps_ref)
+        am = model.apply_model(case["x"], case["t"], case["ctx"], pcond=case["pcond"])
+        assert torch.equal(am, eps_ref)
+        save("unet_pcond", eps=eps_ref, weight_seed=gc.FGDM_WEIGHT_SEED)
 
 
 def golden_control():
@@ -225,6 +243,8 @@ if __name__ == "__main__":
         golden_misc()
     if a.only in ("all", "fgdm"):
         golden_fgdm()
+    if a.only == "pcond":
+        golden_pcond()
     if a.only in ("all", "control"):
         golden_control()
     print("golden fixtures written; oracle restatement agrees with the reference")

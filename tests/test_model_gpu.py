@@ -72,6 +72,32 @@ def test_unet_forward_vs_reference_golden(fgdm):
     assert relmax(eps, gold("unet_fgdm")["eps"]) < EPS_TOL
 
 
+def test_unet_pcond_vs_reference_golden(fgdm):
+    """Joint FG-DM factor: UNetModel.forward(pcond=...) through apply_model's kwargs (ddpm.py:1130, openaimodel.py:836-844)."""
+    import fgdm_oracle as orc
+    model, sd = fgdm
+    c = gc.pcond_case()
+    eps = model.apply_model(c["x"].to(DEV), c["t"].to(DEV), c["ctx"].to(DEV), pcond=c["pcond"].to(DEV))
+    assert relmax(eps, gold("unet_pcond")["eps"]) < EPS_TOL
+    # sampler: pcond features are hoisted out of the captured step; graph path == per-step apply_model path == oracle
+    d = gc.ddim_case()
+    pc = c["pcond"].to(DEV)
+    kw = dict(S=d["S"], conditioning=d["c"].to(DEV), batch_size=d["B"], shape=list(d["shape"]), verbose=False,
+              unconditional_guidance_scale=d["scale"], unconditional_conditioning=d["uc"].to(DEV), eta=0.0,
+              x_T=d["x_T"].to(DEV), pcond=pc)
+    x0, _ = DDIMSampler(model).sample(**kw)
+    x0b, _ = DDIMSampler(model, use_graph=False).sample(**kw)
+    assert relmax(x0b, x0) < 1e-2
+    with torch.no_grad():                                      # fp32 oracle chain, evaluated on the GPU
+        x0o, _ = orc.ddim_sample(
+            lambda x, t, cc: orc.unet_forward(sd, x, t, cc, prefix="model.diffusion_model.", pcond=pc),
+            d["S"], (d["B"],) + tuple(d["shape"]), kw["conditioning"], kw["unconditional_conditioning"], d["scale"],
+            kw["x_T"], model.alphas_cumprod)
+    assert psnr(x0, x0o, float(x0o.abs().max())) > 35.0
+    x0p, _ = DDIMSampler(model).sample(**{k: v for k, v in kw.items() if k != "pcond"})
+    assert relmax(x0p, x0) > 1e-2                              # and differs from the plain (pcond=None) chain
+
+
 def test_ddim_cfg_loop_vs_reference_golden(fgdm):
     model, _ = fgdm
     c, g = gc.ddim_case(), gold("ddim_fgdm")

@@ -45,6 +45,16 @@ def test_oracle_unet_matches_reference_golden(sd_fgdm):
     assert relmax(eps, gold("unet_fgdm")["eps"]) < 1e-4
 
 
+def test_oracle_unet_pcond_matches_reference_golden(sd_fgdm):
+    """UNetModel.forward(pcond=...) (openaimodel.py:836-844): adapter fed by another factor's latent."""
+    c = gc.pcond_case()
+    with torch.no_grad():
+        eps = orc.unet_forward(sd_fgdm, c["x"], c["t"], c["ctx"], prefix="model.diffusion_model.", pcond=c["pcond"])
+        plain = orc.unet_forward(sd_fgdm, c["x"], c["t"], c["ctx"], prefix="model.diffusion_model.")
+    assert relmax(eps, gold("unet_pcond")["eps"]) < 1e-4
+    assert relmax(plain, gold("unet_pcond")["eps"]) > 1e-2      # the pcond branch really changes the result
+
+
 def test_oracle_ddim_loop_matches_reference_golden(sd_fgdm):
     c, g = gc.ddim_case(), gold("ddim_fgdm")
     rec = []
