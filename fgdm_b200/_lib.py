@@ -49,6 +49,7 @@ SIGNATURES = {
     "fgdm_layernorm": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp],
     "fgdm_softmax_rows": [vp, vp, C.c_int, C.c_int, C.c_float, vp],
     "fgdm_cfg_ddim_step": [vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp, C.c_int, vp],
+    "fgdm_plms_step": [vp, vp, vp, vp, vp, C.POINTER(C.c_float), vp, vp, C.c_int, C.c_float, vp, vp, vp, C.c_int, vp],
     "fgdm_timestep_embedding": [vp, vp, vp, C.c_int, C.c_int, vp],
     "fgdm_skinny_linear": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_resample": [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],

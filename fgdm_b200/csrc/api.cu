@@ -106,6 +106,9 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
 int launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, int rows, int C, float eps,
                      cudaStream_t stream);
 int launch_softmax_rows(const float* s, void* p, int rows, int cols, float scale, cudaStream_t stream);
+int launch_plms_step(const float* e_u, const float* e_c, const float* h1, const float* h2, const float* h3,
+                     const float* w, const float* x, const float* coef_table, int index, float scale, float* e_out,
+                     float* x_prev, float* pred_x0, int n, cudaStream_t stream);
 int launch_cfg_ddim(const float* e_u, const float* e_c, const float* x, const float* noise, const float* coef_table,
                     const int* index_ptr, int index, float scale, float temperature, float* x_prev, float* pred_x0,
                     int n, cudaStream_t stream);
@@ -293,6 +296,19 @@ int fgdm_layernorm(const void* x, void* y, const float* gamma, const float* beta
 int fgdm_softmax_rows(const float* s, void* p, int rows, int cols, float scale, void* stream) {
   FGDM_NONNULL(s, "s"); FGDM_NONNULL(p, "p");
   return launch_softmax_rows(s, p, rows, cols, scale, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_plms_step(const float* e_uncond, const float* e_cond, const float* h1, const float* h2, const float* h3,
+                   const float* weights, const float* x, const float* coef_table, int index, float scale, float* e_out,
+                   float* x_prev, float* pred_x0, int n, void* stream) {
+  FGDM_NONNULL(e_uncond, "e_uncond"); FGDM_NONNULL(x, "x"); FGDM_NONNULL(coef_table, "coef_table");
+  FGDM_NONNULL(x_prev, "x_prev"); FGDM_NONNULL(weights, "weights");
+  if ((weights[1] != 0.0f && !h1) || (weights[2] != 0.0f && !h2) || (weights[3] != 0.0f && !h3)) {
+    set_error("fgdm_plms_step: a non-zero weight needs its history tensor");
+    return -2;
+  }
+  return launch_plms_step(e_uncond, e_cond, h1, h2, h3, weights, x, coef_table, index, scale, e_out, x_prev, pred_x0, n,
+                          reinterpret_cast<cudaStream_t>(stream));
 }
 
 int fgdm_cfg_ddim_step(const float* e_uncond, const float* e_cond, const float* x, const float* noise,

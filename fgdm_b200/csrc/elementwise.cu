@@ -56,6 +56,56 @@ int launch_cfg_ddim(const float* e_u, const float* e_c, const float* x, const fl
 }
 
 // ---------------------------------------------------------------------------------------------
+// PLMS step (ldm/models/diffusion/plms.py:172-236): CFG combine, Adams-Bashforth blend with up to three earlier
+// eps, then the same x_{t-1} update as DDIM with eta = 0 (plms.py:22-23 asserts it):
+//   e_t     = e_u + s * (e_c - e_u)                        (written to e_out: the sampler's `old_eps` entry)
+//   e_prime = w0 * e_t + w1 * h1 + w2 * h2 + w3 * h3        (w = {1}, {1/2,1/2}, {3/2,-1/2}, {23,-16,5}/12, {55,-59,37,-9}/24)
+//   x0      = (x - sqrt(1 - a_t) * e_prime) / sqrt(a_t);  x_prev = sqrt(a_prev) * x0 + sqrt(1 - a_prev) * e_prime
+// ---------------------------------------------------------------------------------------------
+__global__ void plms_step_kernel(const float* __restrict__ e_u, const float* __restrict__ e_c,
+                                 const float* __restrict__ h1, const float* __restrict__ h2,
+                                 const float* __restrict__ h3, float w0, float w1, float w2, float w3,
+                                 const float* __restrict__ x, const float* __restrict__ coef_table, int index,
+                                 float scale, float* __restrict__ e_out, float* __restrict__ x_prev,
+                                 float* __restrict__ pred_x0, int n) {
+  const float* cf = coef_table + 5 * index;
+  const float s1m = cf[0], sa = cf[1], sap = cf[2], dir = cf[3];
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 eu = *reinterpret_cast<const float4*>(e_u + i);
+  const float4 ec = e_c ? *reinterpret_cast<const float4*>(e_c + i) : eu;
+  const float4 a1 = h1 ? *reinterpret_cast<const float4*>(h1 + i) : zero;
+  const float4 a2 = h2 ? *reinterpret_cast<const float4*>(h2 + i) : zero;
+  const float4 a3 = h3 ? *reinterpret_cast<const float4*>(h3 + i) : zero;
+  const float4 xv = *reinterpret_cast<const float4*>(x + i);
+  const float eua[4] = {eu.x, eu.y, eu.z, eu.w}, eca[4] = {ec.x, ec.y, ec.z, ec.w}, xa[4] = {xv.x, xv.y, xv.z, xv.w};
+  const float h1a[4] = {a1.x, a1.y, a1.z, a1.w}, h2a[4] = {a2.x, a2.y, a2.z, a2.w}, h3a[4] = {a3.x, a3.y, a3.z, a3.w};
+  float et[4], xp[4], p0[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    et[k] = eua[k] + scale * (eca[k] - eua[k]);
+    const float ep = w0 * et[k] + w1 * h1a[k] + w2 * h2a[k] + w3 * h3a[k];
+    p0[k] = (xa[k] - s1m * ep) / sa;
+    xp[k] = sap * p0[k] + dir * ep;
+  }
+  if (e_out) *reinterpret_cast<float4*>(e_out + i) = make_float4(et[0], et[1], et[2], et[3]);
+  *reinterpret_cast<float4*>(x_prev + i) = make_float4(xp[0], xp[1], xp[2], xp[3]);
+  if (pred_x0) *reinterpret_cast<float4*>(pred_x0 + i) = make_float4(p0[0], p0[1], p0[2], p0[3]);
+}
+
+int launch_plms_step(const float* e_u, const float* e_c, const float* h1, const float* h2, const float* h3,
+                     const float* w, const float* x, const float* coef_table, int index, float scale, float* e_out,
+                     float* x_prev, float* pred_x0, int n, cudaStream_t stream) {
+  if (n % 4 != 0) { set_error("plms_step: n=%d must be a multiple of 4", n); return -1; }
+  const int threads = 256;
+  const int blocks = (n / 4 + threads - 1) / threads;
+  plms_step_kernel<<<blocks, threads, 0, stream>>>(e_u, e_c, h1, h2, h3, w[0], w[1], w[2], w[3], x, coef_table, index,
+                                                   scale, e_out, x_prev, pred_x0, n);
+  return check_launch("plms_step_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
 // Device-side loop bookkeeping (ddim.py:147-149) so a captured graph can be replayed per step.
 // ---------------------------------------------------------------------------------------------
 __global__ void ddim_advance_kernel(int* counter, const long long* __restrict__ t_table,

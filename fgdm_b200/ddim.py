@@ -99,18 +99,40 @@ class _StepGraph:
             self._refill(self.kv_ctrl, self.model.control_model.project_context(self.ctx))
             self.guided.copy_(self.model.control_model.encode_hint(hint))
 
-    def _step(self):
+    def _eps(self):
+        """The model call of one step on the static buffers: eps for the R CFG rows of (self.x, self.t)."""
         m = self.model
-        ops.ddim_advance(self.counter, self.t_table, self.idx_table, self.t, self.index)
         if self.is_control:
-            eps = m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R)
-        else:
-            eps = m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R,
-                                                  adapter_features=self.fa)
+            return m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R)
+        return m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R, adapter_features=self.fa)
+
+    def _step(self):
+        ops.ddim_advance(self.counter, self.t_table, self.idx_table, self.t, self.index)
+        eps = self._eps()
         e_u = eps[:self.B]
         e_c = eps[self.B:] if self.cfg else None
         ops.cfg_ddim_step(e_u, e_c, self.x, self.coef, 0, self.scale, index_ptr=self.index, x_prev=self.x,
                           pred_x0=self.pred_x0)
+
+    def eval_eps(self, t):
+        """Multi-step samplers (PLMS): replay a captured graph of the model call alone at timestep t on self.x.
+        Returns (e_uncond, e_cond) views of the graph's static output (valid until the next replay)."""
+        if getattr(self, "eps_graph", None) is None:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                n0 = ops.launch_count()
+                self._eps()                                   # eager warm-up (function attributes, allocator)
+                self.eps_launches = ops.launch_count() - n0
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            self.eps_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.eps_graph):
+                self.eps_out = self._eps()
+        self.t.fill_(int(t))
+        self.eps_graph.replay()
+        ops.count_launches(self.eps_launches)
+        return self.eps_out[:self.B], (self.eps_out[self.B:] if self.cfg else None)
 
     def capture(self, scale):
         self.scale = float(scale)

@@ -82,6 +82,12 @@ def ddim_case():
                 c=synth.randn((1, 77, 768), 32), uc=synth.randn((1, 77, 768), 33))
 
 
+def plms_case():
+    """PLMS (plms.py): 6 steps exercise the Euler start and the Adams-Bashforth orders 2, 3, 4."""
+    return dict(S=6, B=1, shape=(4, 16, 16), scale=7.5, x_T=synth.randn((1, 4, 16, 16), 34),
+                c=synth.randn((1, 77, 768), 35), uc=synth.randn((1, 77, 768), 36))
+
+
 def vae_case():
     return dict(z=synth.randn((1, 4, 16, 16), 41) * 0.18215 * 3.0)
 

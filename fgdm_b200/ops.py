@@ -203,6 +203,21 @@ def cfg_ddim_step(e_uncond, e_cond, x, coef_table, index, scale, *, noise=None, 
     return x_prev, pred_x0
 
 
+def plms_step(e_uncond, e_cond, hist, weights, x, coef_table, index, scale, *, e_out=None, x_prev=None, pred_x0=None):
+    """hist: [old_eps[-1], old_eps[-2], old_eps[-3]] (shorter lists allowed); weights: 4 floats (e_t first)."""
+    import ctypes as C
+    if x_prev is None:
+        x_prev = torch.empty_like(x)
+    if pred_x0 is None:
+        pred_x0 = torch.empty_like(x)
+    h = list(hist) + [None] * (3 - len(hist))
+    w = (C.c_float * 4)(*[float(v) for v in weights])
+    _call("fgdm_plms_step", ("plms_step", 0.0, 4.0 * (4 + len(hist)) * x.numel()), _p(e_uncond), _p(e_cond), _p(h[0]), _p(h[1]),
+          _p(h[2]), w, _p(x), _p(coef_table), int(index), float(scale), _p(e_out), _p(x_prev), _p(pred_x0), x.numel(),
+          _stream())
+    return x_prev, pred_x0
+
+
 def timestep_embedding(t, freqs, dim):
     out = torch.empty((t.shape[0], dim), device=t.device, dtype=torch.float32)
     _call("fgdm_timestep_embedding", ("temb", 0.0, 4.0 * t.shape[0] * dim), _p(t), _p(freqs), _p(out), t.shape[0], dim, _stream())

@@ -129,6 +129,14 @@ int fgdm_cfg_ddim_step(const float* e_uncond, const float* e_cond, const float* 
                        const float* coef_table, const int* index_ptr, int index, float scale, float temperature,
                        float* x_prev, float* pred_x0, int n, void* stream);
 
+/* PLMS step: plms.py:172-236 (PLMSSampler.p_sample_plms). e_t = CFG(e_uncond, e_cond) -> e_out (the sampler's old_eps
+ * entry, may be NULL); e' = w[0] e_t + w[1] h1 + w[2] h2 + w[3] h3 (host float[4]: Adams-Bashforth orders 1-4 or the
+ * pseudo improved Euler average); x_prev / pred_x0 from e' with the DDIM coefficients of row `index` (eta = 0).
+ * h1..h3 = old_eps[-1], [-2], [-3] (NULL where the weight is 0). */
+int fgdm_plms_step(const float* e_uncond, const float* e_cond, const float* h1, const float* h2, const float* h3,
+                   const float* weights, const float* x, const float* coef_table, int index, float scale, float* e_out,
+                   float* x_prev, float* pred_x0, int n, void* stream);
+
 /* Loop bookkeeping of ddim_sampling (ddim.py:147-149: index = total - i - 1; ts = full((b,), step)) done on
  * the device so one captured CUDA graph replays for every step: i = (*counter)++; t_out[0..rows) =
  * t_table[i]; *index_out = idx_table[i]. */

@@ -430,6 +430,52 @@ def ddim_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod,
     return img, inter
 
 
+def plms_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod, log_every_t=100, record=None):
+    """PLMSSampler.sample/plms_sampling/p_sample_plms, ldm/models/diffusion/plms.py:58-236 (eta must be 0, :25-26).
+    Same schedule tables as DDIM (:24-56). The first step is the pseudo improved Euler (two model calls, :216-220), then
+    Adams-Bashforth of order 2, 3, 4 on the CFG-combined eps history (:221-229). record: receives (e_t, x_prev)."""
+    sched = make_ddim_schedule(alphas_cumprod, S, 0.0)
+    ts = sched["timesteps"]
+    time_range = np.flip(ts)
+    img = x_T
+    b = shape[0]
+    inter = {"x_inter": [img], "pred_x0": [img]}
+    total = ts.shape[0]
+    old_eps = []
+
+    def model_output(x, t):                                   # plms.py:178-192
+        if uncond is None or scale == 1.0:
+            return apply_model(x, t, cond)
+        e_u, e_c = apply_model(torch.cat([x] * 2), torch.cat([t] * 2), torch.cat([uncond, cond])).chunk(2)
+        return e_u + scale * (e_c - e_u)
+
+    for i, step in enumerate(time_range):
+        index = total - i - 1
+        t = torch.full((b,), int(step), device=img.device, dtype=torch.long)
+        t_next = torch.full((b,), int(time_range[min(i + 1, len(time_range) - 1)]), device=img.device, dtype=torch.long)
+        e_t = model_output(img, t)
+        if len(old_eps) == 0:
+            x_prev, _ = ddim_update(img, e_t, sched, index)
+            e_t_next = model_output(x_prev, t_next)
+            e_t_prime = (e_t + e_t_next) / 2
+        elif len(old_eps) == 1:
+            e_t_prime = (3 * e_t - old_eps[-1]) / 2
+        elif len(old_eps) == 2:
+            e_t_prime = (23 * e_t - 16 * old_eps[-1] + 5 * old_eps[-2]) / 12
+        else:
+            e_t_prime = (55 * e_t - 59 * old_eps[-1] + 37 * old_eps[-2] - 9 * old_eps[-3]) / 24
+        img, pred_x0 = ddim_update(img, e_t_prime, sched, index)
+        old_eps.append(e_t)
+        if len(old_eps) >= 4:
+            old_eps.pop(0)
+        if record is not None:
+            record.append((e_t, img))
+        if index % log_every_t == 0 or index == total - 1:
+            inter["x_inter"].append(img)
+            inter["pred_x0"].append(pred_x0)
+    return img, inter
+
+
 # ----------------------------------------------------------------------------------------------
 # factor hand-off (scripts/txt2img_fgdm_inference.py:244-261; controlnet/initialize_cn.py:77-80,98-99)
 # ----------------------------------------------------------------------------------------------

@@ -6,7 +6,7 @@
 3. writes the reference's outputs as golden fixtures to tests/golden/*.npz (inputs are re-derived from
    the seeds stored alongside, weights from the weight seed).
 
-Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond]
+Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond|plms]
 """
 from __future__ import annotations
 
@@ -85,6 +85,7 @@ def golden_fgdm():
         assert torch.equal(am, eps_ref)
         save("unet_fgdm", eps=eps_ref, weight_seed=gc.FGDM_WEIGHT_SEED)
         golden_pcond(model, sd)
+        golden_plms(model, sd)
         # --- DDIM loop with CFG through the reference sampler
         from ldm.models.diffusion.ddim import DDIMSampler
         case = gc.ddim_case()
@@ -155,6 +156,39 @@ def golden_pcond(model=None, sd=None):
         am = model.apply_model(case["x"], case["t"], case["ctx"], pcond=case["pcond"])
         assert torch.equal(am, eps_ref)
         save("unet_pcond", eps=eps_ref, weight_seed=gc.FGDM_WEIGHT_SEED)
+
+
+def golden_plms(model=None, sd=None):
+    """PLMSSampler.sample (plms.py) through the reference's own sampler class."""
+    if model is None:
+        model = rh.build_fgdm()
+        sd = load_weights(model, gc.fgdm_param_shapes(), gc.FGDM_WEIGHT_SEED)
+    from ldm.models.diffusion.plms import PLMSSampler
+    with torch.no_grad():
+        case = gc.plms_case()
+        sampler = rh.cpu_sampler(PLMSSampler(model))
+        steps = []
+        orig = sampler.p_sample_plms
+
+        def spy(*a, **k):
+            out = orig(*a, **k)
+            steps.append(out[0].clone())
+            return out
+        sampler.p_sample_plms = spy
+        x0, inter = sampler.sample(S=case["S"], conditioning=case["c"], batch_size=case["B"], shape=case["shape"],
+                                   verbose=False, unconditional_guidance_scale=case["scale"],
+                                   unconditional_conditioning=case["uc"], eta=0.0, x_T=case["x_T"])
+        rec = []
+        x0_orc, inter_orc = orc.plms_sample(
+            lambda x, t, c: orc.unet_forward(sd, x, t, c, prefix="model.diffusion_model."), case["S"],
+            (case["B"],) + tuple(case["shape"]), case["c"], case["uc"], case["scale"], case["x_T"],
+            model.alphas_cumprod, record=rec)
+        check("PLMSSampler.sample final latent", x0_orc, x0, tol=1e-3)
+        for i, (s_ref, (_, s_orc)) in enumerate(zip(steps, rec)):
+            check(f"  plms step {i} x_prev", s_orc, s_ref, tol=1e-3)
+        assert len(inter["x_inter"]) == len(inter_orc["x_inter"])
+        save("plms_fgdm", x0=x0, steps=torch.stack(steps), pred_x0_last=inter["pred_x0"][-1],
+             n_inter=len(inter["x_inter"]))
 
 
 def golden_control():
@@ -245,6 +279,8 @@ if __name__ == "__main__":
         golden_fgdm()
     if a.only == "pcond":
         golden_pcond()
+    if a.only == "plms":
+        golden_plms()
     if a.only in ("all", "control"):
         golden_control()
     print("golden fixtures written; oracle restatement agrees with the reference")

@@ -288,6 +288,31 @@ def test_cfg_ddim():
     assert torch.equal(xp, xp2)
 
 
+def test_plms_step():
+    """fgdm_plms_step vs plms.py:178-234 in torch (CFG combine, Adams-Bashforth blend, x_prev / pred_x0)."""
+    torch.manual_seed(3)
+    n = (2, 4, 64, 64)
+    e_u, e_c, x = (torch.randn(n, device=DEV) for _ in range(3))
+    old = [torch.randn(n, device=DEV) for _ in range(3)]           # old_eps[-3], [-2], [-1]
+    coef = torch.rand(7, 5, device=DEV) + 0.5
+    s, idx = 7.5, 4
+    s1m, sa, sap, dr, _ = coef[idx].tolist()
+    e_t = e_u + s * (e_c - e_u)
+    cases = {0: e_t, 1: (3 * e_t - old[-1]) / 2, 2: (23 * e_t - 16 * old[-1] + 5 * old[-2]) / 12,
+             3: (55 * e_t - 59 * old[-1] + 37 * old[-2] - 9 * old[-3]) / 24}
+    weights = {0: (1.0, 0.0, 0.0, 0.0), 1: (3 / 2, -1 / 2, 0.0, 0.0), 2: (23 / 12, -16 / 12, 5 / 12, 0.0),
+               3: (55 / 24, -59 / 24, 37 / 24, -9 / 24)}
+    for order, ep in cases.items():
+        e_out = torch.empty_like(x)
+        xp, p0 = ops.plms_step(e_u, e_c, old[::-1][:order], weights[order], x, coef, idx, s, e_out=e_out)
+        ref0 = (x - s1m * ep) / sa
+        torch.testing.assert_close(e_out, e_t, rtol=1e-6, atol=1e-6)
+        torch.testing.assert_close(p0, ref0, rtol=1e-5, atol=2e-5)
+        torch.testing.assert_close(xp, sap * ref0 + dr * ep, rtol=1e-5, atol=2e-5)
+    with pytest.raises(RuntimeError):
+        ops.plms_step(e_u, e_c, [], weights[2], x, coef, idx, s)   # weight without its history tensor
+
+
 def test_timestep_embedding_and_skinny_linear():
     t = torch.tensor([1, 21, 981, 500], device=DEV, dtype=torch.int64)
     freqs = ops.timestep_freqs(320).to(DEV)

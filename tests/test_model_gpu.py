@@ -98,6 +98,29 @@ def test_unet_pcond_vs_reference_golden(fgdm):
     assert relmax(x0p, x0) > 1e-2                              # and differs from the plain (pcond=None) chain
 
 
+def test_plms_loop_vs_reference_golden(fgdm):
+    """PLMSSampler (plms.py) on the captured model-call graph + fgdm_plms_step, against the reference's sampler."""
+    from fgdm_b200.plms import PLMSSampler
+    model, _ = fgdm
+    c, g = gc.plms_case(), gold("plms_fgdm")
+    kw = dict(S=c["S"], conditioning=c["c"].to(DEV), batch_size=c["B"], shape=list(c["shape"]), verbose=False,
+              unconditional_guidance_scale=c["scale"], unconditional_conditioning=c["uc"].to(DEV), eta=0.0,
+              x_T=c["x_T"].to(DEV))
+    sampler = PLMSSampler(model)
+    seen, preds = [], []
+    x0, inter = sampler.sample(img_callback=lambda p, i: (seen.append(i), preds.append(p)), **kw)
+    assert seen == list(range(g["steps"].shape[0]))
+    assert len(inter["x_inter"]) == int(g["n_inter"])
+    peak = float(np.abs(g["x0"]).max())
+    print("plms fgdm: relmax", relmax(x0, g["x0"]), "psnr", psnr(x0, g["x0"], peak))
+    assert relmax(x0, g["x0"]) < 8e-2 and psnr(x0, g["x0"], peak) > 35.0
+    assert relmax(inter["pred_x0"][-1], g["pred_x0_last"]) < 8e-2
+    x0b, _ = sampler.sample(**kw)                              # graph replay is reproducible bit for bit
+    assert torch.equal(x0b, x0)
+    with pytest.raises(ValueError):
+        sampler.sample(**{**kw, "eta": 0.5})                   # plms.py:25-26
+
+
 def test_ddim_cfg_loop_vs_reference_golden(fgdm):
     model, _ = fgdm
     c, g = gc.ddim_case(), gold("ddim_fgdm")

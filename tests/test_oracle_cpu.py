@@ -55,6 +55,22 @@ def test_oracle_unet_pcond_matches_reference_golden(sd_fgdm):
     assert relmax(plain, gold("unet_pcond")["eps"]) > 1e-2      # the pcond branch really changes the result
 
 
+def test_oracle_plms_loop_matches_reference_golden(sd_fgdm):
+    """PLMSSampler.sample (plms.py): Euler start + Adams-Bashforth orders 2-4, vs the reference's own sampler."""
+    c, g = gc.plms_case(), gold("plms_fgdm")
+    rec = []
+    with torch.no_grad():
+        x0, inter = orc.plms_sample(
+            lambda x, t, cc: orc.unet_forward(sd_fgdm, x, t, cc, prefix="model.diffusion_model."), c["S"],
+            (c["B"],) + tuple(c["shape"]), c["c"], c["uc"], c["scale"], c["x_T"],
+            orc.make_schedule_buffers()["alphas_cumprod"], record=rec)
+    assert relmax(x0, g["x0"]) < 1e-3
+    assert len(rec) == g["steps"].shape[0]
+    for i, (_, xp) in enumerate(rec):
+        assert relmax(xp, g["steps"][i]) < 1e-3
+    assert len(inter["x_inter"]) == int(g["n_inter"])
+
+
 def test_oracle_ddim_loop_matches_reference_golden(sd_fgdm):
     c, g = gc.ddim_case(), gold("ddim_fgdm")
     rec = []
