@@ -208,6 +208,14 @@ def kernel_rooflines(pipe, dev_in, pk):
         ach = f["bytes"] / (f["ms"] * 1e-3) / 1e9
         roof = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s",
                 "frac": ach / pk["hbm"], "traffic": None}
+    try:      # DRAM traffic of the family's dominant shape from the committed ncu --set full capture (per launch of
+        # THAT shape; `achieved` is the family average) - bench.py itself never runs under a profiler
+        tr = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")))
+        if tr.get("kernel") == top:
+            roof["traffic"] = tr["dram_bytes_per_launch"]
+            roof["traffic_of"] = {k: tr[k] for k in ("shape", "algorithmic_bytes_per_launch", "source")}
+    except (OSError, ValueError, KeyError):
+        pass
     roof.update(peak_source=pk["src"] + " (sustained)" if tensor_bound else pk["src"], launches=f["launches"],
                 avg_launch_us=1e3 * f["ms"] / f["launches"], share_of_sampled_step=f["ms"] / total_ms,
                 how="1 eager CFG step of each factor + 1 decode, CUDA events around every launch")
