@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libfgdm_b200.so")
 ABI_VERSION = 4
 
 OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32, OUT_NCHW_F32 = 0, 1, 2, 3, 4
-ACT_NONE, ACT_SILU, ACT_RELU = 0, 1, 2
+ACT_NONE, ACT_SILU, ACT_RELU, ACT_QUICK_GELU = 0, 1, 2, 3
 CONV_1X1, CONV_3X3, CONV_3X3_S2 = 0, 1, 2
 
 vp, fp, ip = C.c_void_p, C.c_void_p, C.c_void_p  # all device pointers travel as integers
@@ -45,6 +45,8 @@ SIGNATURES = {
     "fgdm_conv_gemm": [C.POINTER(GemmArgs), vp],
     "fgdm_gemm_stats_slots": [C.POINTER(GemmArgs)],
     "fgdm_attention": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp],
+    "fgdm_attention_causal": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp],
+    "fgdm_embed_tokens": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_groupnorm": [vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp],
     "fgdm_layernorm": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp],
     "fgdm_softmax_rows": [vp, vp, C.c_int, C.c_int, C.c_float, vp],

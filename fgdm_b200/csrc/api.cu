@@ -100,7 +100,9 @@ int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dim
 int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, const void* w, int bn_hint,
                 cudaStream_t stream, int* stats_slots_out = nullptr);
 int launch_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int Nq, int Nk,
-                     int d, int tok_pad, float scale, cudaStream_t stream);
+                     int d, int tok_pad, float scale, int causal, cudaStream_t stream);
+int launch_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_emb, void* out, int rows, int seq,
+                        int dim, int vocab, cudaStream_t stream);
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                      int NB, int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream);
 int launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, int rows, int C, float eps,
@@ -274,8 +276,21 @@ int fgdm_gemm_stats_slots(const fgdm_gemm_args* a) {
 int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int nq, int nk,
                    int d, int tok_pad, float scale, void* stream) {
   FGDM_NONNULL(q, "q"); FGDM_NONNULL(k, "k"); FGDM_NONNULL(vt, "vt"); FGDM_NONNULL(out, "out");
-  return launch_attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale,
+  return launch_attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale, 0,
                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_attention_causal(const void* q, const void* k, const void* vt, void* out, int images, int heads, int n,
+                          int d, int tok_pad, float scale, void* stream) {
+  FGDM_NONNULL(q, "q"); FGDM_NONNULL(k, "k"); FGDM_NONNULL(vt, "vt"); FGDM_NONNULL(out, "out");
+  return launch_attention(q, k, vt, out, images, heads, n, n, d, tok_pad, scale, 1,
+                          reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_emb, void* out, int rows, int seq,
+                      int dim, int vocab, void* stream) {
+  FGDM_NONNULL(ids, "ids"); FGDM_NONNULL(tok_emb, "tok_emb"); FGDM_NONNULL(pos_emb, "pos_emb"); FGDM_NONNULL(out, "out");
+  return launch_embed_tokens(ids, tok_emb, pos_emb, out, rows, seq, dim, vocab, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,

@@ -33,6 +33,7 @@ struct AttnParams {
   float scale_log2; // softmax scale * log2(e)
   __nv_bfloat16* out;  // [images, Nq, heads*d]
   int ld_out;
+  int causal;       // 1: query i only sees keys j <= i (CLIP text transformer)
 };
 
 // QTN = 128-row query tiles per CTA (they share every K/V tile): 2 for self-attention (one CTA per SM, P double-
@@ -264,7 +265,9 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     float m_ref = -INFINITY;                            // reference max (scaled, log2 domain) used for exp2
 
     for (int j = 0; j < num_kv; ++j) {
-      const int valid = p.Nk - j * BN - half * HB;       // keys valid in this thread's half tile (may exceed HB)
+      int valid = p.Nk - j * BN - half * HB;             // keys valid in this thread's half tile (may exceed HB)
+      if (p.causal) valid = min(valid, q0 + t * 128 + row + 1 - j * BN - half * HB);   // per row: keys j <= i
+      const bool full = !p.causal && valid >= HB;        // warp-uniform
       mbar_wait(&bar_s[t], j & 1);
       tc_fence_after();
 
@@ -279,7 +282,7 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
       float hmax;
       {
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-        if (valid >= HB) {
+        if (full) {
 #pragma unroll
           for (int i = 0; i < HB; i += 8) {
 #pragma unroll
@@ -356,7 +359,7 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
           st_shared_16(sP_row + (cc >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
         }
       };
-      if (valid >= HB) emit(std::false_type{}); else emit(std::true_type{});
+      if (full) emit(std::false_type{}); else emit(std::true_type{});
 
       fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
       // Observe PV(j-1) BEFORE enabling PV(j): every bar_o phase is seen in order (no parity aliasing), and it makes
@@ -437,7 +440,7 @@ static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUten
 // q: [images, heads, Nq, d], k: [images, heads, Nk, d], vt: [images, heads, d, tok_pad] (keys contiguous),
 // out: [images, Nq, heads*d]; all bf16.
 int launch_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int Nq, int Nk,
-                     int d, int tok_pad, float scale, cudaStream_t stream) {
+                     int d, int tok_pad, float scale, int causal, cudaStream_t stream) {
   if (d % 8 != 0 || d < 8 || d > 192) { set_error("attention: head dim %d unsupported (multiple of 8, <= 192)", d); return -1; }
   if (tok_pad % 8 != 0 || tok_pad < Nk) { set_error("attention: tok_pad=%d must be a multiple of 8 and >= Nk=%d", tok_pad, Nk); return -1; }
   AttnParams p;
@@ -449,6 +452,7 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   p.scale_log2 = scale * 1.4426950408889634f;
   p.out = reinterpret_cast<__nv_bfloat16*>(out);
   p.ld_out = heads * d;
+  p.causal = causal;
   const int KA = (d + 63) / 64;
   const int BN = (KA == 1) ? 128 : 64;   // keys per tile: two CTAs must fit on an SM
   const int nsplit = (d + 79) / 80;

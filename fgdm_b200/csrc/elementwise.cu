@@ -56,6 +56,39 @@ int launch_cfg_ddim(const float* e_u, const float* e_c, const float* x, const fl
 }
 
 // ---------------------------------------------------------------------------------------------
+// CLIP text embeddings (transformers CLIPTextEmbeddings, used by FrozenCLIPEmbedder, modules.py:137-163):
+// out[r, :] = token_embedding[ids[r]] + position_embedding[r % seq], fp32 tables -> bf16 tokens. One warp per row.
+// An id outside [0, vocab) traps (launch error) instead of reading out of bounds.
+// ---------------------------------------------------------------------------------------------
+__global__ void embed_tokens_kernel(const int64_t* __restrict__ ids, const float* __restrict__ tok,
+                                    const float* __restrict__ pos, __nv_bfloat16* __restrict__ out, int rows, int seq,
+                                    int dim, int vocab) {
+  const int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= rows) return;
+  const int64_t id = ids[r];
+  if (id < 0 || id >= vocab) __trap();
+  const float4* t4 = reinterpret_cast<const float4*>(tok + static_cast<size_t>(id) * dim);
+  const float4* p4 = reinterpret_cast<const float4*>(pos + static_cast<size_t>(r % seq) * dim);
+  uint2* o2 = reinterpret_cast<uint2*>(out + static_cast<size_t>(r) * dim);
+  for (int v = lane; v < dim / 4; v += 32) {
+    const float4 a = t4[v], b = p4[v];
+    o2[v] = make_uint2(pack_bf16x2(a.x + b.x, a.y + b.y), pack_bf16x2(a.z + b.z, a.w + b.w));
+  }
+}
+
+int launch_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_emb, void* out, int rows, int seq,
+                        int dim, int vocab, cudaStream_t stream) {
+  if (dim % 4 != 0 || seq <= 0) { set_error("embed_tokens: dim=%d must be a multiple of 4, seq=%d > 0", dim, seq); return -1; }
+  const int threads = 256;
+  const int blocks = (rows * 32 + threads - 1) / threads;
+  embed_tokens_kernel<<<blocks, threads, 0, stream>>>(ids, static_cast<const float*>(tok_emb),
+                                                      static_cast<const float*>(pos_emb),
+                                                      static_cast<__nv_bfloat16*>(out), rows, seq, dim, vocab);
+  return check_launch("embed_tokens_kernel");
+}
+
+// ---------------------------------------------------------------------------------------------
 // PLMS step (ldm/models/diffusion/plms.py:172-236): CFG combine, Adams-Bashforth blend with up to three earlier
 // eps, then the same x_{t-1} update as DDIM with eta = 0 (plms.py:22-23 asserts it):
 //   e_t     = e_u + s * (e_c - e_u)                        (written to e_out: the sampler's `old_eps` entry)

@@ -580,6 +580,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
               } else if (p.act == kActSilu) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = silu_f(v[j]);
+              } else if (p.act == kActQuickGelu) {             // x * sigmoid(1.702 x): CLIP text MLP
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = v[j] * fast_rcp(1.0f + fast_exp2(-1.702f * 1.4426950408889634f * v[j]));
               }
               if (p.res0) {
 #pragma unroll

@@ -12,7 +12,7 @@ enum GemmOutMode : int {
   kOutNchwF32 = 4, // out[img, n, pix] fp32 for n < n_store (tiny-Cout convs: eps / RGB at the model boundary)
 };
 
-enum GemmAct : int { kActNone = 0, kActSilu = 1, kActRelu = 2 };
+enum GemmAct : int { kActNone = 0, kActSilu = 1, kActRelu = 2, kActQuickGelu = 3 };
 
 struct GemmParams {
   // A operand: up to two NHWC bf16 sources that are concatenated along channels (virtual concat)

@@ -88,6 +88,51 @@ def plms_case():
                 c=synth.randn((1, 77, 768), 35), uc=synth.randn((1, 77, 768), 36))
 
 
+CLIP_WEIGHT_SEED = 7
+
+
+def clip_param_shapes(cfg=None):
+    """State-dict names/shapes of transformers' CLIPTextModel for openai/clip-vit-large-patch14 (text tower) under
+    FrozenCLIPEmbedder's attribute name `transformer` (modules.py:142)."""
+    c = cfg or dict(vocab_size=49408, hidden_size=768, intermediate_size=3072, num_hidden_layers=12,
+                    max_position_embeddings=77)
+    h, f, p = c["hidden_size"], c["intermediate_size"], "transformer.text_model."
+    sh = {p + "embeddings.token_embedding.weight": (c["vocab_size"], h),
+          p + "embeddings.position_embedding.weight": (c["max_position_embeddings"], h)}
+    for i in range(c["num_hidden_layers"]):
+        q = f"{p}encoder.layers.{i}."
+        for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
+            sh[q + f"self_attn.{n}.weight"] = (h, h)
+            sh[q + f"self_attn.{n}.bias"] = (h,)
+        for n in ("layer_norm1", "layer_norm2"):
+            sh[q + n + ".weight"] = (h,)
+            sh[q + n + ".bias"] = (h,)
+        sh[q + "mlp.fc1.weight"], sh[q + "mlp.fc1.bias"] = (f, h), (f,)
+        sh[q + "mlp.fc2.weight"], sh[q + "mlp.fc2.bias"] = (h, f), (h,)
+    sh[p + "final_layer_norm.weight"] = (h,)
+    sh[p + "final_layer_norm.bias"] = (h,)
+    return sh
+
+
+def clip_state_dict():
+    """Seeded synthetic CLIP text weights; q/k projections x3 so that the attention is not near-uniform."""
+    sd = synth.make_state_dict(clip_param_shapes(), CLIP_WEIGHT_SEED)
+    for k in sd:
+        if k.endswith("q_proj.weight") or k.endswith("k_proj.weight"):
+            sd[k] = sd[k] * 3.0
+    return sd
+
+
+def clip_case():
+    """Two prompts of 77 token ids: BOS, random words, EOS then EOS padding (the tokenizer's max_length padding)."""
+    g = torch.Generator(device="cpu").manual_seed(91)
+    ids = torch.randint(1000, 40000, (2, 77), generator=g, dtype=torch.int64)
+    ids[:, 0] = 49406
+    ids[0, 9:] = 49407
+    ids[1, 40:] = 49407
+    return dict(ids=ids)
+
+
 def vae_case():
     return dict(z=synth.randn((1, 4, 16, 16), 41) * 0.18215 * 3.0)
 

@@ -31,6 +31,8 @@ TARGET_ALIASES = {
     "cldm.cldm.ControlLDM": "fgdm_b200.ldm.ControlLDM",
     "cldm.cldm.ControlNet": "fgdm_b200.nets.ControlNet",
     "cldm.cldm.ControlledUnetModel": "fgdm_b200.nets.ControlledUnetModel",
+    "ldm.modules.encoders.modules.FrozenCLIPEmbedder": "fgdm_b200.clip.FrozenCLIPEmbedder",
+    "controlnet.ldm.modules.encoders.modules.FrozenCLIPEmbedder": "fgdm_b200.clip.FrozenCLIPEmbedder",
 }
 
 
@@ -95,6 +97,10 @@ class LatentDiffusion:
         self.model = DiffusionWrapper(unet_config, conditioning_key)
         self.first_stage_model = instantiate_from_config(first_stage_config) if first_stage_config else None
         self.cond_stage_model = IdentityCondStage()
+        if isinstance(cond_stage_config, dict) and str(cond_stage_config.get("target", "")).endswith("FrozenCLIPEmbedder"):
+            # models/config.yaml:74-75 / ddpm.py:626-640: the text encoder, on the same kernels (fgdm_b200/clip.py)
+            params = dict(cond_stage_config.get("params", {}), device=str(self.device))
+            self.cond_stage_model = instantiate_from_config(dict(cond_stage_config, params=params))
         self.register_schedule(given_betas, timesteps, linear_start, linear_end)
 
     # ddpm.py:175-203 with util.py:21-25 (float64 numpy -> float32 buffers)
@@ -131,6 +137,9 @@ class LatentDiffusion:
         _lib.require_device()
         for pre, net in self._parts().items():
             net.load_state_dict(sd, strict=False, prefix=pre, device=self.device)
+        pre = "cond_stage_model."
+        if hasattr(self.cond_stage_model, "text_model") and any(k.startswith(pre) for k in sd):
+            self.cond_stage_model.load_state_dict({k[len(pre):]: v for k, v in sd.items() if k.startswith(pre)})
         return self
 
     def eval(self):
@@ -149,10 +158,12 @@ class LatentDiffusion:
     # -- reference methods ------------------------------------------------------------------------
     def get_learned_conditioning(self, c):
         """ddpm.py:663-674. Tensors (pre-encoded / synthetic contexts) pass through."""
-        if torch.is_tensor(c):
+        if torch.is_tensor(c) and c.is_floating_point():
             return c
-        raise NotImplementedError("text encoding (FrozenCLIPEmbedder) is outside the sampling hot path; pass "
-                                  "[B,77,768] context tensors")
+        if hasattr(self.cond_stage_model, "text_model"):
+            return self.cond_stage_model.encode(c)            # token ids -> [B,77,768] (FrozenCLIPEmbedder)
+        raise NotImplementedError("no text encoder configured (cond_stage_config: FrozenCLIPEmbedder); pass [B,77,768] "
+                                  "context tensors")
 
     def apply_model(self, x_noisy, t, cond, return_ids=False, **kw):
         """ddpm.py:1035-1044,1130-1136: tensor/list cond -> {'c_crossattn': [c]} -> DiffusionWrapper."""

@@ -11,7 +11,7 @@ import math
 import torch
 
 from . import _lib
-from ._lib import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU,
+from ._lib import (ACT_NONE, ACT_QUICK_GELU, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU,
                    OUT_NCHW_F32, OUT_QKV, GemmArgs)
 
 bf16 = torch.bfloat16
@@ -152,6 +152,25 @@ def attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad, scale=None):
     scale = d ** -0.5 if scale is None else scale
     _call("fgdm_attention", ("attn d=%d nq=%d nk=%d" % (d, nq, nk), 4.0 * images * heads * nq * nk * d, 2.0 * images * heads * d * (2 * nq + 2 * nk)), _p(q), _p(k), _p(vt), _p(out), images, heads, nq, nk, d, tok_pad,
                                          scale, _stream())
+    return out
+
+
+def attention_causal(q, k, vt, out, images, heads, n, d, tok_pad, scale=None):
+    """Causal self-attention (CLIP text transformer): query i attends to keys j <= i."""
+    scale = d ** -0.5 if scale is None else scale
+    _call("fgdm_attention_causal", ("attn causal d=%d n=%d" % (d, n), 2.0 * images * heads * n * n * d,
+                                    2.0 * images * heads * d * 4 * n), _p(q), _p(k), _p(vt), _p(out), images, heads, n, d,
+          tok_pad, scale, _stream())
+    return out
+
+
+def embed_tokens(ids, tok_emb, pos_emb):
+    """ids int64 [B, L]; fp32 tables -> bf16 [B*L, dim] = tok_emb[ids] + pos_emb[position]."""
+    b, L = ids.shape
+    dim = tok_emb.shape[1]
+    out = torch.empty((b * L, dim), device=ids.device, dtype=bf16)
+    _call("fgdm_embed_tokens", ("embed_tokens", 0.0, 10.0 * b * L * dim), _p(ids), _p(tok_emb), _p(pos_emb), _p(out), b * L, L,
+          dim, tok_emb.shape[0], _stream())
     return out
 
 

@@ -44,7 +44,7 @@ enum {
   FGDM_OUT_F32 = 3,    /* out[m, n] fp32 */
   FGDM_OUT_NCHW_F32 = 4 /* out[img, c, pix] fp32 for c < n_store: conv_out 320->4 (openaimodel.py:727), 128->3 (model.py:529) */
 };
-enum { FGDM_ACT_NONE = 0, FGDM_ACT_SILU = 1, FGDM_ACT_RELU = 2 };
+enum { FGDM_ACT_NONE = 0, FGDM_ACT_SILU = 1, FGDM_ACT_RELU = 2, FGDM_ACT_QUICK_GELU = 3 /* x*sigmoid(1.702x) */ };
 /* A-operand addressing of fgdm_conv_gemm */
 enum {
   FGDM_CONV_1X1 = 0,      /* Linear / 1x1 conv */
@@ -110,6 +110,16 @@ int fgdm_gemm_stats_slots(const fgdm_gemm_args* args);
  * q [images, heads, nq, d], k [images, heads, nk, d], vt [images, heads, d, tok_pad], out [images, nq, heads*d]. */
 int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int nq, int nk,
                    int d, int tok_pad, float scale, void* stream);
+
+/* Causal self-attention (query i sees keys j <= i) of the CLIP text transformer behind FrozenCLIPEmbedder
+ * (ldm/modules/encoders/modules.py:137-163 -> transformers CLIPAttention with the causal mask); layouts as above. */
+int fgdm_attention_causal(const void* q, const void* k, const void* vt, void* out, int images, int heads, int n,
+                          int d, int tok_pad, float scale, void* stream);
+
+/* CLIP text embeddings (transformers CLIPTextEmbeddings): out[r] = tok_emb[ids[r]] + pos_emb[r % seq]; fp32 tables
+ * [vocab, dim] / [seq, dim], bf16 out [rows, dim]. */
+int fgdm_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_emb, void* out, int rows, int seq,
+                      int dim, int vocab, void* stream);
 
 /* GroupNorm32 (+SiLU): util.py:223-225, openaimodel.py:221-224; attention.py:76-77; model.py:33-39.
  * x0/x1 virtual channel concat; workspace >= nb*129*groups*8 bytes. */

@@ -430,6 +430,53 @@ def ddim_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod,
     return img, inter
 
 
+# ----------------------------------------------------------------------------------------------
+# text conditioning: FrozenCLIPEmbedder.forward, ldm/modules/encoders/modules.py:137-163
+# ----------------------------------------------------------------------------------------------
+# The arithmetic lives in a third-party dependency that is not vendored in the reference: Hugging Face
+# `transformers` (pinned transformers==4.19.2, fgdm.yml:175), class CLIPTextModel / CLIPTextTransformer
+# (models/clip/modeling_clip.py). Restated from its published algorithm: token + learned position embeddings; 12
+# pre-LayerNorm blocks of [causal multi-head self-attention (q scaled by d^-1/2 before q k^T), + residual,
+# MLP fc1 -> quick_gelu (x * sigmoid(1.702 x)) -> fc2, + residual]; final LayerNorm; the embedder returns
+# `last_hidden_state` (no pooling, modules.py:160). Pinned against transformers' own CLIPTextModel run in the build
+# container (oracle/make_golden.py --only clip; tests/golden/clip_text.npz).
+CLIP_TEXT_CFG = dict(vocab_size=49408, hidden_size=768, intermediate_size=3072, num_hidden_layers=12,
+                     num_attention_heads=12, max_position_embeddings=77, layer_norm_eps=1e-5)
+
+
+def clip_text_forward(sd, ids, cfg=None, prefix="transformer.text_model."):
+    """ids: int64 [B, L<=77] -> last_hidden_state fp32 [B, L, hidden]."""
+    cfg = cfg or CLIP_TEXT_CFG
+    p = prefix
+    b, L = ids.shape
+    heads = cfg["num_attention_heads"]
+    eps = cfg["layer_norm_eps"]
+    h = sd[p + "embeddings.token_embedding.weight"].float()[ids] + \
+        sd[p + "embeddings.position_embedding.weight"].float()[:L][None]
+    c = h.shape[-1]
+    d = c // heads
+    mask = torch.full((L, L), float("-inf"), device=h.device).triu(1)          # causal: token i sees j <= i
+
+    def lin(name, x):
+        return F.linear(x, sd[name + ".weight"].float(), sd[name + ".bias"].float())
+
+    for i in range(cfg["num_hidden_layers"]):
+        q_ = f"{p}encoder.layers.{i}."
+        r = h
+        x = F.layer_norm(h, (c,), sd[q_ + "layer_norm1.weight"].float(), sd[q_ + "layer_norm1.bias"].float(), eps)
+        q = (lin(q_ + "self_attn.q_proj", x) * d ** -0.5).view(b, L, heads, d).transpose(1, 2)
+        k = lin(q_ + "self_attn.k_proj", x).view(b, L, heads, d).transpose(1, 2)
+        v = lin(q_ + "self_attn.v_proj", x).view(b, L, heads, d).transpose(1, 2)
+        a = torch.softmax(q @ k.transpose(-1, -2) + mask, dim=-1) @ v
+        h = r + lin(q_ + "self_attn.out_proj", a.transpose(1, 2).reshape(b, L, c))
+        r = h
+        x = F.layer_norm(h, (c,), sd[q_ + "layer_norm2.weight"].float(), sd[q_ + "layer_norm2.bias"].float(), eps)
+        x = lin(q_ + "mlp.fc1", x)
+        x = x * torch.sigmoid(1.702 * x)
+        h = r + lin(q_ + "mlp.fc2", x)
+    return F.layer_norm(h, (c,), sd[p + "final_layer_norm.weight"].float(), sd[p + "final_layer_norm.bias"].float(), eps)
+
+
 def plms_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod, log_every_t=100, record=None):
     """PLMSSampler.sample/plms_sampling/p_sample_plms, ldm/models/diffusion/plms.py:58-236 (eta must be 0, :25-26).
     Same schedule tables as DDIM (:24-56). The first step is the pseudo improved Euler (two model calls, :216-220), then

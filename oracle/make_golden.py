@@ -6,7 +6,7 @@
 3. writes the reference's outputs as golden fixtures to tests/golden/*.npz (inputs are re-derived from
    the seeds stored alongside, weights from the weight seed).
 
-Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond|plms]
+Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond|plms|clip]
 """
 from __future__ import annotations
 
@@ -191,6 +191,30 @@ def golden_plms(model=None, sd=None):
              n_inter=len(inter["x_inter"]))
 
 
+def golden_clip():
+    """FrozenCLIPEmbedder.forward (modules.py:137-163) = transformers CLIPTextModel(...).last_hidden_state: the
+    dependency itself, built from its config with the seeded synthetic weights (no checkpoint download)."""
+    from transformers import CLIPTextConfig, CLIPTextModel
+    cfg = CLIPTextConfig(vocab_size=49408, hidden_size=768, intermediate_size=3072, num_hidden_layers=12,
+                         num_attention_heads=12, max_position_embeddings=77, hidden_act="quick_gelu",
+                         layer_norm_eps=1e-5, projection_dim=768)
+    model = CLIPTextModel(cfg).eval()
+    sd = gc.clip_state_dict()
+    ref_sd = model.state_dict()
+    stripped = {k[len("transformer."):]: v for k, v in sd.items()}
+    for k, v in stripped.items():
+        assert k in ref_sd and tuple(ref_sd[k].shape) == tuple(v.shape), k
+    missing = [k for k in ref_sd if k not in stripped and not k.endswith("position_ids")]
+    assert not missing, missing
+    model.load_state_dict(stripped, strict=False)
+    case = gc.clip_case()
+    with torch.no_grad():
+        z_ref = model(input_ids=case["ids"]).last_hidden_state
+        z_orc = orc.clip_text_forward(sd, case["ids"])
+    check("CLIPTextModel.last_hidden_state", z_orc, z_ref)
+    save("clip_text", z=z_ref, weight_seed=gc.CLIP_WEIGHT_SEED)
+
+
 def golden_control():
     print("== image factor (ControlLDM = ControlNet + ControlledUnetModel) ==")
     t0 = time.time()
@@ -281,6 +305,8 @@ if __name__ == "__main__":
         golden_pcond()
     if a.only == "plms":
         golden_plms()
+    if a.only in ("all", "clip"):
+        golden_clip()
     if a.only in ("all", "control"):
         golden_control()
     print("golden fixtures written; oracle restatement agrees with the reference")

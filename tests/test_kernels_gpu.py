@@ -227,6 +227,46 @@ def test_attention(images, heads, nq, nk, d):
     assert relerr(out, ref) < 1.5e-2
 
 
+def test_attention_causal_and_text_kernels():
+    """Causal mask (CLIP text transformer), token+position gather, quick-GELU epilogue."""
+    images, heads, n, d = 3, 12, 77, 64
+    q = torch.randn(images, heads, n, d, device=DEV).to(torch.bfloat16)
+    k = torch.randn(images, heads, n, d, device=DEV).to(torch.bfloat16)
+    v = torch.randn(images, heads, n, d, device=DEV).to(torch.bfloat16)
+    tp = 80
+    vt = torch.zeros(images, heads, d, tp, device=DEV, dtype=torch.bfloat16)
+    vt[..., :n] = v.transpose(-1, -2)
+    out = torch.empty(images, n, heads * d, device=DEV, dtype=torch.bfloat16)
+    ops.attention_causal(q, k, vt, out, images, heads, n, d, tp)
+    s = torch.einsum("bhid,bhjd->bhij", q.float(), k.float()) * d ** -0.5
+    s = s + torch.full((n, n), float("-inf"), device=DEV).triu(1)
+    ref = torch.einsum("bhij,bhjd->bhid", s.softmax(-1), v.float()).permute(0, 2, 1, 3).reshape(images, n, heads * d)
+    assert relerr(out, ref) < 1e-2
+    for n2 in (200, 300):                                  # more than one KV tile / query tile
+        q2, k2, v2 = (torch.randn(1, 2, n2, d, device=DEV).to(torch.bfloat16) for _ in range(3))
+        tp2 = (n2 + 7) // 8 * 8
+        vt2 = torch.zeros(1, 2, d, tp2, device=DEV, dtype=torch.bfloat16)
+        vt2[..., :n2] = v2.transpose(-1, -2)
+        o2 = torch.empty(1, n2, 2 * d, device=DEV, dtype=torch.bfloat16)
+        ops.attention_causal(q2, k2, vt2, o2, 1, 2, n2, d, tp2)
+        s2 = torch.einsum("bhid,bhjd->bhij", q2.float(), k2.float()) * d ** -0.5
+        s2 = s2 + torch.full((n2, n2), float("-inf"), device=DEV).triu(1)
+        r2 = torch.einsum("bhij,bhjd->bhid", s2.softmax(-1), v2.float()).permute(0, 2, 1, 3).reshape(1, n2, 2 * d)
+        assert relerr(o2, r2) < 1e-2
+    # embeddings
+    tok, pos = torch.randn(1000, 768, device=DEV), torch.randn(77, 768, device=DEV)
+    ids = torch.randint(0, 1000, (4, 77), device=DEV)
+    e = ops.embed_tokens(ids, tok, pos)
+    assert relerr(e.view(4, 77, 768), tok[ids] + pos[None]) < 5e-3
+    # quick-GELU epilogue
+    x = torch.randn(154, 768, device=DEV).to(torch.bfloat16)
+    w = (torch.randn(3072, 768, device=DEV) / math.sqrt(768)).to(torch.bfloat16)
+    b = torch.randn(3072, device=DEV)
+    y = ops.conv_gemm(x, w, 3072, bias=b, act=ops.ACT_QUICK_GELU)
+    h = x.float() @ w.float().t() + b
+    assert relerr(y, h * torch.sigmoid(1.702 * h)) < 1e-2
+
+
 def test_qkv_projection_layouts():
     images, n, c, heads = 2, 256, 320, 8
     d = c // heads

@@ -98,6 +98,43 @@ def test_unet_pcond_vs_reference_golden(fgdm):
     assert relmax(x0p, x0) > 1e-2                              # and differs from the plain (pcond=None) chain
 
 
+def test_clip_text_encoder_vs_transformers_golden():
+    """FrozenCLIPEmbedder (modules.py:137-163) on the B200 kernels vs transformers' CLIPTextModel (golden) and the oracle."""
+    import fgdm_oracle as orc
+    from fgdm_b200.clip import FrozenCLIPEmbedder
+    sd = gc.clip_state_dict()
+    enc = FrozenCLIPEmbedder(device=DEV)
+    assert enc.param_shapes() == {k: tuple(v) for k, v in gc.clip_param_shapes().items()}
+    enc.load_state_dict(sd)
+    ids = gc.clip_case()["ids"]
+    z = enc.encode(ids.to(DEV))
+    g = gold("clip_text")["z"]
+    assert z.shape == (2, 77, 768) and z.dtype == torch.bfloat16
+    print("clip text: relmax", relmax(z, g), "psnr", psnr(z, g, float(np.abs(g).max())))
+    assert relmax(z, g) < 3e-2 and psnr(z, g, float(np.abs(g).max())) > 40.0
+    # causal mask: position i ignores later tokens; shorter sequences and a batch of one work
+    ids2 = ids.clone()
+    ids2[:, 5:] = 1234
+    z2 = enc.encode(ids2.to(DEV))
+    assert torch.equal(z2[:, :5], z[:, :5]) and relmax(z2[:, 5:], z[:, 5:].float().cpu().numpy()) > 1e-2
+    sd_dev = {k: v.to(DEV) for k, v in sd.items()}
+    z3 = enc.encode(ids[:1, :20].to(DEV))
+    ref3 = orc.clip_text_forward(sd_dev, ids[:1, :20].to(DEV))
+    assert relmax(z3, ref3.cpu().numpy()) < 3e-2
+    with pytest.raises(NotImplementedError):
+        enc.encode(["a photo of a cat"])
+    # wired in through the reference's config: cond_stage_config target FrozenCLIPEmbedder (models/config.yaml:74-75)
+    cfg = gc.fgdm_config()
+    cfg["params"] = dict(cfg["params"], cond_stage_config={"target": "ldm.modules.encoders.modules.FrozenCLIPEmbedder"})
+    ldm = instantiate_from_config(cfg)
+    ldm.cond_stage_model.load_state_dict(sd)
+    assert torch.equal(ldm.get_learned_conditioning(ids.to(DEV)), z)
+    ctx = torch.randn(1, 77, 768, device=DEV)
+    assert ldm.get_learned_conditioning(ctx) is ctx
+    with pytest.raises(ValueError):
+        enc.encode(torch.full((1, 77), 60000, dtype=torch.int64))     # id outside the vocabulary
+
+
 def test_plms_loop_vs_reference_golden(fgdm):
     """PLMSSampler (plms.py) on the captured model-call graph + fgdm_plms_step, against the reference's sampler."""
     from fgdm_b200.plms import PLMSSampler

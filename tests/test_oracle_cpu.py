@@ -55,6 +55,22 @@ def test_oracle_unet_pcond_matches_reference_golden(sd_fgdm):
     assert relmax(plain, gold("unet_pcond")["eps"]) > 1e-2      # the pcond branch really changes the result
 
 
+def test_oracle_clip_text_matches_transformers_golden():
+    """FrozenCLIPEmbedder.forward (modules.py:137-163) = transformers CLIPTextModel(...).last_hidden_state."""
+    sd = gc.clip_state_dict()
+    with torch.no_grad():
+        z = orc.clip_text_forward(sd, gc.clip_case()["ids"])
+    g = gold("clip_text")["z"]
+    assert z.shape == (2, 77, 768)
+    assert relmax(z, g) < 1e-4
+    # causal: the hidden state of position i does not depend on later tokens
+    ids2 = gc.clip_case()["ids"].clone()
+    ids2[:, 5:] = 1234
+    with torch.no_grad():
+        z2 = orc.clip_text_forward(sd, ids2)
+    assert torch.allclose(z2[:, :5], z[:, :5], atol=1e-5) and not torch.allclose(z2[:, 5:], z[:, 5:], atol=1e-3)
+
+
 def test_oracle_plms_loop_matches_reference_golden(sd_fgdm):
     """PLMSSampler.sample (plms.py): Euler start + Adams-Bashforth orders 2-4, vs the reference's own sampler."""
     c, g = gc.plms_case(), gold("plms_fgdm")
