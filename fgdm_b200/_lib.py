@@ -53,6 +53,8 @@ SIGNATURES = {
     "fgdm_cfg_ddim_step": [vp, vp, vp, vp, vp, vp, C.c_int, C.c_float, C.c_float, vp, vp, C.c_int, vp],
     "fgdm_plms_step": [vp, vp, vp, vp, vp, C.POINTER(C.c_float), vp, vp, C.c_int, C.c_float, vp, vp, vp, C.c_int, vp],
     "fgdm_timestep_embedding": [vp, vp, vp, C.c_int, C.c_int, vp],
+    "fgdm_timestep_embedding_f32": [vp, vp, vp, C.c_int, C.c_int, vp],
+    "fgdm_lincomb3": [C.c_float, vp, C.c_float, vp, C.c_float, vp, vp, C.c_int, vp],
     "fgdm_skinny_linear": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_resample": [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_add_bf16": [vp, vp, vp, C.c_size_t, vp],

@@ -101,6 +101,9 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
                 cudaStream_t stream, int* stats_slots_out = nullptr);
 int launch_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int Nq, int Nk,
                      int d, int tok_pad, float scale, int causal, cudaStream_t stream);
+int launch_timestep_embedding_f32(const float* t, const float* freqs, float* out, int rows, int dim, cudaStream_t stream);
+int launch_lincomb3(float a, const float* x, float b, const float* y, float c, const float* z, float* out, int n,
+                    cudaStream_t stream);
 int launch_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_emb, void* out, int rows, int seq,
                         int dim, int vocab, cudaStream_t stream);
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
@@ -333,6 +336,17 @@ int fgdm_cfg_ddim_step(const float* e_uncond, const float* e_cond, const float* 
   FGDM_NONNULL(x_prev, "x_prev");
   return launch_cfg_ddim(e_uncond, e_cond, x, noise, coef_table, index_ptr, index, scale, temperature, x_prev, pred_x0,
                          n, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_timestep_embedding_f32(const float* t, const float* freqs, float* out, int rows, int dim, void* stream) {
+  FGDM_NONNULL(t, "t"); FGDM_NONNULL(freqs, "freqs"); FGDM_NONNULL(out, "out");
+  return launch_timestep_embedding_f32(t, freqs, out, rows, dim, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_lincomb3(float a, const float* x, float b, const float* y, float c, const float* z, float* out, int n,
+                  void* stream) {
+  FGDM_NONNULL(x, "x"); FGDM_NONNULL(out, "out");
+  return launch_lincomb3(a, x, b, y, c, z, out, n, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int fgdm_timestep_embedding(const int64_t* t, const float* freqs, float* out, int rows, int dim, void* stream) {

@@ -164,7 +164,8 @@ int launch_ddim_advance(int* counter, const long long* t_table, const int* idx_t
 // timestep_embedding (ldm/modules/diffusionmodules/util.py:160-180): out[r] = [cos(t f), sin(t f)]
 // with the frequency table computed on the host exactly as the reference does.
 // ---------------------------------------------------------------------------------------------
-__global__ void timestep_embedding_kernel(const long long* __restrict__ t, const float* __restrict__ freqs,
+template <typename T>
+__global__ void timestep_embedding_kernel(const T* __restrict__ t, const float* __restrict__ freqs,
                                           float* __restrict__ out, int rows, int half) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= rows * half) return;
@@ -178,8 +179,43 @@ int launch_timestep_embedding(const long long* t, const float* freqs, float* out
                               cudaStream_t stream) {
   if (dim % 2) { set_error("timestep_embedding: odd dim %d", dim); return -1; }
   const int n = rows * (dim / 2);
-  timestep_embedding_kernel<<<(n + 255) / 256, 256, 0, stream>>>(t, freqs, out, rows, dim / 2);
+  timestep_embedding_kernel<long long><<<(n + 255) / 256, 256, 0, stream>>>(t, freqs, out, rows, dim / 2);
   return check_launch("timestep_embedding_kernel");
+}
+
+// float timesteps: DPM-Solver feeds the UNet t = (t_continuous - 1/N) * 1000 (dpm_solver.py:278-287)
+int launch_timestep_embedding_f32(const float* t, const float* freqs, float* out, int rows, int dim,
+                                  cudaStream_t stream) {
+  if (dim % 2) { set_error("timestep_embedding: odd dim %d", dim); return -1; }
+  const int n = rows * (dim / 2);
+  timestep_embedding_kernel<float><<<(n + 255) / 256, 256, 0, stream>>>(t, freqs, out, rows, dim / 2);
+  return check_launch("timestep_embedding_kernel<float>");
+}
+
+// out = a * x + b * y + c * z (y, z optional): the x_t update of DPM-Solver++ multistep (dpm_solver.py:504-535,755-796),
+// whose terms are all scalar multiples of x and of the last two x0-predictions. In place (out == x) allowed.
+__global__ void lincomb3_kernel(float a, const float* __restrict__ x, float b, const float* __restrict__ y, float c,
+                                const float* __restrict__ z, float* __restrict__ out, int n) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= n) return;
+  const float4 xv = *reinterpret_cast<const float4*>(x + i);
+  float4 r = make_float4(a * xv.x, a * xv.y, a * xv.z, a * xv.w);
+  if (y) {
+    const float4 v = *reinterpret_cast<const float4*>(y + i);
+    r.x += b * v.x; r.y += b * v.y; r.z += b * v.z; r.w += b * v.w;
+  }
+  if (z) {
+    const float4 v = *reinterpret_cast<const float4*>(z + i);
+    r.x += c * v.x; r.y += c * v.y; r.z += c * v.z; r.w += c * v.w;
+  }
+  *reinterpret_cast<float4*>(out + i) = r;
+}
+
+int launch_lincomb3(float a, const float* x, float b, const float* y, float c, const float* z, float* out, int n,
+                    cudaStream_t stream) {
+  if (n % 4 != 0) { set_error("lincomb3: n=%d must be a multiple of 4", n); return -1; }
+  lincomb3_kernel<<<(n / 4 + 255) / 256, 256, 0, stream>>>(a, x, b, y, c, z, out, n);
+  return check_launch("lincomb3_kernel");
 }
 
 // ---------------------------------------------------------------------------------------------

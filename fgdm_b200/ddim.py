@@ -46,14 +46,14 @@ def make_ddim_sampling_parameters(alphacums, ddim_timesteps, eta, verbose=True):
 class _StepGraph:
     """One captured DDIM step for fixed (model, B, latent shape, context length, CFG on/off)."""
 
-    def __init__(self, model, B, shape, ctx_len, cfg, S_max=1000, pcond_rows=0):
+    def __init__(self, model, B, shape, ctx_len, cfg, S_max=1000, pcond_rows=0, float_t=False):
         dev = model.device
         self.model, self.B, self.cfg = model, B, cfg
         self.R = 2 * B if cfg else B
         C, H, W = shape
         self.x = torch.zeros((B, C, H, W), device=dev, dtype=torch.float32)
         self.pred_x0 = torch.zeros_like(self.x)
-        self.t = torch.zeros((self.R,), device=dev, dtype=torch.int64)
+        self.t = torch.zeros((self.R,), device=dev, dtype=torch.float32 if float_t else torch.int64)
         self.index = torch.zeros((1,), device=dev, dtype=torch.int32)
         self.counter = torch.zeros((1,), device=dev, dtype=torch.int32)
         self.t_table = torch.zeros((S_max,), device=dev, dtype=torch.int64)
@@ -129,7 +129,7 @@ class _StepGraph:
             self.eps_graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.eps_graph):
                 self.eps_out = self._eps()
-        self.t.fill_(int(t))
+        self.t.fill_(float(t) if self.t.is_floating_point() else int(t))
         self.eps_graph.replay()
         ops.count_launches(self.eps_launches)
         return self.eps_out[:self.B], (self.eps_out[self.B:] if self.cfg else None)

@@ -88,6 +88,12 @@ def plms_case():
                 c=synth.randn((1, 77, 768), 35), uc=synth.randn((1, 77, 768), 36))
 
 
+def dpm_case():
+    """DPM-Solver++(2M) via DPMSolverSampler: 5 steps (< 15: the final step drops to first order)."""
+    return dict(S=5, B=1, shape=(4, 16, 16), scale=7.5, x_T=synth.randn((1, 4, 16, 16), 37),
+                c=synth.randn((1, 77, 768), 38), uc=synth.randn((1, 77, 768), 39))
+
+
 CLIP_WEIGHT_SEED = 7
 
 

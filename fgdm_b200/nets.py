@@ -195,7 +195,9 @@ class _UNetBase(_Net):
         return [s.project_context(ctx) for s in self._sts]
 
     def _emb(self, timesteps):
-        emb = self.time_embed.forward(timesteps.to(torch.int64).contiguous())
+        # int64 steps (DDIM/PLMS) or DPM-Solver's fractional float32 timesteps (util.py:160-180 takes either)
+        ts = timesteps.to(torch.float32 if timesteps.is_floating_point() else torch.int64).contiguous()
+        emb = self.time_embed.forward(ts)
         return ops.skinny_linear(emb, self.w_emb, self.b_emb, in_act=True)   # emb_layers = SiLU, Linear
 
     def _run(self, blk, h, h1, emb_all, kvs, res1=None):

@@ -238,8 +238,20 @@ def plms_step(e_uncond, e_cond, hist, weights, x, coef_table, index, scale, *, e
 
 
 def timestep_embedding(t, freqs, dim):
+    """t: int64 (DDIM/PLMS) or float32 (DPM-Solver's fractional timesteps) [rows]."""
     out = torch.empty((t.shape[0], dim), device=t.device, dtype=torch.float32)
-    _call("fgdm_timestep_embedding", ("temb", 0.0, 4.0 * t.shape[0] * dim), _p(t), _p(freqs), _p(out), t.shape[0], dim, _stream())
+    fn = "fgdm_timestep_embedding_f32" if t.dtype == torch.float32 else "fgdm_timestep_embedding"
+    assert t.dtype in (torch.float32, torch.int64)
+    _call(fn, ("temb", 0.0, 4.0 * t.shape[0] * dim), _p(t), _p(freqs), _p(out), t.shape[0], dim, _stream())
+    return out
+
+
+def lincomb3(a, x, b=0.0, y=None, c=0.0, z=None, out=None):
+    """out = a x + b y + c z on fp32 tensors (y, z optional)."""
+    if out is None:
+        out = torch.empty_like(x)
+    _call("fgdm_lincomb3", ("lincomb3", 0.0, 16.0 * x.numel()), float(a), _p(x), float(b), _p(y), float(c), _p(z), _p(out),
+          x.numel(), _stream())
     return out
 
 

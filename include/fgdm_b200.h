@@ -155,6 +155,12 @@ int fgdm_ddim_advance(int* counter, const int64_t* t_table, const int* idx_table
 
 /* timestep_embedding: util.py:160-180. t int64 [rows]; freqs fp32 [dim/2]; out fp32 [rows, dim]. */
 int fgdm_timestep_embedding(const int64_t* t, const float* freqs, float* out, int rows, int dim, void* stream);
+/* same with float timesteps: DPM-Solver calls the UNet at t = (t_continuous - 1/N) * 1000 (dpm_solver.py:278-287) */
+int fgdm_timestep_embedding_f32(const float* t, const float* freqs, float* out, int rows, int dim, void* stream);
+/* out = a x + b y + c z (y, z may be NULL; out == x allowed): x_t update of DPM-Solver++ multistep,
+ * dpm_solver.py:504-535 (first order) and :755-796 (second order), predict_x0 branches. */
+int fgdm_lincomb3(float a, const float* x, float b, const float* y, float c, const float* z, float* out, int n,
+                  void* stream);
 
 /* Skinny Linear y = out_act(in_act(x) W^T + b), x/y fp32 [rows, k]/[rows, n], W bf16 [n, k]: time_embed
  * (openaimodel.py:538-542) and the batched ResBlock emb_layers (openaimodel.py:238-244). act: 0 none, 1 SiLU. */

@@ -431,6 +431,81 @@ def ddim_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod,
 
 
 # ----------------------------------------------------------------------------------------------
+# DPM-Solver++ (2M): DPMSolverSampler.sample, ldm/models/diffusion/dpm_solver/sampler.py:23-82, which fixes the
+# configuration to NoiseScheduleVP('discrete'), model_type "noise", classifier-free guidance, predict_x0=True,
+# multistep order 2, skip_type "time_uniform", lower_order_final=True (dpm_solver.py line numbers below).
+# ----------------------------------------------------------------------------------------------
+def dpm_schedule(alphas_cumprod):
+    """NoiseScheduleVP('discrete', alphas_cumprod=...), dpm_solver.py:99-108."""
+    log_alphas = 0.5 * torch.log(alphas_cumprod.float())
+    n = log_alphas.shape[0]
+    return dict(N=n, t_array=torch.linspace(0., 1., n + 1)[1:], log_alpha=log_alphas)
+
+
+def dpm_marginals(sched, t):
+    """marginal_log_mean_coeff / alpha / std / lambda at continuous t in [1/N, 1], dpm_solver.py:125-156 with the
+    piecewise-linear interpolate_fn (:1132-1171; inside the knot range it is plain linear interpolation)."""
+    xp, yp = sched["t_array"].double().numpy(), sched["log_alpha"].double().numpy()
+    la = torch.tensor(np.interp(np.asarray(t, dtype=np.float64), xp, yp), dtype=torch.float32)
+    return dict(log_alpha=la, alpha=torch.exp(la), sigma=torch.sqrt(1. - torch.exp(2. * la)),
+                lam=la - 0.5 * torch.log(1. - torch.exp(2. * la)))
+
+
+def dpm_solver_sample(apply_model, S, shape, cond, uncond, scale, x_T, alphas_cumprod, record=None):
+    """DPM_Solver.sample(method='multistep', order=2), dpm_solver.py:1060-1096; model_wrapper's classifier-free
+    model_fn (:321-344) with t_input = (t - 1/N) * 1000 (:278-287, a FLOAT timestep); data_prediction_fn (:386-399);
+    dpm_solver_first_update (:504-535) and multistep_dpm_solver_second_update (:755-796), predict_x0 branches."""
+    sched = dpm_schedule(alphas_cumprod)
+    n = sched["N"]
+    ts = torch.linspace(1.0, 1.0 / n, S + 1)                    # get_time_steps('time_uniform'), :429-430
+    mg = dpm_marginals(sched, ts.numpy())
+    b = shape[0]
+    x = x_T
+
+    def model_fn(x, i):                                         # -> x0 prediction at timesteps[i]
+        t_in = ((ts[i] - 1. / n) * 1000.).to(x.device).expand(b)
+        if uncond is None or scale == 1.0:
+            e = apply_model(x, t_in, cond)
+        else:
+            e_u, e_c = apply_model(torch.cat([x] * 2), torch.cat([t_in] * 2), torch.cat([uncond, cond])).chunk(2)
+            e = e_u + scale * (e_c - e_u)
+        return (x - mg["sigma"][i] * e) / mg["alpha"][i]
+
+    def first(x, s, t, m_s):
+        h = mg["lam"][t] - mg["lam"][s]
+        return (mg["sigma"][t] / mg["sigma"][s]) * x - (mg["alpha"][t] * torch.expm1(-h)) * m_s
+
+    def second(x, p1, p0, t, m1, m0):
+        h_0 = mg["lam"][p0] - mg["lam"][p1]
+        h = mg["lam"][t] - mg["lam"][p0]
+        r0 = h_0 / h
+        d1 = (1. / r0) * (m0 - m1)
+        a = mg["alpha"][t] * (torch.exp(-h) - 1.)
+        return (mg["sigma"][t] / mg["sigma"][p0]) * x - a * m0 - 0.5 * a * d1
+
+    assert S >= 2
+    models, tprev = [model_fn(x, 0)], [0]
+    x = first(x, 0, 1, models[-1])                              # init_order = 1
+    if record is not None:
+        record.append(x)
+    models.append(model_fn(x, 1))
+    tprev.append(1)
+    for step in range(2, S + 1):
+        order = min(2, S + 1 - step) if S < 15 else 2           # lower_order_final
+        if order == 1:
+            x = first(x, tprev[-1], step, models[-1])
+        else:
+            x = second(x, tprev[0], tprev[1], step, models[0], models[1])
+        if record is not None:
+            record.append(x)
+        tprev[0], models[0] = tprev[1], models[1]
+        tprev[1] = step
+        if step < S:
+            models[1] = model_fn(x, step)
+    return x
+
+
+# ----------------------------------------------------------------------------------------------
 # text conditioning: FrozenCLIPEmbedder.forward, ldm/modules/encoders/modules.py:137-163
 # ----------------------------------------------------------------------------------------------
 # The arithmetic lives in a third-party dependency that is not vendored in the reference: Hugging Face

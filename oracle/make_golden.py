@@ -6,7 +6,7 @@
 3. writes the reference's outputs as golden fixtures to tests/golden/*.npz (inputs are re-derived from
    the seeds stored alongside, weights from the weight seed).
 
-Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond|plms|clip]
+Usage: python oracle/make_golden.py [--only fgdm|control|misc|pcond|plms|dpm|clip]
 """
 from __future__ import annotations
 
@@ -191,6 +191,28 @@ def golden_plms(model=None, sd=None):
              n_inter=len(inter["x_inter"]))
 
 
+def golden_dpm(model=None, sd=None):
+    """DPMSolverSampler.sample (dpm_solver/sampler.py) through the reference's own solver."""
+    if model is None:
+        model = rh.build_fgdm()
+        sd = load_weights(model, gc.fgdm_param_shapes(), gc.FGDM_WEIGHT_SEED)
+    from ldm.models.diffusion.dpm_solver import sampler as ds
+    ds.DPMSolverSampler.register_buffer = lambda self, name, attr: setattr(self, name, attr)   # reference forces cuda
+    with torch.no_grad():
+        case = gc.dpm_case()
+        smp = ds.DPMSolverSampler(model)
+        x0, _ = smp.sample(S=case["S"], conditioning=case["c"], batch_size=case["B"], shape=case["shape"],
+                           verbose=False, unconditional_guidance_scale=case["scale"],
+                           unconditional_conditioning=case["uc"], eta=0.0, x_T=case["x_T"])
+        rec = []
+        x0_orc = orc.dpm_solver_sample(
+            lambda x, t, c: orc.unet_forward(sd, x, t, c, prefix="model.diffusion_model."), case["S"],
+            (case["B"],) + tuple(case["shape"]), case["c"], case["uc"], case["scale"], case["x_T"],
+            model.alphas_cumprod, record=rec)
+        check("DPMSolverSampler.sample final latent", x0_orc, x0, tol=1e-3)
+        save("dpm_fgdm", x0=x0, steps=torch.stack(rec))
+
+
 def golden_clip():
     """FrozenCLIPEmbedder.forward (modules.py:137-163) = transformers CLIPTextModel(...).last_hidden_state: the
     dependency itself, built from its config with the seeded synthetic weights (no checkpoint download)."""
@@ -305,6 +327,8 @@ if __name__ == "__main__":
         golden_pcond()
     if a.only == "plms":
         golden_plms()
+    if a.only in ("all", "dpm"):
+        golden_dpm()
     if a.only in ("all", "clip"):
         golden_clip()
     if a.only in ("all", "control"):

@@ -328,6 +328,22 @@ def test_cfg_ddim():
     assert torch.equal(xp, xp2)
 
 
+def test_lincomb3_and_float_timestep_embedding():
+    x, y, z = (torch.randn(2, 4, 64, 64, device=DEV) for _ in range(3))
+    torch.testing.assert_close(ops.lincomb3(0.7, x, -1.3, y, 0.25, z), 0.7 * x - 1.3 * y + 0.25 * z, rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(ops.lincomb3(0.7, x, -1.3, y), 0.7 * x - 1.3 * y, rtol=1e-6, atol=1e-6)
+    xc = x.clone()
+    ops.lincomb3(2.0, xc, 1.0, y, out=xc)
+    torch.testing.assert_close(xc, 2.0 * x + y, rtol=1e-6, atol=1e-6)
+    freqs = ops.timestep_freqs(320).to(DEV)
+    t = torch.tensor([999.0, 749.25, 0.0, 12.5], device=DEV)
+    e = ops.timestep_embedding(t, freqs, 320)
+    arg = t[:, None] * freqs[None]
+    torch.testing.assert_close(e, torch.cat([arg.cos(), arg.sin()], -1), rtol=1e-4, atol=2e-4)
+    ti = torch.tensor([999, 749, 0, 12], device=DEV)
+    torch.testing.assert_close(ops.timestep_embedding(ti, freqs, 320), ops.timestep_embedding(ti.float(), freqs, 320))
+
+
 def test_plms_step():
     """fgdm_plms_step vs plms.py:178-234 in torch (CFG combine, Adams-Bashforth blend, x_prev / pred_x0)."""
     torch.manual_seed(3)

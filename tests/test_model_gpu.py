@@ -135,6 +135,26 @@ def test_clip_text_encoder_vs_transformers_golden():
         enc.encode(torch.full((1, 77), 60000, dtype=torch.int64))     # id outside the vocabulary
 
 
+def test_dpm_solver_vs_reference_golden(fgdm):
+    """DPMSolverSampler (DPM-Solver++ 2M) on the captured model-call graph, against the reference's solver."""
+    from fgdm_b200.dpm_solver import DPMSolverSampler
+    model, _ = fgdm
+    c, g = gc.dpm_case(), gold("dpm_fgdm")
+    kw = dict(S=c["S"], conditioning=c["c"].to(DEV), batch_size=c["B"], shape=list(c["shape"]), verbose=False,
+              unconditional_guidance_scale=c["scale"], unconditional_conditioning=c["uc"].to(DEV), eta=0.0,
+              x_T=c["x_T"].to(DEV))
+    sampler = DPMSolverSampler(model)
+    x0, extra = sampler.sample(**kw)
+    assert extra is None
+    peak = float(np.abs(g["x0"]).max())
+    print("dpm fgdm: relmax", relmax(x0, g["x0"]), "psnr", psnr(x0, g["x0"], peak))
+    assert relmax(x0, g["x0"]) < 8e-2 and psnr(x0, g["x0"], peak) > 35.0
+    x0b, _ = sampler.sample(**kw)
+    assert torch.equal(x0b, x0)                                # graph replay is reproducible bit for bit
+    x20, _ = sampler.sample(**{**kw, "S": 20})                 # S >= 15: second order to the end
+    assert torch.isfinite(x20).all()
+
+
 def test_plms_loop_vs_reference_golden(fgdm):
     """PLMSSampler (plms.py) on the captured model-call graph + fgdm_plms_step, against the reference's sampler."""
     from fgdm_b200.plms import PLMSSampler

@@ -71,6 +71,19 @@ def test_oracle_clip_text_matches_transformers_golden():
     assert torch.allclose(z2[:, :5], z[:, :5], atol=1e-5) and not torch.allclose(z2[:, 5:], z[:, 5:], atol=1e-3)
 
 
+def test_oracle_dpm_solver_matches_reference_golden(sd_fgdm):
+    """DPMSolverSampler.sample (dpm_solver/sampler.py: DPM-Solver++ 2M, float model timesteps) vs the reference."""
+    c, g = gc.dpm_case(), gold("dpm_fgdm")
+    rec = []
+    with torch.no_grad():
+        x0 = orc.dpm_solver_sample(
+            lambda x, t, cc: orc.unet_forward(sd_fgdm, x, t, cc, prefix="model.diffusion_model."), c["S"],
+            (c["B"],) + tuple(c["shape"]), c["c"], c["uc"], c["scale"], c["x_T"],
+            orc.make_schedule_buffers()["alphas_cumprod"], record=rec)
+    assert relmax(x0, g["x0"]) < 1e-3
+    assert len(rec) == c["S"] and relmax(rec[-1], g["x0"]) < 1e-3
+
+
 def test_oracle_plms_loop_matches_reference_golden(sd_fgdm):
     """PLMSSampler.sample (plms.py): Euler start + Adams-Bashforth orders 2-4, vs the reference's own sampler."""
     c, g = gc.plms_case(), gold("plms_fgdm")
