@@ -331,8 +331,9 @@ class BasicTransformerBlock(Layer):
     def load(self, sd, prefix, dev):
         for n in ("norm1", "norm2", "norm3"):
             self.children[n].load(sd, prefix + n + ".", dev)
-        wide = self.norm1.c >= self.FOLD_MIN_DIM
-        for consumer, norm, fold in ((self.attn1, self.norm1, wide), (self.attn2, self.norm2, True),
+        on = os.environ.get("FGDM_LN_FOLD", "1") != "0"           # 0: every LayerNorm runs as its own kernel
+        wide = on and self.norm1.c >= self.FOLD_MIN_DIM
+        for consumer, norm, fold in ((self.attn1, self.norm1, wide), (self.attn2, self.norm2, on),
                                      (self.ff.net[0], self.norm3, wide)):
             consumer.ln, consumer.ln_fold = norm, fold
         for n in ("attn1", "ff", "attn2"):
