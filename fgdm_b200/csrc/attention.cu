@@ -85,7 +85,8 @@ FGDM_DEVINL void named_bar_sync(int id, int threads) {
 // The softmax denominator is NOT accumulated on the CUDA cores: V^T row `dv_real` of every tile is overwritten with
 // 1.0, so O[:, dv_real] = sum_j P[:, j] comes out of the PV tensor-core product (from the same bf16-rounded P as
 // the numerator) and is rescaled together with O.
-template <int KA, int DV, int BN, int QTN>
+// CAUSAL is a template parameter: as a run-time flag its per-row key limit spilled the d = 40 self-attention kernel.
+template <int KA, int DV, int BN, int QTN, bool CAUSAL = false>
 __global__ void __launch_bounds__(AttnWarps<QTN>::kThreads, AttnCfg<KA, DV, BN, QTN>::kMinBlocks)
 attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
@@ -266,8 +267,8 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 
     for (int j = 0; j < num_kv; ++j) {
       int valid = p.Nk - j * BN - half * HB;             // keys valid in this thread's half tile (may exceed HB)
-      if (p.causal) valid = min(valid, q0 + t * 128 + row + 1 - j * BN - half * HB);   // per row: keys j <= i
-      const bool full = !p.causal && valid >= HB;        // warp-uniform
+      if constexpr (CAUSAL) valid = min(valid, q0 + t * 128 + row + 1 - j * BN - half * HB);   // per row: keys j <= i
+      const bool full = !CAUSAL && valid >= HB;          // warp-uniform
       mbar_wait(&bar_s[t], j & 1);
       tc_fence_after();
 
@@ -408,13 +409,13 @@ attention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
   }
 }
 
-template <int KA, int DV, int BN, int QTN>
+template <int KA, int DV, int BN, int QTN, bool CAUSAL = false>
 static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
                          int nsplit, cudaStream_t stream) {
   using Cfg = AttnCfg<KA, DV, BN, QTN>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention_kernel<KA, DV, BN, QTN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(attention_kernel<KA, DV, BN, QTN, CAUSAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("attention: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -423,7 +424,7 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
     configured = true;
   }
   dim3 grid((p.Nq + 128 * QTN - 1) / (128 * QTN), p.BH, nsplit);
-  cudaError_t e = launch_pdl(attention_kernel<KA, DV, BN, QTN>, grid, dim3(AttnWarps<QTN>::kThreads), Cfg::kSmemBytes, stream,
+  cudaError_t e = launch_pdl(attention_kernel<KA, DV, BN, QTN, CAUSAL>, grid, dim3(AttnWarps<QTN>::kThreads), Cfg::kSmemBytes, stream,
                              mq, mk, mv, p);
   if (e != cudaSuccess) { set_error("attention_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("attention_kernel");
@@ -432,6 +433,8 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
 template <int KA, int DV, int BN>
 static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
                        int nsplit, cudaStream_t stream) {
+  // causal (CLIP text, 77 tokens): the one-tile CTA instance only
+  if (p.causal) return launch_attn_q<KA, DV, BN, 1, true>(mq, mk, mv, p, nsplit, stream);
   // short KV (text cross-attention) or a single query tile: the one-tile CTA; otherwise two query tiles per CTA
   if (p.Nk <= 2 * BN || p.Nq <= 128) return launch_attn_q<KA, DV, BN, 1>(mq, mk, mv, p, nsplit, stream);
   return launch_attn_q<KA, DV, BN, 2>(mq, mk, mv, p, nsplit, stream);
