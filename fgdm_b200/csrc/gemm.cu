@@ -490,6 +490,86 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
           if (finish) __threadfence();
         }
 
+        // Lean path for the common epilogue (bf16 out, bias, optional first residual / row statistics, nothing else):
+        // the short-K transformer linears are paced by the INSTRUCTION COUNT of this loop (ncu: 372 per 32x32 panel in
+        // the generic loop, ~220 of them address arithmetic, mode tests and constant loads), so pointers and row masks
+        // are hoisted out of the panel loop and every mode test is gone.
+        const bool lean = staged && !partial && p.bias != nullptr && p.rowvec == nullptr && p.alpha == 1.0f &&
+                          p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr && (p.N & 31) == 0;
+        if (lean) {
+          const int col0 = n_tile * BN + half * 32;
+          const __nv_bfloat16* rptr[4];
+          __nv_bfloat16* optr[4];
+          uint32_t sst[4], sld[4];
+          bool ok[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int idx = lane + 32 * q, rr = idx >> 2, ch = idx & 3;
+            ok[q] = m_warp + rr < p.M;
+            const size_t mrow = static_cast<size_t>(ok[q] ? m_warp + rr : 0);
+            rptr[q] = pre_res ? p.res0 + mrow * p.ld_res0 + col0 + ch * 8 : nullptr;
+            optr[q] = reinterpret_cast<__nv_bfloat16*>(p.out) + mrow * p.ldo + p.col_off + col0 + ch * 8;
+            sld[q] = stg_u32 + rr * kStgRow + ch * 16;          // coalesced view: (row rr, 16-byte chunk ch)
+            sst[q] = stg_u32 + lane * kStgRow + q * 16;         // row-owner view: (row lane, chunk q)
+          }
+          const int npv = min(np, (p.N - col0 + 63) / 64);       // this warp's panels that lie inside N
+#pragma unroll 1
+          for (int i = 0; i < npv; ++i) {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
+            if (pre_res) {                                       // residual panel i: coalesced registers -> smem
+#pragma unroll
+              for (int q = 0; q < 4; ++q) st_shared_16(sld[q], rres[q]);
+              if (i + 1 < npv) {                                 // panel i + 1 is in flight during this one
+#pragma unroll
+                for (int q = 0; q < 4; ++q) rres[q] = ok[q] ? *reinterpret_cast<const uint4*>(rptr[q] + 64 * (i + 1)) : make_uint4(0, 0, 0, 0);
+              }
+              __syncwarp();
+            }
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const uint4 u = ld_shared_16(sbias_u32 + i * 128 + j * 4);
+              v[j] = __uint_as_float(r[j]) + __uint_as_float(u.x);
+              v[j + 1] = __uint_as_float(r[j + 1]) + __uint_as_float(u.y);
+              v[j + 2] = __uint_as_float(r[j + 2]) + __uint_as_float(u.z);
+              v[j + 3] = __uint_as_float(r[j + 3]) + __uint_as_float(u.w);
+            }
+            if (pre_res) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint4 u = ld_shared_16(sst[q]);
+                const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float2 f = unpack_bf16x2(w4[e]);
+                  v[q * 8 + e * 2] += f.x;
+                  v[q * 8 + e * 2 + 1] += f.y;
+                }
+              }
+            }
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+            if (p.row_stats) {       // statistics of the ROUNDED values: exactly what the consuming GEMM multiplies
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const float2 f = unpack_bf16x2(pk[j]);
+                rs_sum += f.x + f.y;
+                rs_sq = fmaf(f.x, f.x, fmaf(f.y, f.y, rs_sq));
+              }
+            }
+            // (a lane overwrites only the row it has just read: no barrier needed before the stores)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) st_shared_16(sst[q], make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]));
+            __syncwarp();
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              if (ok[q]) *reinterpret_cast<uint4*>(optr[q] + 64 * i) = ld_shared_16(sld[q]);
+            __syncwarp();
+          }
+        } else
 #pragma unroll 1
         for (int i = 0; finish && i < np; ++i) {
           {
