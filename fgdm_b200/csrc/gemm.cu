@@ -955,7 +955,11 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   // FGDM_PAIR=0 never, FGDM_PAIR=1 wherever the kernel allows it; bn_hint = 1000 + BN forces it (tests).
   static int pair_mode = -2;
   if (pair_mode == -2) { const char* e = getenv("FGDM_PAIR"); pair_mode = e ? atoi(e) : -1; }
-  const bool want_pair = force_pair || pair_mode == 1 || (pair_mode == -1 && num_k_chunks >= 30);
+  // Threshold re-measured on the final kernels (tools/diag_geglu.py, diag_shortk.py): at K = 1280 (20 chunks) the pair
+  // wins 8-10 % (4096x1280->1280 19.1 -> 17.5 us, GEGLU 4096x1280->10240 76.9 -> 69.6 us); at K = 640 it loses 3-10 %.
+  static int pair_min = -1;
+  if (pair_min < 0) { const char* e = getenv("FGDM_PAIR_MIN"); pair_min = e ? atoi(e) : 20; }
+  const bool want_pair = force_pair || pair_mode == 1 || (pair_mode == -1 && num_k_chunks >= pair_min);
   const int ctas = (want_pair && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
   if (p.range_ctas) {
     if (static_cast<size_t>(p.range_ctas) * 2 * kBM * BN * 4 > kSplitWsBytes) { set_error("gemm: range scratch too small"); return -1; }
