@@ -951,7 +951,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   // L2->SM operand traffic per FLOP - the bound of this kernel once the producer loop is lean (every tile width moves
   // ~110 GB/s per SM). Measured on B200 (tools/bench_bn.py, m=65536 k=2880 n=1280): BN=160 1198 -> 1328, 224 1291 ->
   // 1391, 256 1360 -> 1450 TFLOP/s; in the UNet the 3x3 convs gain 7-19 %, K = 1920/2560 linears 10-13 %, K = 1280 is a
-  // wash and K <= 960 loses 6-16 % (cluster launch + pair hand-offs on a short K loop). Hence: pairs from 30 K chunks up.
+  // wash and K <= 960 loses 6-16 % (cluster launch + pair hand-offs on a short K loop). Hence pairs from 30 K chunks up at first; K = 1280 (20 chunks) was measured later and wins too (below).
   // FGDM_PAIR=0 never, FGDM_PAIR=1 wherever the kernel allows it; bn_hint = 1000 + BN forces it (tests).
   static int pair_mode = -2;
   if (pair_mode == -2) { const char* e = getenv("FGDM_PAIR"); pair_mode = e ? atoi(e) : -1; }
