@@ -95,10 +95,16 @@ class CLIPTextTransformer(Layer):
 
 
 class FrozenCLIPEmbedder:
-    """modules.py:137-163. `transformer.text_model.*` parameters; forward(token ids) -> [B, L, 768] bf16 context."""
+    """modules.py:137-163. `transformer.text_model.*` parameters; forward(token ids | list of str) -> [B, L, 768]
+    bf16 context. Strings are tokenised exactly as modules.py:154-156 does (`CLIPTokenizer(text, truncation=True,
+    max_length=77, padding="max_length")["input_ids"]`) when a tokenizer is available: pass one as `tokenizer=`, or
+    let `transformers.CLIPTokenizer.from_pretrained(version)` find its vocabulary files locally. Those files are a
+    download, not part of the reference repository, so offline without them strings raise and token ids are the
+    input."""
 
-    def __init__(self, version="openai/clip-vit-large-patch14", device="cuda", max_length=77, **cfg):
+    def __init__(self, version="openai/clip-vit-large-patch14", device="cuda", max_length=77, tokenizer=None, **cfg):
         self.version, self.device, self.max_length = version, device, max_length
+        self.tokenizer = tokenizer
         self.text_model = CLIPTextTransformer(**cfg)
 
     def param_shapes(self):
@@ -108,12 +114,28 @@ class FrozenCLIPEmbedder:
         self.text_model.load(sd, "transformer.text_model.", torch.device(self.device))
         return self
 
+    def tokenize(self, text):
+        """modules.py:154-156."""
+        if self.tokenizer is None:
+            try:
+                from transformers import CLIPTokenizer
+                tok = CLIPTokenizer.from_pretrained(self.version, local_files_only=True)
+                if len(tok) < 49408:      # transformers >= 5 hands back an EMPTY tokenizer when the files are absent
+                    raise FileNotFoundError(f"vocabulary of {len(tok)} entries")
+                self.tokenizer = tok
+            except Exception as e:  # vocabulary files absent (no network)
+                raise NotImplementedError(
+                    f"CLIPTokenizer vocabulary for {self.version!r} is not available offline ({type(e).__name__}); pass "
+                    "`tokenizer=` to FrozenCLIPEmbedder or call with the tokenizer's input_ids ([B, <=77] int64)") from e
+        enc = self.tokenizer(text, truncation=True, max_length=self.max_length, return_length=True,
+                             return_overflowing_tokens=False, padding="max_length", return_tensors="pt")
+        return enc["input_ids"]
+
     @torch.no_grad()
     def forward(self, tokens):
         if not torch.is_tensor(tokens):
-            raise NotImplementedError("CLIPTokenizer vocabulary files are not part of the reference repository; pass the "
-                                      "tokenizer's input_ids ([B, <=77] int64)")
-        vocab = self.text_model.tok.w.shape[0]
+            tokens = self.tokenize(list(tokens) if not isinstance(tokens, str) else [tokens])
+        vocab = self.text_model.tok.params["weight"][0]
         if tokens.numel() and (int(tokens.min()) < 0 or int(tokens.max()) >= vocab):       # nn.Embedding's IndexError
             raise ValueError(f"token id outside [0, {vocab})")
         return self.text_model.forward(tokens.to(self.device, torch.int64))

@@ -16,10 +16,10 @@ namespace fgdm {
 // replayed for every step. At 131 k elements this kernel is launch-latency bound, not HBM bound.
 // ---------------------------------------------------------------------------------------------
 __global__ void cfg_ddim_kernel(const float* __restrict__ e_u, const float* __restrict__ e_c,
-                                const float* __restrict__ x, const float* __restrict__ noise,
+                                const float* x, const float* __restrict__ noise,
                                 const float* __restrict__ coef_table, const int* __restrict__ index_ptr, int index,
-                                float scale, float temperature, float* __restrict__ x_prev,
-                                float* __restrict__ pred_x0, int n) {
+                                float scale, float temperature, float* x_prev,
+                                float* __restrict__ pred_x0, int n) {   // x_prev may alias x (in-place step): no restrict
   const int row = index_ptr ? *index_ptr : index;
   const float* cf = coef_table + 5 * row;
   const float s1m = cf[0], sa = cf[1], sap = cf[2], dir = cf[3], sigma = cf[4];
@@ -98,9 +98,9 @@ int launch_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos
 __global__ void plms_step_kernel(const float* __restrict__ e_u, const float* __restrict__ e_c,
                                  const float* __restrict__ h1, const float* __restrict__ h2,
                                  const float* __restrict__ h3, float w0, float w1, float w2, float w3,
-                                 const float* __restrict__ x, const float* __restrict__ coef_table, int index,
-                                 float scale, float* __restrict__ e_out, float* __restrict__ x_prev,
-                                 float* __restrict__ pred_x0, int n) {
+                                 const float* x, const float* __restrict__ coef_table, int index,
+                                 float scale, float* __restrict__ e_out, float* x_prev,
+                                 float* __restrict__ pred_x0, int n) {   // x_prev may alias x: no restrict on the pair
   const float* cf = coef_table + 5 * index;
   const float s1m = cf[0], sa = cf[1], sap = cf[2], dir = cf[3];
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -194,8 +194,8 @@ int launch_timestep_embedding_f32(const float* t, const float* freqs, float* out
 
 // out = a * x + b * y + c * z (y, z optional): the x_t update of DPM-Solver++ multistep (dpm_solver.py:504-535,755-796),
 // whose terms are all scalar multiples of x and of the last two x0-predictions. In place (out == x) allowed.
-__global__ void lincomb3_kernel(float a, const float* __restrict__ x, float b, const float* __restrict__ y, float c,
-                                const float* __restrict__ z, float* __restrict__ out, int n) {
+__global__ void lincomb3_kernel(float a, const float* x, float b, const float* y, float c,
+                                const float* z, float* out, int n) {   // out may alias any input: no restrict
   const int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= n) return;
   const float4 xv = *reinterpret_cast<const float4*>(x + i);

@@ -9,10 +9,13 @@ Fast path (models from fgdm_b200.ldm): one DDIM step = [device-side loop bookkee
 forward on the 2B CFG rows, fused CFG-combine + x_{t-1} update] captured ONCE in a CUDA graph and replayed
 S times with no host work in between. Step-invariant work is hoisted out of the loop: text K/V projections
 of all cross-attentions and the ControlNet hint stem. Options outside the reference's default sampling
-call (mask/x0 inpainting, score_corrector, quantize_x0, noise_dropout, inference_loss, eta > 0 noise on
-the graph path) raise NotImplementedError — there is no slow fallback that silently changes the path.
+call (mask/x0 inpainting, score_corrector, quantize_x0, noise_dropout, inference_loss) raise
+NotImplementedError. eta > 0, ControlNet guess mode (uncond c_concat=None) and foreign models take the per-step
+generic path (`p_sample_ddim` through `apply_model`, same kernels, same arithmetic as the reference's loop).
 """
 from __future__ import annotations
+
+import os
 
 import numpy as np
 import torch
@@ -41,6 +44,17 @@ def make_ddim_sampling_parameters(alphacums, ddim_timesteps, eta, verbose=True):
     a = alphas.numpy()
     sigmas = eta * np.sqrt((1 - alphas_prev) / (1 - a) * (1 - a / alphas_prev))
     return sigmas, alphas, alphas_prev
+
+
+def uncond_hint_matches(cond, uncond, hint_c, hint_u):
+    """True when the unconditional half may reuse the conditional half's ControlNet hint: no unconditional
+    conditioning at all, a non-dict one (FG-DM factor: no hint anywhere), or a dict whose c_concat equals cond's.
+    False for ControlNet guess mode (c_concat=None next to a cond hint) and for differing hints."""
+    if uncond is None or not isinstance(uncond, dict) or not isinstance(cond, dict):
+        return True
+    if hint_u is None or hint_c is None:
+        return hint_u is None and hint_c is None
+    return hint_u is hint_c or (hint_u.shape == hint_c.shape and torch.equal(hint_u, hint_c))
 
 
 class _StepGraph:
@@ -173,7 +187,8 @@ class DDIMSampler(object):
         self.ddpm_num_timesteps = model.num_timesteps
         self.schedule = schedule
         self._graphs = {}
-        self.use_graph = kwargs.get("use_graph", True)
+        # FGDM_USE_GRAPH=0: every step goes through p_sample_ddim / apply_model (the reference's own control flow)
+        self.use_graph = kwargs.get("use_graph", os.environ.get("FGDM_USE_GRAPH", "1") != "0")
 
     def register_buffer(self, name, attr):
         setattr(self, name, attr)
@@ -267,9 +282,12 @@ class DDIMSampler(object):
         cfg = not (unconditional_conditioning is None or unconditional_guidance_scale == 1.)
         ctx_c, hint_c = self._split_cond(cond)
         ctx_u, hint_u = self._split_cond(unconditional_conditioning)
+        # The captured step feeds ONE hint to both CFG halves. ControlNet guess mode (initialize_cn.py:87: un_cond has
+        # c_concat=None, so ddim_hacked.py:191 evaluates the uncond half with control=None) and any other uncond hint
+        # that differs from the cond hint take the sequential generic path below, which calls apply_model per half.
+        same_hint = uncond_hint_matches(cond, unconditional_conditioning, hint_c, hint_u)
         fast = (self.use_graph and isinstance(model, LatentDiffusion) and eta == 0. and ctx_c is not None
-                and (hint_u is None or hint_u is hint_c or (hint_u.shape == hint_c.shape and torch.equal(hint_u, hint_c)))
-                and (not isinstance(model, ControlLDM) or hint_c is not None))
+                and same_hint and (not isinstance(model, ControlLDM) or hint_c is not None))
         if fast:
             if pcond is not None and isinstance(model, ControlLDM):
                 raise NotImplementedError("pcond belongs to the FG-DM UNet (adapter), not to the ControlNet factor")

@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .ddim import DDIMSampler, _StepGraph
+from .ddim import DDIMSampler, _StepGraph, uncond_hint_matches
 from .ldm import ControlLDM, LatentDiffusion
 
 
@@ -59,7 +59,10 @@ class DPMSolverSampler(object):
         cfg = not (unconditional_conditioning is None or unconditional_guidance_scale == 1.)
         scale = float(unconditional_guidance_scale) if cfg else 1.0
         ctx_c, hint_c = DDIMSampler._split_cond(conditioning)
-        ctx_u, _ = DDIMSampler._split_cond(unconditional_conditioning)
+        ctx_u, hint_u = DDIMSampler._split_cond(unconditional_conditioning)
+        if not uncond_hint_matches(conditioning, unconditional_conditioning, hint_c, hint_u):
+            raise NotImplementedError("DPM-Solver: an unconditional c_concat that differs from the conditional one "
+                                      "(ControlNet guess mode) is only provided by DDIMSampler")
         pcond = kwargs.get("pcond")
         if isinstance(model, ControlLDM) and (hint_c is None or pcond is not None):
             raise NotImplementedError("ControlLDM needs a c_concat hint and takes no pcond")

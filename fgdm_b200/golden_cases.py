@@ -13,6 +13,7 @@ from . import synth
 FGDM_WEIGHT_SEED = 11
 CONTROL_WEIGHT_SEED = 12
 CONTROL_SCALES_VARIANT = tuple(0.5 + 0.1 * i for i in range(13))
+GUESS_MODE_SCALES = tuple(1.0 * (0.825 ** float(12 - i)) for i in range(13))   # initialize_cn.py:92, strength 1
 
 # models/config.yaml:33-48 and controlnet/models/cldm_v15_canny.yaml:21-53
 UNET_PARAMS = dict(image_size=32, in_channels=4, out_channels=4, model_channels=320, attention_resolutions=[4, 2, 1],

@@ -12,12 +12,14 @@ the YAML `target:` strings to `fgdm_b200.ldm.LatentDiffusion`, `fgdm_b200.nets.U
 from __future__ import annotations
 
 import importlib
+import os
 
 import numpy as np
 import torch
 
 from . import _lib, ops
-from .nets import AutoencoderKL, ControlledUnetModel, ControlNet, UNetModel  # noqa: F401  (targets)
+from .nets import (AutoencoderKL, ControlledUnetModel, ControlNet, IncompatibleKeys,  # noqa: F401  (targets)
+                   UNetModel)
 
 # reference target string -> our class, so the reference's own YAMLs can be used verbatim
 TARGET_ALIASES = {
@@ -36,9 +38,10 @@ TARGET_ALIASES = {
 }
 
 
-def get_obj_from_str(string, reload=False):
-    """ldm/util.py:88-93."""
-    string = TARGET_ALIASES.get(string, string)
+def get_obj_from_str(string, reload=False, alias=True):
+    """ldm/util.py:88-93 (+ the alias table; alias=False resolves the string as written)."""
+    if alias:
+        string = TARGET_ALIASES.get(string, string)
     module, cls = string.rsplit(".", 1)
     return getattr(importlib.import_module(module, package=None), cls)
 
@@ -96,12 +99,35 @@ class LatentDiffusion:
         self.device = torch.device(device)
         self.model = DiffusionWrapper(unet_config, conditioning_key)
         self.first_stage_model = instantiate_from_config(first_stage_config) if first_stage_config else None
-        self.cond_stage_model = IdentityCondStage()
-        if isinstance(cond_stage_config, dict) and str(cond_stage_config.get("target", "")).endswith("FrozenCLIPEmbedder"):
-            # models/config.yaml:74-75 / ddpm.py:626-640: the text encoder, on the same kernels (fgdm_b200/clip.py)
-            params = dict(cond_stage_config.get("params", {}), device=str(self.device))
-            self.cond_stage_model = instantiate_from_config(dict(cond_stage_config, params=params))
+        self.use_ema = bool(use_ema)
+        self._ema_loaded = False
+        self.cond_stage_forward = cond_stage_forward
+        self.cond_stage_model = self._make_cond_stage(cond_stage_config)
         self.register_schedule(given_betas, timesteps, linear_start, linear_end)
+
+    def _make_cond_stage(self, config):
+        """ddpm.py:618-640 `instantiate_cond_stage`. Three cases:
+        * the FrozenCLIPEmbedder target (models/config.yaml:74-75) -> fgdm_b200.clip.FrozenCLIPEmbedder, the text
+          transformer on the B200 kernels (token ids, or strings when a CLIPTokenizer is available / injected);
+        * an already constructed object with `encode` (e.g. the reference's own FrozenCLIPEmbedder instance, built
+          by the maintainer where `ldm` + its tokenizer files are importable) is kept as is;
+        * any other `target:` is instantiated through the plugin loader exactly as the reference would (ldm/util.py)
+          — `torch.nn.Identity` / None / "__is_unconditional__" give the pass-through for pre-encoded contexts."""
+        if config is None or config in ("__is_unconditional__", "__is_first_stage__"):
+            return IdentityCondStage()
+        if not isinstance(config, (dict,)) and not hasattr(config, "get"):
+            if hasattr(config, "encode") or callable(config):
+                return config                                         # a ready-made encoder object
+            raise TypeError(f"cond_stage_config: expected a config mapping or an encoder object, got {type(config)}")
+        target = str(config.get("target", ""))
+        if target in ("torch.nn.Identity", ""):
+            return IdentityCondStage()
+        is_clip = TARGET_ALIASES.get(target, target) == "fgdm_b200.clip.FrozenCLIPEmbedder"
+        if is_clip and os.environ.get("FGDM_KEEP_REFERENCE_CLIP", "0") != "1":
+            params = dict(config.get("params", {}) or {}, device=str(self.device))
+            return instantiate_from_config(dict(target=target, params=params))
+        # the reference's own class, resolved as written (needs `ldm` / its dependencies importable)
+        return get_obj_from_str(target, alias=False)(**(config.get("params", None) or {}))
 
     # ddpm.py:175-203 with util.py:21-25 (float64 numpy -> float32 buffers)
     def register_schedule(self, given_betas=None, timesteps=1000, linear_start=1e-4, linear_end=2e-2):
@@ -131,39 +157,111 @@ class LatentDiffusion:
             out.update({pre + k: v for k, v in net.param_shapes().items()})
         return out
 
-    def load_state_dict(self, sd, strict=False):
-        """Accepts the reference's checkpoint keys (`model.diffusion_model.*`, `first_stage_model.*`,
-        `control_model.*`); encoder / cond-stage / loss keys are ignored."""
-        _lib.require_device()
-        for pre, net in self._parts().items():
-            net.load_state_dict(sd, strict=False, prefix=pre, device=self.device)
-        pre = "cond_stage_model."
-        if hasattr(self.cond_stage_model, "text_model") and any(k.startswith(pre) for k in sd):
-            self.cond_stage_model.load_state_dict({k[len(pre):]: v for k, v in sd.items() if k.startswith(pre)})
-        return self
+    # keys of a reference checkpoint that belong to modules this inference-only path does not hold (VAE encoder,
+    # training losses, schedule buffers of ddpm.py:175-227): the reference's own module tree has them, so they are
+    # neither "missing" nor "unexpected" there and are not reported here either.
+    _UNUSED_PREFIXES = ("first_stage_model.encoder.", "first_stage_model.quant_conv.", "first_stage_model.loss.",
+                        "model_ema.", "cond_stage_model.")
+    _SCHEDULE_BUFFERS = ("betas", "alphas_cumprod", "alphas_cumprod_prev", "sqrt_alphas_cumprod",
+                         "sqrt_one_minus_alphas_cumprod", "log_one_minus_alphas_cumprod", "sqrt_recip_alphas_cumprod",
+                         "sqrt_recipm1_alphas_cumprod", "posterior_variance", "posterior_log_variance_clipped",
+                         "posterior_mean_coef1", "posterior_mean_coef2", "lvlb_weights", "logvar", "scale_factor")
 
+    def _ema_state_dict(self, sd):
+        """LitEma (ldm/modules/ema.py:16-21) keeps a shadow of every DiffusionWrapper parameter under
+        `model_ema.<name without dots>`; map them back onto `model.diffusion_model.*` names."""
+        out = {}
+        for k in self.model.diffusion_model.param_shapes():
+            s_name = "model_ema." + ("diffusion_model." + k).replace(".", "")
+            if s_name not in sd:
+                return None
+            out["model.diffusion_model." + k] = sd[s_name]
+        return out
+
+    def load_state_dict(self, sd, strict=True):
+        """torch semantics: returns IncompatibleKeys(missing_keys, unexpected_keys) so that the reference's
+        `m, u = model.load_state_dict(sd, strict=False)` (scripts/txt2img_fgdm_inference.py:28,
+        controlnet/initialize_cn.py:28-35) runs unchanged. Accepts the reference's checkpoint keys
+        (`model.diffusion_model.*`, `first_stage_model.*`, `control_model.*`, `cond_stage_model.*`).
+        use_ema=True with `model_ema.*` shadows in the checkpoint: the EMA weights are what the reference samples
+        with (every sampling call site is inside `with model.ema_scope()`, ddpm.py:230-241), so they are the ones
+        packed for the UNet; without shadows in the checkpoint the raw weights are used and a warning is printed."""
+        _lib.require_device()
+        missing, consumed = [], set()
+        unet_sd = sd
+        if self.use_ema:
+            ema = self._ema_state_dict(sd)
+            if ema is not None:
+                unet_sd, self._ema_loaded = ema, True
+            else:
+                print("fgdm_b200: use_ema=True but the checkpoint holds no (complete) model_ema.* shadows; "
+                      "sampling with the raw weights")
+        for pre, net in self._parts().items():
+            src = unet_sd if pre == "model.diffusion_model." else sd
+            r = net.load_state_dict(src, strict=False, prefix=pre, device=self.device)
+            missing += r.missing_keys
+            consumed.update(pre + k for k in net.param_shapes())
+        cs = self.cond_stage_model
+        pre = "cond_stage_model."
+        if hasattr(cs, "text_model") and hasattr(cs, "param_shapes"):          # our CLIP text tower
+            want = [pre + k for k in cs.param_shapes()]
+            if any(k in sd for k in want):
+                miss = [k for k in want if k not in sd]
+                missing += miss
+                if not miss:
+                    cs.load_state_dict({k[len(pre):]: v for k, v in sd.items() if k.startswith(pre)})
+            consumed.update(want)
+        elif isinstance(cs, torch.nn.Module):                                   # the reference's own encoder, kept
+            sub = {k[len(pre):]: v for k, v in sd.items() if k.startswith(pre)}
+            if sub:
+                cs.load_state_dict(sub, strict=False)
+        unexpected = [k for k in sd if k not in consumed and not k.startswith(self._UNUSED_PREFIXES)
+                      and k not in self._SCHEDULE_BUFFERS]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"Error(s) in loading state_dict for {type(self).__name__}: "
+                               f"missing {missing[:8]}{' ...' if len(missing) > 8 else ''}, "
+                               f"unexpected {unexpected[:8]}{' ...' if len(unexpected) > 8 else ''}")
+        return IncompatibleKeys(missing, unexpected)
+
+    # nn.Module look-alikes the reference's drivers call (txt2img_fgdm_inference.py:36-37,185; cldm/model.py:26;
+    # initialize_cn.py:27,39). The packed weights live on the B200 only, so device moves are no-ops.
     def eval(self):
         return self
 
     def cuda(self, *a):
         return self
 
+    def cpu(self):
+        return self
+
     def to(self, *a, **k):
         return self
 
-    def ema_scope(self, *a, **k):
+    def low_vram_shift(self, is_diffusing):
+        """cldm.py:933-943 pages sub-models between host and device under config.save_memory; a 180 GB B200 keeps
+        all of them resident (4.4 GB of bf16 weights), so there is nothing to shift."""
+        return None
+
+    def ema_scope(self, context=None):
+        """ddpm.py:230-241. Inference-only: the EMA weights (when present) were packed at load_state_dict."""
         import contextlib
         return contextlib.nullcontext()
 
     # -- reference methods ------------------------------------------------------------------------
     def get_learned_conditioning(self, c):
-        """ddpm.py:663-674. Tensors (pre-encoded / synthetic contexts) pass through."""
+        """ddpm.py:663-674: `cond_stage_model.encode(c)` (or `cond_stage_forward`), result on the model device.
+        Pre-encoded float tensors ([B,77,768] contexts) pass through; strings / token ids go to the text encoder."""
         if torch.is_tensor(c) and c.is_floating_point():
             return c
-        if hasattr(self.cond_stage_model, "text_model"):
-            return self.cond_stage_model.encode(c)            # token ids -> [B,77,768] (FrozenCLIPEmbedder)
-        raise NotImplementedError("no text encoder configured (cond_stage_config: FrozenCLIPEmbedder); pass [B,77,768] "
-                                  "context tensors")
+        cs = self.cond_stage_model
+        if isinstance(cs, IdentityCondStage):
+            raise NotImplementedError("no text encoder configured (cond_stage_config: FrozenCLIPEmbedder or an encoder "
+                                      "object); pass [B,77,768] context tensors")
+        if self.cond_stage_forward is None:
+            out = cs.encode(c) if callable(getattr(cs, "encode", None)) else cs(c)
+        else:
+            out = getattr(cs, self.cond_stage_forward)(c)
+        return out.to(self.device) if torch.is_tensor(out) else out
 
     def apply_model(self, x_noisy, t, cond, return_ids=False, **kw):
         """ddpm.py:1035-1044,1130-1136: tensor/list cond -> {'c_crossattn': [c]} -> DiffusionWrapper."""

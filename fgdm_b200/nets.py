@@ -11,6 +11,8 @@ bf16 and every arithmetic op is a kernel of libfgdm_b200.so. Only inference (`no
 """
 from __future__ import annotations
 
+from collections import namedtuple
+
 import torch
 
 from . import _lib, ops
@@ -25,6 +27,15 @@ def _unsupported(**flags):
                                   f"unsupported constructor options: {bad}")
 
 
+class IncompatibleKeys(namedtuple("IncompatibleKeys", ["missing_keys", "unexpected_keys"])):
+    """What torch.nn.Module.load_state_dict returns (torch/nn/modules/module.py `_IncompatibleKeys`)."""
+
+    def __repr__(self):
+        if not self.missing_keys and not self.unexpected_keys:
+            return "<All keys matched successfully>"
+        return super().__repr__()
+
+
 class _Net(Layer):
     """Common module-ish surface (enough of nn.Module for the reference's call sites)."""
 
@@ -37,22 +48,36 @@ class _Net(Layer):
         return dict(self.specs(""))
 
     def load_state_dict(self, sd, strict=True, prefix="", device=None):
-        dev = torch.device(device or "cuda")
+        """torch.nn.Module.load_state_dict semantics (the reference's call sites unpack `m, u = ...`,
+        scripts/txt2img_fgdm_inference.py:28, controlnet/initialize_cn.py:28-35): returns
+        `IncompatibleKeys(missing_keys, unexpected_keys)`; strict=True raises RuntimeError when either list is
+        non-empty. A shape mismatch raises RuntimeError under both settings (as torch does). With strict=False and
+        missing keys nothing is packed: the net stays unloaded and the first forward raises, naming the keys —
+        there are no default-initialised weights to fall back to on this path."""
+        dev = torch.device(device or self.device or "cuda")
         _lib.require_device()
         want = self.param_shapes()
-        missing = [k for k in want if prefix + k not in sd]
-        if missing:
-            raise KeyError(f"load_state_dict: {len(missing)} missing keys, e.g. {missing[:3]}")
-        if strict:
-            extra = [k for k in sd if k.startswith(prefix) and k[len(prefix):] not in want]
-            if extra:
-                raise KeyError(f"load_state_dict: {len(extra)} unexpected keys, e.g. {extra[:3]}")
-        with torch.no_grad():
-            self.load(sd, prefix, dev)
-            self._finalize(dev)
-        self.device = dev
-        self._loaded = True
-        return self
+        missing = [prefix + k for k in want if prefix + k not in sd]
+        unexpected = [k for k in sd if k.startswith(prefix) and k[len(prefix):] not in want]
+        bad = [f"size mismatch for {prefix + k}: checkpoint {tuple(sd[prefix + k].shape)} vs model {tuple(shp)}"
+               for k, shp in want.items() if prefix + k in sd and tuple(sd[prefix + k].shape) != tuple(shp)]
+        errs = list(bad)
+        if strict and unexpected:
+            errs.append("Unexpected key(s) in state_dict: " + ", ".join(f'"{k}"' for k in unexpected[:8])
+                        + (" ..." if len(unexpected) > 8 else ""))
+        if strict and missing:
+            errs.append("Missing key(s) in state_dict: " + ", ".join(f'"{k}"' for k in missing[:8])
+                        + (" ..." if len(missing) > 8 else ""))
+        if errs:
+            raise RuntimeError(f"Error(s) in loading state_dict for {type(self).__name__}:\n\t" + "\n\t".join(errs))
+        self._missing = missing
+        if not missing:
+            with torch.no_grad():
+                self.load(sd, prefix, dev)
+                self._finalize(dev)
+            self.device = dev
+            self._loaded = True
+        return IncompatibleKeys(missing, unexpected)
 
     def _finalize(self, dev):
         pass
@@ -64,6 +89,10 @@ class _Net(Layer):
     def cuda(self, *a):
         return self
 
+    def cpu(self):
+        """The packed weights live on the B200 only; `.cpu()` (controlnet/cldm/model.py:26) is a no-op."""
+        return self
+
     def to(self, *a, **k):
         return self
 
@@ -72,7 +101,9 @@ class _Net(Layer):
 
     def __call__(self, *a, **k):
         if not self._loaded:
-            raise RuntimeError("weights not loaded: call load_state_dict(reference_state_dict) first")
+            miss = getattr(self, "_missing", None)
+            raise RuntimeError("weights not loaded: " + (f"{len(miss)} keys were missing from the state_dict, e.g. {miss[:3]}"
+                                                         if miss else "call load_state_dict(reference_state_dict) first"))
         with torch.no_grad():
             return self.forward(*a, **k)
 

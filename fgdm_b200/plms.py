@@ -12,7 +12,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .ddim import DDIMSampler, _StepGraph
+from .ddim import DDIMSampler, _StepGraph, uncond_hint_matches
 from .ldm import ControlLDM, LatentDiffusion
 
 # e' = w0 e_t + w1 old[-1] + w2 old[-2] + w3 old[-3]   (plms.py:221-229)
@@ -59,7 +59,10 @@ class PLMSSampler(DDIMSampler):
         cfg = not (unconditional_conditioning is None or unconditional_guidance_scale == 1.)
         scale = float(unconditional_guidance_scale) if cfg else 1.0
         ctx_c, hint_c = self._split_cond(cond)
-        ctx_u, _ = self._split_cond(unconditional_conditioning)
+        ctx_u, hint_u = self._split_cond(unconditional_conditioning)
+        if not uncond_hint_matches(cond, unconditional_conditioning, hint_c, hint_u):
+            raise NotImplementedError("PLMS: an unconditional c_concat that differs from the conditional one (ControlNet "
+                                      "guess mode) is only provided by DDIMSampler")
         if isinstance(model, ControlLDM) and (hint_c is None or pcond is not None):
             raise NotImplementedError("ControlLDM needs a c_concat hint and takes no pcond")
         key = ("plms", b, tuple(shape[1:]), ctx_c.shape[1], cfg,

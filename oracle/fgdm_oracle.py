@@ -284,8 +284,11 @@ def controlled_unet_forward(sd, x, t, context, control, cfg=None, prefix="", onl
 
 def control_ldm_apply(sd, x, t, hint, context, control_scales=None, only_mid_control=False, cfg=None,
                       unet_prefix="model.diffusion_model.", control_prefix="control_model."):
-    """ControlLDM.apply_model, controlnet/cldm/cldm.py:836-849."""
+    """ControlLDM.apply_model, controlnet/cldm/cldm.py:836-849. hint=None is the `c_concat is None` branch (:841-842,
+    ControlNet guess mode's unconditional half): the UNet runs with control=None."""
     scales = control_scales or [1.0] * 13
+    if hint is None:
+        return controlled_unet_forward(sd, x, t, context, None, cfg, unet_prefix, only_mid_control)
     control = controlnet_forward(sd, x, hint, t, context, cfg, control_prefix)
     control = [c * s for c, s in zip(control, scales)]
     return controlled_unet_forward(sd, x, t, context, control, cfg, unet_prefix, only_mid_control)

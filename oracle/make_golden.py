@@ -282,6 +282,23 @@ def golden_control():
             model.alphas_cumprod, sequential_cfg=True)
         check("ddim_hacked sample final latent", x0_orc, x0, tol=1e-3)
         save("ddim_control", x0=x0, pred_x0_last=inter["pred_x0"][-1])
+        # --- ControlNet guess mode (initialize_cn.py:87,92 with guess_mode=True): the unconditional half has
+        # c_concat=None (ddim_hacked.py:191 -> cldm.py:841-842, control=None) and the scales decay 0.825**(12-i)
+        gscales = list(gc.GUESS_MODE_SCALES)
+        model.control_scales = gscales
+        un_g = {"c_concat": None, "c_crossattn": [case["uc"]]}
+        xg, _ = sampler.sample(case["S"], case["B"], case["shape"], cond, verbose=False, eta=0.0,
+                               unconditional_guidance_scale=case["scale"], unconditional_conditioning=un_g,
+                               x_T=case["x_T"])
+        model.control_scales = [1.0] * 13
+        xg_orc, _ = orc.ddim_sample(
+            lambda x, t, c: orc.control_ldm_apply(sd, x, t, case["hint"] if c is case["c"] else None, c,
+                                                  control_scales=gscales), case["S"],
+            (case["B"],) + tuple(case["shape"]), case["c"], case["uc"], case["scale"], case["x_T"],
+            model.alphas_cumprod, sequential_cfg=True)
+        check("ddim_hacked guess-mode final latent", xg_orc, xg, tol=1e-3)
+        assert float((xg - x0).abs().max()) > 1e-3, "guess mode must differ from the guided-uncond run"
+        save("ddim_control_guess", x0=xg)
 
 
 def golden_misc():

@@ -1,0 +1,246 @@
+"""GPU parity at the BENCHMARK's shapes and adversarial kernel inputs (VERDICT r01 "Next round" item 2).
+
+* the UNet / ControlLDM CFG step at R = 16 rows of 64x64 latents (what bench.py runs: other tile widths, stream-K
+  ranges and CTA pairs than the 2-row tests select) against the fp32 oracle, micro-batched;
+* batch invariance: prompt i's image from one B = 8 chain against its own B = 1 chain;
+* attention with logits spanning +-60 and with a row maximum that grows on every KV tile (the lazy-rescale path);
+* GroupNorm on inputs with |mean| >> std (variance cancellation);
+* ControlNet guess mode against the reference's ddim_hacked golden.
+
+Tolerance: eps error is max|delta| / max|ref| <= 2e-2 ("rel-to-max"); the element-wise figure
+printed next to it is the 99.9th percentile of |delta| / (|ref| + 1e-3 max|ref|).
+"""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+from fgdm_b200 import _lib, ops, synth  # noqa: E402
+from fgdm_b200 import golden_cases as gc  # noqa: E402
+from fgdm_b200.ddim import DDIMSampler  # noqa: E402
+from fgdm_b200.ldm import instantiate_from_config  # noqa: E402
+
+DEV = "cuda"
+EPS_TOL = 2e-2
+
+
+def relmax(a, b):
+    a, b = torch.as_tensor(a).float().cpu(), torch.as_tensor(b).float().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-12))
+
+
+def rel_p999(a, b):
+    """99.9th percentile of the element-wise relative error |a-b| / (|b| + 1e-3 max|b|)."""
+    a, b = torch.as_tensor(a).float().cpu().flatten(), torch.as_tensor(b).float().cpu().flatten()
+    e = (a - b).abs() / (b.abs() + 1e-3 * b.abs().max())
+    return float(torch.quantile(e[:: max(1, e.numel() // 4_000_000)], 0.999))
+
+
+def psnr(a, b, peak):
+    mse = float(((torch.as_tensor(a).double().cpu() - torch.as_tensor(b).double().cpu()) ** 2).mean())
+    return 10.0 * np.log10(peak * peak / max(mse, 1e-20))
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _dev():
+    _lib.require_device()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+
+
+@pytest.fixture(scope="module")
+def fgdm():
+    model = instantiate_from_config(gc.fgdm_config())
+    sd = synth.make_state_dict(model.param_shapes(), gc.FGDM_WEIGHT_SEED)
+    model.load_state_dict(sd)
+    return model, {k: v.to(DEV) for k, v in sd.items()}
+
+
+@pytest.fixture(scope="module")
+def control():
+    model = instantiate_from_config(gc.control_config())
+    sd = synth.make_state_dict(model.param_shapes(), gc.CONTROL_WEIGHT_SEED)
+    model.load_state_dict(sd)
+    return model, {k: v.to(DEV) for k, v in sd.items()}
+
+
+def _cfg_rows(B, seed):
+    """The 2B CFG rows of a bench step: rows [0,B) uncond, [B,2B) cond share the B latents (ddim.py:222-226)."""
+    x = torch.stack([synth.randn((4, 64, 64), seed + i) for i in range(B)]).to(DEV)
+    ctx = torch.stack([synth.randn((77, 768), seed + 100 + i) for i in range(2 * B)]).to(DEV)
+    t = torch.full((2 * B,), 521, device=DEV, dtype=torch.int64)
+    return x, t, ctx
+
+
+def test_unet_eps_R16_vs_oracle(fgdm):
+    """FG-DM UNet on the bench's 16 CFG rows (B=8, 64x64) in ONE call against the oracle in 2-row micro-batches."""
+    import fgdm_oracle as orc
+    model, sd = fgdm
+    B = 8
+    x, t, ctx = _cfg_rows(B, 500)
+    unet = model.model.diffusion_model
+    eps = unet.forward(x, t, kv=unet.project_context(ctx), rows=2 * B)          # the sampler's call (ddim._StepGraph._eps)
+    x2 = torch.cat([x, x])
+    ref = torch.cat([orc.unet_forward(sd, x2[i:i + 2], t[i:i + 2], ctx[i:i + 2], prefix="model.diffusion_model.")
+                     for i in range(0, 2 * B, 2)])
+    print("unet R=16 64x64: relmax", relmax(eps, ref), "p99.9 element-wise", rel_p999(eps, ref))
+    assert eps.shape == ref.shape
+    assert relmax(eps, ref) < EPS_TOL
+    # and through the public apply_model with the reference's torch.cat([x]*2) inputs: same rows, same kernels
+    eps2 = model.apply_model(x2, t, ctx)
+    assert relmax(eps2, ref) < EPS_TOL
+
+
+def test_control_step_R16_vs_oracle(control):
+    """ControlLDM.control_step (ControlNet + controlled UNet) on 16 CFG rows against the oracle, micro-batched."""
+    import fgdm_oracle as orc
+    model, sd = control
+    B = 8
+    x, t, ctx = _cfg_rows(B, 700)
+    hint = gc._hint(B, 512, 77).to(DEV)
+    unet, cn = model.model.diffusion_model, model.control_model
+    eps = model.control_step(x, t, unet.project_context(ctx), cn.project_context(ctx), cn.encode_hint(hint), 2 * B)
+    x2, h2 = torch.cat([x, x]), torch.cat([hint, hint])
+    ref = torch.cat([orc.control_ldm_apply(sd, x2[i:i + 2], t[i:i + 2], h2[i:i + 2], ctx[i:i + 2])
+                     for i in range(0, 2 * B, 2)])
+    print("control R=16 64x64: relmax", relmax(eps, ref), "p99.9 element-wise", rel_p999(eps, ref))
+    assert relmax(eps, ref) < EPS_TOL
+
+
+def test_batch_invariance_B8_vs_B1(fgdm, control):
+    """Prompts 0..7 in one B=8 chain (the bench's step) against eight B=1 chains with the same per-prompt x_T:
+    PSNR >= 35 dB per image (tile widths / split-K change with M, so bit equality is reported, not required)."""
+    from fgdm_b200.pipeline import FGDMPipeline
+    (seg, _), (img, _) = fgdm, control
+    pipe = FGDMPipeline(seg, img, seg_steps=50, img_steps=50)
+    idx = list(range(8))
+    inp = {k: v.to(DEV) for k, v in synth.prompt_inputs(idx, (64, 64)).items()}
+    out8 = pipe(inp["c"], inp["uc"], inp["xT_seg"], inp["c2"], inp["uc2"], inp["xT_img"], return_all=True)
+    worst, equal = 1e9, 0
+    for i in idx:
+        one = {k: v[i:i + 1].contiguous() for k, v in inp.items()}
+        out1 = pipe(one["c"], one["uc"], one["xT_seg"], one["c2"], one["uc2"], one["xT_img"], return_all=True)
+        p = psnr(out8["img_u8"][i].float(), out1["img_u8"][0].float(), 255.0)
+        ps = psnr(out8["seg_u8"][i].float(), out1["seg_u8"][0].float(), 255.0)
+        equal += int(torch.equal(out8["img_u8"][i], out1["img_u8"][0]))
+        worst = min(worst, p, ps)
+    print(f"batch invariance B=8 vs 8 x B=1: worst PSNR {worst:.1f} dB, bit-equal images {equal}/8")
+    assert worst > 35.0
+
+
+# ---------------------------------------------------------------------------------------------
+# adversarial kernel inputs
+# ---------------------------------------------------------------------------------------------
+def _run_attn(q, k, v):
+    images, heads, nq, d = q.shape
+    nk = k.shape[2]
+    tp = (nk + 7) // 8 * 8
+    vt = torch.zeros(images, heads, d, tp, device=DEV, dtype=torch.bfloat16)
+    vt[..., :nk] = v.transpose(-1, -2)
+    out = torch.empty(images, nq, heads * d, device=DEV, dtype=torch.bfloat16)
+    ops.attention(q, k, vt, out, images, heads, nq, nk, d, tp)
+    s = torch.einsum("bhid,bhjd->bhij", q.float(), k.float()) * d ** -0.5
+    ref = torch.einsum("bhij,bhjd->bhid", s.softmax(-1), v.float()).permute(0, 2, 1, 3).reshape(images, nq, heads * d)
+    return out, ref, s
+
+
+@pytest.mark.parametrize("d,n", [(40, 4096), (80, 1024), (160, 256), (40, 1000)])
+def test_attention_wide_logits(d, n):
+    """q, k scaled x8: logits span roughly +-60 (natural units), softmax nearly one-hot; exercises P up to 2^8 and
+    large negative exponents."""
+    torch.manual_seed(5)
+    q = (torch.randn(1, 4, n, d, device=DEV) * 2.8).to(torch.bfloat16)
+    k = (torch.randn(1, 4, n, d, device=DEV) * 2.8).to(torch.bfloat16)
+    v = torch.randn(1, 4, n, d, device=DEV).to(torch.bfloat16)
+    out, ref, s = _run_attn(q, k, v)
+    print(f"attention wide logits d={d}: logit range [{float(s.min()):.0f}, {float(s.max()):.0f}], relmax", relmax(out, ref))
+    assert float(s.max()) > 40 and float(s.min()) < -40
+    assert torch.isfinite(out.float()).all()
+    assert relmax(out, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("d,n,step", [(40, 4096, 12.0), (40, 4096, 3.0), (80, 1024, 20.0), (160, 512, 9.0)])
+def test_attention_rising_row_max(d, n, step):
+    """Every KV tile raises every row's maximum by `step` log2-units-ish (key j carries a component along a fixed
+    direction that grows with j // 64): the reference max is refreshed (lazy rescale of O in TMEM) over and over, and
+    with step < 8 the un-refreshed P > 1 path is taken."""
+    torch.manual_seed(6)
+    u = F.normalize(torch.randn(d, device=DEV), dim=0)
+    q = torch.randn(1, 2, n, d, device=DEV) * 0.3 + u * (d ** 0.5)              # q . u == sqrt(d) -> logit += ramp
+    ramp = (torch.arange(n, device=DEV) // 64).float() * (step * 0.6931)        # natural-log units per 64 keys
+    k = torch.randn(1, 2, n, d, device=DEV) * 0.3 + u[None, None, None, :] * ramp[None, None, :, None]
+    v = torch.randn(1, 2, n, d, device=DEV)
+    q, k, v = q.to(torch.bfloat16), k.to(torch.bfloat16), v.to(torch.bfloat16)
+    out, ref, s = _run_attn(q, k, v)
+    print(f"attention rising max d={d} step={step}: logit max {float(s.max()):.0f}, relmax", relmax(out, ref))
+    assert torch.isfinite(out.float()).all()
+    assert relmax(out, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("nb,h,w,c,mean,std", [(2, 64, 64, 320, 50.0, 0.5), (2, 16, 16, 1280, -30.0, 0.25),
+                                               (1, 128, 128, 128, 100.0, 1.0), (2, 32, 32, 640, 8.0, 0.05)])
+def test_groupnorm_large_mean(nb, h, w, c, mean, std):
+    """|mean| >> std: E[x^2] - mean^2 cancels catastrophically in fp32; the kernel must use shifted / Welford-style
+    statistics (real checkpoints have such channels). Reference: F.group_norm on the same bf16-rounded input."""
+    torch.manual_seed(7)
+    x = (torch.randn(nb, h, w, c, device=DEV) * std + mean).to(torch.bfloat16)
+    g, b = torch.randn(c, device=DEV), torch.randn(c, device=DEV)
+    y = ops.groupnorm(x, g, b, eps=1e-5, silu=False)
+    ref = F.group_norm(x.float().permute(0, 3, 1, 2), 32, g, b, 1e-5).permute(0, 2, 3, 1)
+    print(f"groupnorm mean={mean} std={std}: relmax", relmax(y, ref))
+    assert relmax(y, ref) < 1e-2
+
+
+# ---------------------------------------------------------------------------------------------
+# ControlNet guess mode: uncond half runs with control=None
+# ---------------------------------------------------------------------------------------------
+def test_ddim_hacked_guess_mode_vs_reference_golden(control):
+    model, _ = control
+    c = gc.control_ddim_case()
+    g = np.load(os.path.join(GOLD, "ddim_control_guess.npz"))
+    g_plain = np.load(os.path.join(GOLD, "ddim_control.npz"))
+    hint = c["hint"].to(DEV)
+    cond = {"c_concat": [hint], "c_crossattn": [c["c"].to(DEV)]}
+    un = {"c_concat": None, "c_crossattn": [c["uc"].to(DEV)]}               # initialize_cn.py:87 with guess_mode=True
+    model.control_scales = list(gc.GUESS_MODE_SCALES)
+    try:
+        x0, _ = DDIMSampler(model).sample(c["S"], c["B"], list(c["shape"]), cond, verbose=False, eta=0.0,
+                                          unconditional_guidance_scale=c["scale"], unconditional_conditioning=un,
+                                          x_T=c["x_T"].to(DEV))
+    finally:
+        model.control_scales = [1.0] * 13
+    p = psnr(x0, g["x0"], float(np.abs(g["x0"]).max()))
+    print("ddim guess mode: relmax", relmax(x0, g["x0"]), "psnr", p)
+    assert p > 35.0
+    assert psnr(x0, g_plain["x0"], float(np.abs(g_plain["x0"]).max())) < 30.0      # and is NOT the guided-uncond result
+    from fgdm_b200.plms import PLMSSampler
+    with pytest.raises(NotImplementedError):
+        PLMSSampler(model).sample(c["S"], c["B"], list(c["shape"]), cond, verbose=False, eta=0.0,
+                                  unconditional_guidance_scale=c["scale"], unconditional_conditioning=un,
+                                  x_T=c["x_T"].to(DEV))
+
+
+# ---------------------------------------------------------------------------------------------
+# an N-GPU sharded run equals the 1-GPU run of the same prompt indices
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
+def test_sharded_run_equals_single_gpu_run():
+    import json
+    import subprocess
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", str(29600 + os.getpid() % 300), os.path.join(ROOT, "tests", "sharding_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-2000:]
+    res = json.loads(lines[-1])
+    print(res)
+    assert res["sharding_determinism"] and all(s["bit_equal_to_single_gpu"] for s in res["shards"])
