@@ -16,6 +16,7 @@
 // attention.py:199-200) is dead at inference (only [0] is used, attention.py:235-238) and is not
 // produced.
 #include "common.cuh"
+#include <cstdlib>
 #include <type_traits>
 
 namespace fgdm {
@@ -430,6 +431,375 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
   return check_launch("attention_kernel");
 }
 
+// =====================================================================================================================
+// attention4_kernel: the self-attention kernel for small head dims (d <= 56: the UNet's 64x64 level, d = 40, N = 4096,
+// which is 3/4 of all attention time). The exponential, not the tensor core, bounds this shape: 16 ex2/clk/SM is 1024
+// clk per 128x128 score tile against 448 clk of MMA, so the kernel is organised around keeping the MUFU pipe fed:
+//   * FOUR 128-row query tiles per CTA and 64-key tiles: ONE thread per query row holds its 64 scores in registers, so
+//     there is no partner-warp exchange of half-row maxima (the old kernel's 64-thread named barrier per tile) and every
+//     SM sub-partition runs 4 softmax warps that belong to 4 DIFFERENT query tiles: they are coupled only through the
+//     K/V ring (KST stages), so one warp's TMEM wait / max phase is covered by the other three warps' exp phases;
+//   * S_t = Q_t K^T is a 128x64 MMA over ceil(d/16) K-steps only (d = 40: 3 instead of the 4 a 64-wide chunk holds);
+//   * everything else as in attention_kernel: TMA rings, S and O in TMEM, lazy 2^8 rescale, bf16 P through swizzled
+//     smem, the softmax denominator from an all-ones V^T row.
+// TMEM: 4 tiles x 128 columns (S at +0: 64 columns, O at +64: DV <= 64 columns) = 512.
+// =====================================================================================================================
+template <int DV, int KST, int PB>
+struct Attn4Cfg {
+  static constexpr int QT = 4, BN = 64;
+  static constexpr int kQBytes = 128 * 128;            // one swizzle atom [128 rows x 128 B] per query tile
+  static constexpr int kKBytes = BN * 128;
+  static constexpr int kVBytes = DV * 128;             // one key-atom (64 keys) of [DV rows x 128 B]
+  static constexpr int kPBytes = 128 * 128;            // [128 rows x 64 keys] bf16
+  static constexpr int kSmemBytes = 1024 + QT * kQBytes + KST * (kKBytes + kVBytes) + QT * PB * kPBytes + 512;
+  static constexpr int kSoftmaxWarps = 4 * QT;
+  static constexpr int kIssue0 = kSoftmaxWarps;
+  static constexpr int kTma = kSoftmaxWarps + QT;
+  // 6 warpgroups: 4 softmax, 1 MMA issue, 1 with the TMA producer warp (+3 idle warps: setmaxnreg is per warpgroup).
+  // Registers are allocated for 24 warps either way (4-warp granularity): launched at 80 per thread, the issue / TMA
+  // warpgroups drop to 32 and hand theirs to the softmax warpgroups (104), which then hold a 64-score row without spills.
+  static constexpr int kThreads = 32 * 24;
+  static constexpr int kRegsSoftmax = 104, kRegsOther = 32;
+  static constexpr int kTmemStride = 128;
+  static_assert(BN + DV <= kTmemStride, "TMEM budget");
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+};
+
+template <int DV, int KST, int PB>
+__global__ void __launch_bounds__(Attn4Cfg<DV, KST, PB>::kThreads, 1)
+attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
+  using Cfg = Attn4Cfg<DV, KST, PB>;
+  constexpr int QT = Cfg::QT, BN = Cfg::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;                                  // [QT]
+  uint8_t* sK = sQ + QT * Cfg::kQBytes;                // [KST]
+  uint8_t* sV = sK + KST * Cfg::kKBytes;               // [KST]
+  uint8_t* sP = sV + KST * Cfg::kVBytes;               // [QT][PB]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + QT * PB * Cfg::kPBytes);
+  uint64_t* bar_q = bars;
+  uint64_t* bar_k = bars + 1;                          // [KST] K(j) landed
+  uint64_t* bar_v = bar_k + KST;                       // [KST] V(j) landed
+  uint64_t* k_empty = bar_v + KST;                     // [KST] all QT tiles' S(j) have read the stage
+  uint64_t* v_empty = k_empty + KST;                   // [KST] all QT tiles' PV(j) have read the stage
+  uint64_t* bar_s = v_empty + KST;                     // [QT] S_t(j) complete
+  uint64_t* bar_o = bar_s + QT;                        // [QT] PV_t(j) complete
+  uint64_t* bar_sfree = bar_o + QT;                    // [QT] S_t(j) is in registers (4 warp arrivals)
+  uint64_t* bar_pready = bar_sfree + QT;               // [QT] P_t(j) is in smem       (4 warp arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_pready + QT);
+  static_assert((1 + 4 * KST + 4 * QT) * 8 + 4 <= 512, "barrier block");
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int q0 = blockIdx.x * (128 * QT);
+  const int bh = blockIdx.y;
+  const int num_kv = (p.Nk + BN - 1) / BN;
+  const int ksteps = (p.d + 15) >> 4;                  // K-steps of the S MMA that hold real head-dim columns
+
+  if (tid == 0) {
+    tma_prefetch_desc(&map_q);
+    tma_prefetch_desc(&map_k);
+    tma_prefetch_desc(&map_vt);
+    mbar_init(bar_q, 1);
+    for (int i = 0; i < KST; ++i) {
+      mbar_init(&bar_k[i], 1);
+      mbar_init(&bar_v[i], 1);
+      mbar_init(&k_empty[i], QT);
+      mbar_init(&v_empty[i], QT);
+    }
+    for (int t = 0; t < QT; ++t) {
+      mbar_init(&bar_s[t], 1);
+      mbar_init(&bar_o[t], 1);
+      mbar_init(&bar_sfree[t], 4);
+      mbar_init(&bar_pready[t], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == Cfg::kTma) {
+    tmem_alloc(tmem_ptr, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  if (warp >= Cfg::kIssue0) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(Cfg::kRegsOther));
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(Cfg::kRegsSoftmax));
+  }
+
+  if (warp > Cfg::kTma) {
+    // idle warps of the producer warpgroup
+  } else if (warp == Cfg::kTma) {
+    // ===================== TMA producer: 4 Q tiles once, then KST-stage K and V rings =====================
+    if (lane == 0) {
+      mbar_expect_tx(bar_q, QT * Cfg::kQBytes);
+#pragma unroll
+      for (int t = 0; t < QT; ++t) tma_load_3d(sQ + t * Cfg::kQBytes, &map_q, bar_q, 0, q0 + t * 128, bh);
+      int st = 0, ph = 0;                               // ring position of load j, parity of its (j / KST)-th use
+      for (int j = 0; j < num_kv; ++j) {
+        if (j >= KST) mbar_wait(&k_empty[st], ph ^ 1);
+        mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
+        tma_load_3d(sK + st * Cfg::kKBytes, &map_k, &bar_k[st], 0, j * BN, bh);
+        if (j >= KST) mbar_wait(&v_empty[st], ph ^ 1);
+        mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
+        tma_load_3d(sV + st * Cfg::kVBytes, &map_vt, &bar_v[st], j * BN, 0, bh);
+        if (++st == KST) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp >= Cfg::kIssue0) {
+    // ===================== MMA issue warp of query tile t =====================
+    const int t = warp - Cfg::kIssue0;
+    const uint32_t tm = tmem_base + t * Cfg::kTmemStride;
+    auto issue_s = [&](int st) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN);
+      const uint64_t dq = make_desc_sw128(smem_u32(sQ + t * Cfg::kQBytes));
+      const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes));
+      for (int k = 0; k < ksteps; ++k) tc_mma_bf16(tm, dq + 2 * k, dk + 2 * k, idesc, k != 0 ? 1u : 0u);
+      tc_commit(&bar_s[t]);
+      tc_commit(&k_empty[st]);
+    };
+    auto issue_pv = [&](int j, int st) {
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
+      const uint64_t dp = make_desc_sw128(smem_u32(sP + (t * PB + (PB == 2 ? (j & 1) : 0)) * Cfg::kPBytes));
+      const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes));
+#pragma unroll
+      for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16(tm + BN, dp + 2 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+      tc_commit(&bar_o[t]);
+      tc_commit(&v_empty[st]);
+    };
+    if (lane == 0) {
+      mbar_wait(bar_q, 0);
+      mbar_wait(&bar_k[0], 0);
+      tc_fence_after();
+      issue_s(0);
+    }
+    int st = 0, ph = 0;                                 // ring position / parity of tile j
+    for (int j = 0; j < num_kv; ++j) {
+      int st1 = st + 1, ph1 = ph;
+      if (st1 == KST) { st1 = 0; ph1 ^= 1; }
+      if (lane == 0 && j + 1 < num_kv) {
+        mbar_wait(&bar_k[st1], ph1);
+        mbar_wait(&bar_sfree[t], j & 1);               // S_t(j) is in registers: its TMEM columns are free
+        tc_fence_after();
+        issue_s(st1);                                   // overlaps the softmax of tile j
+      }
+      __syncwarp();
+      mbar_wait(&bar_v[st], ph);
+      // ones-row: V^T row dv_real := 1.0 (a full 128-byte swizzle row). All four issue warps write the same bytes.
+      if (lane < 8) {
+        st_shared_16(smem_u32(sV + st * Cfg::kVBytes) + p.dv_real * 128 + lane * 16,
+                     make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u));
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_wait(&bar_pready[t], j & 1);
+        tc_fence_after();
+        issue_pv(j, st);
+      }
+      __syncwarp();
+      st = st1;
+      ph = ph1;
+    }
+  } else {
+    // ===================== softmax warps: one thread per query row =====================
+    const int t = warp >> 2;                           // query tile
+    const int row = (warp & 3) * 32 + lane;            // query row within the tile == TMEM lane
+    const uint32_t s_addr = tmem_base + t * Cfg::kTmemStride + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+    const uint32_t o_addr = s_addr + BN;
+    uint64_t* my_bar_o = &bar_o[t];
+    float m_ref = -INFINITY;                           // reference max (scaled, log2 domain) used for exp2
+    const uint32_t sP_row0 = smem_u32(sP + t * PB * Cfg::kPBytes) + row * 128;
+    const int sw = row & 7;
+
+    for (int j = 0; j < num_kv; ++j) {
+      const int valid = p.Nk - j * BN;                  // keys valid in this tile (may exceed BN)
+      const bool full = valid >= BN;                    // CTA-uniform
+      mbar_wait(&bar_s[t], j & 1);
+      tc_fence_after();
+      uint32_t s[BN];
+      tmem_ld_32x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
+      tmem_ld_32x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_sfree[t]);
+      float rmax;
+      {
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (full) {
+#pragma unroll
+          for (int i = 0; i < BN; i += 8) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              mx[u] = fmax3(mx[u], __uint_as_float(s[i + 2 * u]), __uint_as_float(s[i + 2 * u + 1]));
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < BN; i += 8) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int c = i + 2 * u;
+              mx[u] = fmax3(mx[u], (c < valid) ? __uint_as_float(s[c]) : -INFINITY,
+                            (c + 1 < valid) ? __uint_as_float(s[c + 1]) : -INFINITY);
+            }
+          }
+        }
+        rmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      }
+      const float tmax = rmax * p.scale_log2;
+
+      // ---- single P buffer: PV(j-1) must have drained before the P tile is overwritten ----
+      if (PB == 1 && j > 0) {
+        mbar_wait(my_bar_o, (j - 1) & 1);
+        tc_fence_after();
+      }
+      // ---- lazy rescale: refresh the reference max only when it grew by more than 2^8 ----
+      const bool need = tmax > m_ref + kRescaleThreshold;
+      if (__any_sync(0xffffffffu, need)) {
+        const float m_new = need ? tmax : m_ref;
+        const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
+        m_ref = m_new;
+        if (j > 0) {
+          if (PB == 2) {                                  // O may only be touched once PV(j-1) has drained
+            mbar_wait(my_bar_o, (j - 1) & 1);
+            tc_fence_after();
+          }
+#pragma unroll
+          for (int c = 0; c < DV; c += 8) {
+            uint32_t r[8];
+            tmem_ld_32x8(o_addr + c, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st_32x8(o_addr + c, r);
+          }
+          tmem_st_wait();
+        }
+      }
+
+      // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major): 8 chunks of 8 keys per row ----
+      const float neg_m = -m_ref;
+      const uint32_t sP_row = sP_row0 + (PB == 2 ? (j & 1) * Cfg::kPBytes : 0);
+      auto emit = [&](auto masked) {
+#pragma unroll
+        for (int c = 0; c < BN; c += 8) {
+          uint32_t pk[4];
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
+            float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
+            if constexpr (decltype(masked)::value) {
+              if (c + i >= valid) p0 = 0.0f;
+              if (c + i + 1 >= valid) p1 = 0.0f;
+            }
+            pk[i >> 1] = pack_bf16x2(p0, p1);
+          }
+          st_shared_16(sP_row + (((c >> 3) ^ sw) << 4), make_uint4(pk[0], pk[1], pk[2], pk[3]));
+        }
+      };
+      if (full) emit(std::false_type{}); else emit(std::true_type{});
+
+      fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+      // Observe PV(j-1) BEFORE enabling PV(j): every bar_o phase is seen in order (no parity aliasing).
+      if (PB == 2 && j > 0) mbar_wait(my_bar_o, (j - 1) & 1);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar_pready[t]);
+    }
+
+    // ---- normalise and store: out[img, q, head*d + e]; the denominator is O column dv_real ----
+    mbar_wait(my_bar_o, (num_kv - 1) & 1);
+    tc_fence_after();
+    const int q = q0 + t * 128 + row;
+    float inv;
+    {
+      uint32_t r1;
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1) : "r"(o_addr + p.dv_real) : "memory");
+      tmem_ld_wait();
+      inv = 1.0f / __uint_as_float(r1);
+    }
+    const int img = bh / p.heads;
+    const int head = bh - img * p.heads;
+    __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d;
+#pragma unroll
+    for (int c = 0; c < DV; c += 8) {
+      uint32_t r[8];
+      tmem_ld_32x8(o_addr + c, r);
+      tmem_ld_wait();
+      if (q < p.Nq && c < p.d) {
+        *reinterpret_cast<uint4*>(dst + c) =
+            make_uint4(pack_bf16x2(__uint_as_float(r[0]) * inv, __uint_as_float(r[1]) * inv),
+                       pack_bf16x2(__uint_as_float(r[2]) * inv, __uint_as_float(r[3]) * inv),
+                       pack_bf16x2(__uint_as_float(r[4]) * inv, __uint_as_float(r[5]) * inv),
+                       pack_bf16x2(__uint_as_float(r[6]) * inv, __uint_as_float(r[7]) * inv));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == Cfg::kTma) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <int DV, int KST, int PB>
+static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams p, int tok_pad, cudaStream_t stream) {
+  using Cfg = Attn4Cfg<DV, KST, PB>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::kSmemBytes);
+    if (e != cudaSuccess) {
+      set_error("attention4: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
+      return -1;
+    }
+    configured = true;
+  }
+  CUtensorMap mq, mk, mv;
+  {
+    uint64_t dims[3] = {static_cast<uint64_t>(p.d), static_cast<uint64_t>(p.Nq), static_cast<uint64_t>(p.BH)};
+    uint64_t strides[2] = {static_cast<uint64_t>(p.d) * 2, static_cast<uint64_t>(p.Nq) * p.d * 2};
+    uint32_t box[3] = {64, 128, 1};
+    if (encode_tmap(&mq, q, 3, dims, strides, box)) return -1;
+  }
+  {
+    uint64_t dims[3] = {static_cast<uint64_t>(p.d), static_cast<uint64_t>(p.Nk), static_cast<uint64_t>(p.BH)};
+    uint64_t strides[2] = {static_cast<uint64_t>(p.d) * 2, static_cast<uint64_t>(p.Nk) * p.d * 2};
+    uint32_t box[3] = {64, 64, 1};
+    if (encode_tmap(&mk, k, 3, dims, strides, box)) return -1;
+  }
+  {
+    uint64_t dims[3] = {static_cast<uint64_t>(p.Nk), static_cast<uint64_t>(p.d), static_cast<uint64_t>(p.BH)};
+    uint64_t strides[2] = {static_cast<uint64_t>(tok_pad) * 2, static_cast<uint64_t>(p.d) * tok_pad * 2};
+    uint32_t box[3] = {64, static_cast<uint32_t>(DV), 1};
+    if (encode_tmap(&mv, vt, 3, dims, strides, box)) return -1;
+  }
+  dim3 grid((p.Nq + 511) / 512, p.BH, 1);
+  cudaError_t e = launch_pdl(attention4_kernel<DV, KST, PB>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p);
+  if (e != cudaSuccess) { set_error("attention4_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
+  return check_launch("attention4_kernel");
+}
+
+// FGDM_ATTN4: 0 = never use attention4_kernel, 1 (default) = KST 3 / one P buffer, 2 = KST 2 / two P buffers
+static int attn4_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("FGDM_ATTN4");
+    mode = e ? atoi(e) : 1;
+  }
+  return mode;
+}
+
 template <int KA, int DV, int BN>
 static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p,
                        int nsplit, cudaStream_t stream) {
@@ -464,6 +834,19 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   p.dv_per = dv_per;
   p.dv_real = dv_per;
   const int DV = (dv_per + 1 + 15) / 16 * 16;   // + the ones-row, MMA N granularity 16
+
+  // small head dims, long self-attention: four query tiles per CTA, one thread per row (attention4_kernel)
+  if (KA == 1 && nsplit == 1 && DV <= 64 && !causal && Nq >= 512 && Nk >= 512 && attn4_mode() != 0) {
+    const int mode = attn4_mode();
+#define FGDM_ATTN4_CASE(DV_) \
+    if (DV == DV_) return mode == 2 ? launch_attn4<DV_, 2, 2>(q, k, vt, p, tok_pad, stream) \
+                                    : launch_attn4<DV_, 3, 1>(q, k, vt, p, tok_pad, stream);
+    FGDM_ATTN4_CASE(16)
+    FGDM_ATTN4_CASE(32)
+    FGDM_ATTN4_CASE(48)
+    FGDM_ATTN4_CASE(64)
+#undef FGDM_ATTN4_CASE
+  }
 
   CUtensorMap mq, mk, mv;
   {
