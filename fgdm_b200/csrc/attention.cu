@@ -22,7 +22,7 @@
 namespace fgdm {
 
 int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dims,
-                const uint64_t* strides_bytes, const uint32_t* box);
+                const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes = 128);
 
 struct AttnParams {
   int BH;           // images * heads
@@ -451,6 +451,13 @@ struct Attn4Cfg {
   static constexpr int kKBytes = BN * 128;
   static constexpr int kVBytes = DV * 128;             // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kPBytes = 128 * 128;            // [128 rows x 64 keys] bf16
+  // PB == 0: P never touches shared memory. The softmax threads store bf16 P into the first 32 TMEM columns of their
+  // S tile (tcgen05.st) and PV is a TS MMA (A = P from TMEM, B = V^T from smem). Shared-memory bandwidth (128 B/clk/SM)
+  // is what held the smem-P variants at 65 % of the ex2 bound: per 4x(128x64) step the SS MMAs read 72 KB (Q, K) +
+  // 88 KB (P, V) and the softmax warps write 64 KB of P = 1750 clk of smem time next to 2048 clk of MUFU time; with P
+  // in TMEM it is 96 KB = 750 clk. The price: S_t(j+1) overwrites P_t(j), so it is issued after PV_t(j) (same thread,
+  // in order) instead of during softmax(j) - covered by the other three query tiles of the sub-partition.
+  static constexpr bool kTS = PB == 0;
   static constexpr int kSmemBytes = 1024 + QT * kQBytes + KST * (kKBytes + kVBytes) + QT * PB * kPBytes + 512;
   static constexpr int kSoftmaxWarps = 4 * QT;
   static constexpr int kIssue0 = kSoftmaxWarps;
@@ -567,10 +574,15 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     };
     auto issue_pv = [&](int j, int st) {
       constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
-      const uint64_t dp = make_desc_sw128(smem_u32(sP + (t * PB + (PB == 2 ? (j & 1) : 0)) * Cfg::kPBytes));
       const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes));
+      if constexpr (Cfg::kTS) {
 #pragma unroll
-      for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16(tm + BN, dp + 2 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+        for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16_ts(tm + BN, tm + 8 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+      } else {
+        const uint64_t dp = make_desc_sw128(smem_u32(sP + (t * PB + (PB == 2 ? (j & 1) : 0)) * Cfg::kPBytes));
+#pragma unroll
+        for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16(tm + BN, dp + 2 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+      }
       tc_commit(&bar_o[t]);
       tc_commit(&v_empty[st]);
     };
@@ -584,7 +596,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     for (int j = 0; j < num_kv; ++j) {
       int st1 = st + 1, ph1 = ph;
       if (st1 == KST) { st1 = 0; ph1 ^= 1; }
-      if (lane == 0 && j + 1 < num_kv) {
+      if (!Cfg::kTS && lane == 0 && j + 1 < num_kv) {
         mbar_wait(&bar_k[st1], ph1);
         mbar_wait(&bar_sfree[t], j & 1);               // S_t(j) is in registers: its TMEM columns are free
         tc_fence_after();
@@ -600,9 +612,11 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
+        if (Cfg::kTS && j + 1 < num_kv) mbar_wait(&bar_k[st1], ph1);   // so that S(j+1) follows PV(j) without a gap
         mbar_wait(&bar_pready[t], j & 1);
         tc_fence_after();
         issue_pv(j, st);
+        if (Cfg::kTS && j + 1 < num_kv) issue_s(st1);   // overwrites P_t(j): in order behind PV_t(j) (same issuing thread)
       }
       __syncwarp();
       st = st1;
@@ -628,9 +642,11 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
       tmem_ld_32x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
       tmem_ld_32x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
       tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar_sfree[t]);
+      if constexpr (!Cfg::kTS) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_sfree[t]);
+      }
       float rmax;
       {
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -657,6 +673,8 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
       const float tmax = rmax * p.scale_log2;
 
       // ---- single P buffer: PV(j-1) must have drained before the P tile is overwritten ----
+      // (TS mode: S_t(j) was issued behind PV_t(j-1) by the same thread and tcgen05.commit covers every earlier MMA of
+      // that thread, so bar_s(j) already implies that PV_t(j-1) has read P_t(j-1) and written O)
       if (PB == 1 && j > 0) {
         mbar_wait(my_bar_o, (j - 1) & 1);
         tc_fence_after();
@@ -685,37 +703,61 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         }
       }
 
-      // ---- probabilities -> bf16 P tile in smem (128B swizzle, K-major): 8 chunks of 8 keys per row ----
+      // ---- probabilities -> bf16 P: TMEM columns [0,32) of this tile (TS) or the swizzled smem tile ----
       const float neg_m = -m_ref;
-      const uint32_t sP_row = sP_row0 + (PB == 2 ? (j & 1) * Cfg::kPBytes : 0);
-      auto emit = [&](auto masked) {
+      if constexpr (Cfg::kTS) {
 #pragma unroll
-        for (int c = 0; c < BN; c += 8) {
-          uint32_t pk[4];
+        for (int h = 0; h < 2; ++h) {                     // two 16-column stores: the S registers die as P is produced
+          uint32_t pk[16];
+          if (full) {
 #pragma unroll
-          for (int i = 0; i < 8; i += 2) {
-            float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
-            float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
-            if constexpr (decltype(masked)::value) {
-              if (c + i >= valid) p0 = 0.0f;
-              if (c + i + 1 >= valid) p1 = 0.0f;
+            for (int c = 0; c < 32; c += 2)
+              pk[c >> 1] = pack_bf16x2(fast_exp2(fmaf(__uint_as_float(s[32 * h + c]), p.scale_log2, neg_m)),
+                                       fast_exp2(fmaf(__uint_as_float(s[32 * h + c + 1]), p.scale_log2, neg_m)));
+          } else {
+#pragma unroll
+            for (int c = 0; c < 32; c += 2) {
+              const int cc = 32 * h + c;
+              const float p0 = cc < valid ? fast_exp2(fmaf(__uint_as_float(s[cc]), p.scale_log2, neg_m)) : 0.0f;
+              const float p1 = cc + 1 < valid ? fast_exp2(fmaf(__uint_as_float(s[cc + 1]), p.scale_log2, neg_m)) : 0.0f;
+              pk[c >> 1] = pack_bf16x2(p0, p1);
             }
-            pk[i >> 1] = pack_bf16x2(p0, p1);
           }
-          st_shared_16(sP_row + (((c >> 3) ^ sw) << 4), make_uint4(pk[0], pk[1], pk[2], pk[3]));
+          tmem_st_32x16(s_addr + 16 * h, pk);
         }
-      };
-      if (full) emit(std::false_type{}); else emit(std::true_type{});
-
-      fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
-      // Observe PV(j-1) BEFORE enabling PV(j): every bar_o phase is seen in order (no parity aliasing).
-      if (PB == 2 && j > 0) mbar_wait(my_bar_o, (j - 1) & 1);
+        tmem_st_wait();
+      } else {
+        const uint32_t sP_row = sP_row0 + (PB == 2 ? (j & 1) * Cfg::kPBytes : 0);
+        auto emit = [&](auto masked) {
+#pragma unroll
+          for (int c = 0; c < BN; c += 8) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+              float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
+              float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
+              if constexpr (decltype(masked)::value) {
+                if (c + i >= valid) p0 = 0.0f;
+                if (c + i + 1 >= valid) p1 = 0.0f;
+              }
+              pk[i >> 1] = pack_bf16x2(p0, p1);
+            }
+            st_shared_16(sP_row + (((c >> 3) ^ sw) << 4), make_uint4(pk[0], pk[1], pk[2], pk[3]));
+          }
+        };
+        if (full) emit(std::false_type{}); else emit(std::true_type{});
+        fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
+        // Observe PV(j-1) BEFORE enabling PV(j): every bar_o phase is seen in order (no parity aliasing).
+        if (PB == 2 && j > 0) mbar_wait(my_bar_o, (j - 1) & 1);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar_pready[t]);
     }
 
     // ---- normalise and store: out[img, q, head*d + e]; the denominator is O column dv_real ----
+    // (TS mode never looked at bar_o inside the loop, but bar_s(j) implied PV(j-1): every earlier phase of bar_o has
+    // completed before the last softmax tile began, so the parity wait below can only match the final phase)
     mbar_wait(my_bar_o, (num_kv - 1) & 1);
     tc_fence_after();
     const int q = q0 + t * 128 + row;
@@ -790,7 +832,8 @@ static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams
   return check_launch("attention4_kernel");
 }
 
-// FGDM_ATTN4: 0 = never use attention4_kernel, 1 (default) = KST 3 / one P buffer, 2 = KST 2 / two P buffers
+// FGDM_ATTN4: 0 = never use attention4_kernel, 1 (default) = P in TMEM (TS MMA), 4-stage K/V ring; 2 / 3 = P through
+// shared memory (2 stages + 2 P buffers / 3 stages + 1 P buffer)
 static int attn4_mode() {
   static int mode = -1;
   if (mode < 0) {
@@ -840,7 +883,8 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
     const int mode = attn4_mode();
 #define FGDM_ATTN4_CASE(DV_) \
     if (DV == DV_) return mode == 2 ? launch_attn4<DV_, 2, 2>(q, k, vt, p, tok_pad, stream) \
-                                    : launch_attn4<DV_, 3, 1>(q, k, vt, p, tok_pad, stream);
+                        : mode == 3 ? launch_attn4<DV_, 3, 1>(q, k, vt, p, tok_pad, stream) \
+                                    : launch_attn4<DV_, 4, 0>(q, k, vt, p, tok_pad, stream);
     FGDM_ATTN4_CASE(16)
     FGDM_ATTN4_CASE(32)
     FGDM_ATTN4_CASE(48)

@@ -28,7 +28,7 @@
 namespace fgdm {
 
 int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dims,
-                const uint64_t* strides_bytes, const uint32_t* box);
+                const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes = 128);
 
 static constexpr int kBM = 128;
 static constexpr int kBK = 64;
@@ -39,16 +39,30 @@ static constexpr int kStgBytes = 32 * kStgRow + 8 * 128;  // per epilogue warp: 
 
 // CTAS = 2: a CTA pair (2-cluster, cta_group::2) computes a 256 x BN tile; each CTA stages its own 128 rows of A and
 // HALF of the B tile (BN/2 rows), so per-SM operand traffic (TMA writes + MMA reads) drops by the B half.
+// TMA epilogue (single-CTA kernels narrower than 256 columns: the short-K transformer linears, which are epilogue-paced):
+// every epilogue warp owns three rotating 32x32 bf16 panels (64-byte rows, 64B swizzle = what a TMA box {32, 32} reads
+// and writes). The first residual arrives in a panel by cp.async.bulk.tensor two panels ahead (across tile boundaries),
+// the lane that owns a row adds and packs IN PLACE with conflict-free 16-byte accesses, and the panel leaves by a TMA
+// store: no per-lane global access and no smem transposition in the epilogue; TMA clips / zero-fills the M tail.
+static constexpr int kTmaPanelBytes = 32 * 64;
+static constexpr int kTmaPanels = 3;
+static constexpr int kStgBytesTma = kTmaPanels * kTmaPanelBytes + 8 * 128;
+
 template <int BN, int CTAS = 1>
 struct GemmCfg {
+  static constexpr bool kTmaEpi = CTAS == 1 && BN != 256;
+  static constexpr int kStg = kTmaEpi ? kStgBytesTma : kStgBytes;   // staging bytes per epilogue warp
+  static constexpr int kStgBias = kTmaEpi ? kTmaPanels * kTmaPanelBytes : 32 * kStgRow;   // offset of the bias / LN panels
   static constexpr int kABytes = kBM * kBK * 2;                // 16 KB
   static constexpr int kBBytes = (BN / CTAS) * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages1 = (BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4;   // 224: 4 x 44 KB, 256: 4 x 48 KB
+  // single CTA: 64: 6 x 24 KB, 128: 5 x 32, 160: 4 x 36, 224: 3 x 44 (+ 56 KB of TMA panels), 256: 4 x 48 (+ 28 KB)
+  static constexpr int kStages1 = (BN <= 64) ? 6 : (BN <= 128) ? 5 : (BN <= 160) ? 4 : (BN <= 224) ? 3 : 4;
   static constexpr int kStages = CTAS == 1 ? kStages1 : 6;     // pair: 6 x (16 + <= 16) KB
   static constexpr int kAccStride = (BN <= 64) ? 64 : (BN <= 128) ? 128 : 256;  // TMEM columns
   static constexpr int kTmemCols = 2 * kAccStride;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kStgBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiWarps * kStg + 1024 /*align*/ + 512 /*barriers*/;
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
 // Work iterator shared by the three warp roles: classic mode hands out whole tiles round-robin; range mode walks this
@@ -97,7 +111,8 @@ FGDM_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpi
 template <int BN, int CTAS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
-               const __grid_constant__ CUtensorMap map_b, const __grid_constant__ GemmParams p) {
+               const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_out,
+               const __grid_constant__ CUtensorMap map_res, const __grid_constant__ GemmParams p) {
   using Cfg = GemmCfg<BN, CTAS>;
   constexpr int kStages = Cfg::kStages;
   const uint32_t cta_rank = CTAS == 2 ? cluster_ctarank() : 0;   // 0 = leader (issues the pair MMAs)
@@ -107,13 +122,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * Cfg::kABytes;
   uint8_t* smem_stg = smem + kStages * Cfg::kStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stg + kEpiWarps * kStgBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_stg + kEpiWarps * Cfg::kStg);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* acc_full = bars + 2 * kStages;
   uint64_t* acc_empty = bars + 2 * kStages + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   volatile uint32_t* split_flag = tmem_ptr + 1;    // epilogue warps: "this CTA finishes the tile"
+  uint64_t* res_bar = bars + 2 * kStages + 5;      // [kEpiWarps][kTmaPanels] residual panel landed (TMA epilogue)
+  static_assert((2 * kStages + 5 + kEpiWarps * kTmaPanels) * 8 <= 512, "barrier block");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -129,6 +146,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     for (int i = 0; i < 2; ++i) {
       mbar_init(&acc_full[i], 1);
       mbar_init(&acc_empty[i], kEpiWarps * CTAS);    // pair: the peer's epilogue warps arrive remotely on the leader
+    }
+    if (Cfg::kTmaEpi) {
+      tma_prefetch_desc(&map_out);
+      tma_prefetch_desc(&map_res);
+      for (int i = 0; i < kEpiWarps * kTmaPanels; ++i) mbar_init(&res_bar[i], 1);
     }
     fence_barrier_init();
   }
@@ -270,9 +292,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     const int ew = warp - 2;
     const int quarter = warp & 3;
     const int half = ew >> 2;
-    uint8_t* stg = smem_stg + ew * kStgBytes;
+    uint8_t* stg = smem_stg + ew * Cfg::kStg;
     const uint32_t stg_u32 = smem_u32(stg);
-    const uint32_t sbias_u32 = stg_u32 + 32 * kStgRow;           // [kMaxPanels][32] floats
+    const uint32_t sbias_u32 = stg_u32 + Cfg::kStgBias;          // [kMaxPanels][32] floats
     constexpr int kPanels = BN / 32;
     constexpr int kMaxP = (kPanels + 1) / 2;                     // panels per warp (upper bound)
     const int np = (kPanels + 1 - half) / 2;                     // this warp's panels: c0 = half*32 + 64*i
@@ -285,6 +307,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     int bias_pf_ntile = -1;
 #pragma unroll
     for (int i = 0; i < kMaxP; ++i) bias_pf[i] = 0.0f;
+    // ---- TMA epilogue state (p.tma_epi: classic tile loop, lean epilogue; see GemmCfg) ----
+    uint32_t tg = 0;                                             // panels this warp has processed: panel buffer = tg % 3
+    uint32_t tl = 0;                                             // panels whose residual load has been issued
+    int pf_tile = blockIdx.x, pf_i = 0;                          // prefetch cursor (tile, panel of this warp)
+    uint64_t* my_res_bar = res_bar + ew * kTmaPanels;
+    auto tma_npv = [&](int tl_) {                                // this warp's panels of tile tl_ that lie inside N
+      const int c0 = (tl_ % p.num_n_tiles) * BN + half * 32;
+      return max(0, min(np, (p.N - c0 + 63) / 64));
+    };
+    // keep the residual of the next two panels in flight (across tile boundaries). Called just before panel tg is written
+    // back: the buffer of panel tg + 2 was last read by the TMA store of panel tg - 1, issued most of a panel ago.
+    auto tma_prefetch_res = [&]() {
+      while (tl < tg + 3 && pf_tile < num_tiles) {
+        if (pf_i >= tma_npv(pf_tile)) { pf_tile += gridDim.x; pf_i = 0; continue; }
+        if (lane == 0) {
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          const uint32_t b = tl % kTmaPanels;
+          mbar_expect_tx(&my_res_bar[b], kTmaPanelBytes);
+          tma_load_2d(stg + b * kTmaPanelBytes, &map_res, &my_res_bar[b],
+                      (pf_tile % p.num_n_tiles) * BN + half * 32 + 64 * pf_i, (pf_tile / p.num_n_tiles) * kBM + quarter * 32);
+        }
+        ++tl;
+        ++pf_i;
+      }
+    };
+    if (Cfg::kTmaEpi && p.tma_epi && p.res0) tma_prefetch_res();
     while (it.next(tile, kc_begin, kc_end)) {
       const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
       const int my_slot = first_seg ? 0 : 1;
@@ -420,7 +468,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
           }
         };
         uint4 rres[4];
-        if (pre_res) load_res(0, rres);
+        const bool tma_epi = Cfg::kTmaEpi && p.tma_epi;
+        if (pre_res && !tma_epi) load_res(0, rres);
         if (p.bias) {
           // bias panels -> smem. The loads for this CTA's NEXT tile are issued here and land while this tile is
           // processed (4 registers): an epilogue-bound GEMM otherwise pays this latency on every tile.
@@ -496,7 +545,72 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         // are hoisted out of the panel loop and every mode test is gone.
         const bool lean = staged && !partial && p.bias != nullptr && p.rowvec == nullptr && p.alpha == 1.0f &&
                           p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr && (p.N & 31) == 0;
-        if (lean) {
+        if (Cfg::kTmaEpi && p.tma_epi) {
+          const int col0 = n_tile * BN + half * 32;
+          const int npv = tma_npv(tile);
+          const uint32_t row_u32 = lane * 64;                    // this lane's row inside a panel
+          const uint32_t swz = (lane >> 1) & 3;                  // 64B swizzle: 16-byte chunk c of row r sits at c ^ ((r >> 1) & 3)
+#pragma unroll 1
+          for (int i = 0; i < npv; ++i) {
+            const uint32_t buf = tg % kTmaPanels;
+            const uint32_t pan = stg_u32 + buf * kTmaPanelBytes + row_u32;
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
+            if (p.res0) mbar_wait(&my_res_bar[buf], (tg / kTmaPanels) & 1);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const uint4 u = ld_shared_16(sbias_u32 + i * 128 + j * 4);
+              v[j] = __uint_as_float(r[j]) + __uint_as_float(u.x);
+              v[j + 1] = __uint_as_float(r[j + 1]) + __uint_as_float(u.y);
+              v[j + 2] = __uint_as_float(r[j + 2]) + __uint_as_float(u.z);
+              v[j + 3] = __uint_as_float(r[j + 3]) + __uint_as_float(u.w);
+            }
+            if (p.res0) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint4 u = ld_shared_16(pan + ((q ^ swz) << 4));
+                const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float2 f = unpack_bf16x2(w4[e]);
+                  v[q * 8 + e * 2] += f.x;
+                  v[q * 8 + e * 2 + 1] += f.y;
+                }
+              }
+            } else {
+              // no load ordered this buffer behind its last TMA store (panel tg - 3): do it here
+              if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+              __syncwarp();
+            }
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+            if (p.row_stats) {       // statistics of the ROUNDED values: exactly what the consuming GEMM multiplies
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const float2 f = unpack_bf16x2(pk[j]);
+                rs_sum += f.x + f.y;
+                rs_sq = fmaf(f.x, f.x, fmaf(f.y, f.y, rs_sq));
+              }
+            }
+            if (p.res0) tma_prefetch_res();
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              st_shared_16(pan + ((q ^ swz) << 4), make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]));
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                               reinterpret_cast<uint64_t>(&map_out)),
+                           "r"(stg_u32 + buf * kTmaPanelBytes), "r"(col0 + 64 * i), "r"(m_warp)
+                           : "memory");
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            ++tg;
+          }
+        } else if (lean) {
           const int col0 = n_tile * BN + half * 32;
           const __nv_bfloat16* rptr[4];
           __nv_bfloat16* optr[4];
@@ -785,6 +899,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
   }
 
+  if (Cfg::kTmaEpi && p.tma_epi && warp >= 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   if (CTAS == 2) cluster_sync_all();   // the peer may still be signalling this CTA's barriers / reading its smem
@@ -796,8 +911,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 }
 
 template <int BN, int CTAS>
-static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUtensorMap& mb, const GemmParams& p,
-                     cudaStream_t stream) {
+static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUtensorMap& mb, const CUtensorMap& mo,
+                     const CUtensorMap& mr, const GemmParams& p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, CTAS>;
   static bool configured = false;
   if (!configured) {
@@ -825,7 +940,7 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = CTAS == 2 ? 2 : 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS>, ma0, ma1, mb, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS>, ma0, ma1, mb, mo, mr, p);
   if (e != cudaSuccess) { set_error("gemm_tc_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("gemm_tc_kernel");
 }
@@ -1000,20 +1115,40 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     uint32_t box[2] = {kBK, static_cast<uint32_t>(BN / ctas)};   // pair mode: each CTA fetches its half of the B tile
     if (encode_tmap(&mb, w, 2, dims, strides, box)) return -1;
   }
+  // TMA epilogue: the lean epilogue (bf16 out, bias, optional first residual / row statistics) of the single-CTA kernels
+  // narrower than 256 columns, classic tile loop. FGDM_TMA_EPI=0 switches it off (A/B measurements).
+  static int tma_epi_on = -1;
+  if (tma_epi_on < 0) { const char* e = getenv("FGDM_TMA_EPI"); tma_epi_on = e ? atoi(e) : 1; }
+  __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + p.col_off;
+  p.tma_epi = tma_epi_on && ctas == 1 && BN != 256 && p.range_ctas == 0 && p.out_mode == kOutBf16 && p.bias != nullptr &&
+              p.rowvec == nullptr && p.alpha == 1.0f && p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr &&
+              (p.N & 31) == 0 && (reinterpret_cast<uintptr_t>(obase) & 15) == 0 && (p.ldo & 7) == 0 &&
+              (p.res0 == nullptr || ((reinterpret_cast<uintptr_t>(p.res0) & 15) == 0 && (p.ld_res0 & 7) == 0));
+  CUtensorMap mo = mb, mr = mb;
+  if (p.tma_epi) {
+    uint64_t dims[2] = {static_cast<uint64_t>(p.N), static_cast<uint64_t>(p.M)};
+    uint32_t box[2] = {32, 32};
+    uint64_t so[1] = {static_cast<uint64_t>(p.ldo) * 2};
+    if (encode_tmap(&mo, obase, 2, dims, so, box, 64)) return -1;
+    if (p.res0) {
+      uint64_t sr[1] = {static_cast<uint64_t>(p.ld_res0) * 2};
+      if (encode_tmap(&mr, p.res0, 2, dims, sr, box, 64)) return -1;
+    }
+  }
   if (ctas == 2) {
     switch (BN) {
-      case 160: return launch_bn<160, 2>(ma0, ma1, mb, p, stream);
-      case 224: return launch_bn<224, 2>(ma0, ma1, mb, p, stream);
-      case 256: return launch_bn<256, 2>(ma0, ma1, mb, p, stream);
+      case 160: return launch_bn<160, 2>(ma0, ma1, mb, mo, mr, p, stream);
+      case 224: return launch_bn<224, 2>(ma0, ma1, mb, mo, mr, p, stream);
+      case 256: return launch_bn<256, 2>(ma0, ma1, mb, mo, mr, p, stream);
       default: set_error("gemm: unsupported pair BN=%d", BN); return -1;
     }
   }
   switch (BN) {
-    case 64: return launch_bn<64, 1>(ma0, ma1, mb, p, stream);
-    case 128: return launch_bn<128, 1>(ma0, ma1, mb, p, stream);
-    case 160: return launch_bn<160, 1>(ma0, ma1, mb, p, stream);
-    case 224: return launch_bn<224, 1>(ma0, ma1, mb, p, stream);
-    case 256: return launch_bn<256, 1>(ma0, ma1, mb, p, stream);
+    case 64: return launch_bn<64, 1>(ma0, ma1, mb, mo, mr, p, stream);
+    case 128: return launch_bn<128, 1>(ma0, ma1, mb, mo, mr, p, stream);
+    case 160: return launch_bn<160, 1>(ma0, ma1, mb, mo, mr, p, stream);
+    case 224: return launch_bn<224, 1>(ma0, ma1, mb, mo, mr, p, stream);
+    case 256: return launch_bn<256, 1>(ma0, ma1, mb, mo, mr, p, stream);
     default: set_error("gemm: unsupported BN=%d", BN); return -1;
   }
 }

@@ -68,6 +68,7 @@ struct GemmParams {
   // covers only part of a tile's K dumps its fp32 partial into its own scratch slot; the LAST contributor of a tile
   // to finish (ticket) sums the partials in CTA order (bit-reproducible) and runs the epilogue. 0 = classic loop.
   int range_ctas;
+  int tma_epi;                  // set by the launcher: lean epilogue through TMA panels (GemmCfg::kTmaEpi kernels only)
   float* split_ws;              // [cta][2 slots: first / later segment][128 x BN] fp32, library-owned
   unsigned int* split_tickets;  // [tile], zero between launches
 };
