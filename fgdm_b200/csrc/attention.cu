@@ -433,38 +433,38 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
 
 // =====================================================================================================================
 // attention4_kernel: the self-attention kernel for small head dims (d <= 56: the UNet's 64x64 level, d = 40, N = 4096,
-// which is 3/4 of all attention time). The exponential, not the tensor core, bounds this shape: 16 ex2/clk/SM is 1024
-// clk per 128x128 score tile against 448 clk of MMA, so the kernel is organised around keeping the MUFU pipe fed:
+// which is 3/4 of all attention time). The exponential, not the tensor core, bounds this shape: 16 ex2/clk/SM
+// (tools/ubench/mufu.cu measures 15.4 with the softmax's instruction mix) is 1024 clk per 128x128 score tile against
+// ~450 clk of MMA, so the kernel is organised around the MUFU pipe:
 //   * FOUR 128-row query tiles per CTA and 64-key tiles: ONE thread per query row holds its 64 scores in registers, so
-//     there is no partner-warp exchange of half-row maxima (the old kernel's 64-thread named barrier per tile) and every
-//     SM sub-partition runs 4 softmax warps that belong to 4 DIFFERENT query tiles: they are coupled only through the
-//     K/V ring (KST stages), so one warp's TMEM wait / max phase is covered by the other three warps' exp phases;
+//     there is no partner-warp exchange of half-row maxima (attention_kernel's 64-thread named barrier per tile) and
+//     every SM sub-partition runs 4 softmax warps that belong to 4 different query tiles;
 //   * S_t = Q_t K^T is a 128x64 MMA over ceil(d/16) K-steps only (d = 40: 3 instead of the 4 a 64-wide chunk holds);
-//   * everything else as in attention_kernel: TMA rings, S and O in TMEM, lazy 2^8 rescale, bf16 P through swizzled
-//     smem, the softmax denominator from an all-ones V^T row.
+//   * two bf16 P buffers per tile in swizzled smem; no barrier wait protects them on the fast path: S_t(j) is issued
+//     behind PV_t(j-2) by the same thread and tcgen05.commit covers every earlier MMA of that thread, so bar_s(j)
+//     already says that P buffer j & 1 is free;
+//   * setmaxnreg: launched at 80 registers, the issue / producer warpgroups drop to 32 and the softmax warpgroups take
+//     104, enough for a 64-score row without spills;
+//   * K and V rings have their own producer warps (a K load never queues behind a V slot the slowest tile still reads).
 // TMEM: 4 tiles x 128 columns (S at +0: 64 columns, O at +64: DV <= 64 columns) = 512.
+// What was measured and NOT kept (B200, 16x8 heads, N = 4096, d = 40; profiles/r02_attention_experiments.md): P in
+// TMEM with a TS MMA for PV (854 us: S(j+1) must then follow PV(j)), one P buffer + 3..6 ring stages (771..804 us),
+// MUFU ping-pong between tile pairs through named barriers (760 us), the softmax warps issuing their own MMAs behind
+// 128-thread named barriers (1023 us), mbarrier suspend-time hints (935 us). This form: 707 us (attention_kernel: 745).
 // =====================================================================================================================
-template <int DV, int KST, int PB>
+template <int DV, int KST>
 struct Attn4Cfg {
-  static constexpr int QT = 4, BN = 64;
+  static constexpr int QT = 4, BN = 64, PB = 2;
   static constexpr int kQBytes = 128 * 128;            // one swizzle atom [128 rows x 128 B] per query tile
   static constexpr int kKBytes = BN * 128;
   static constexpr int kVBytes = DV * 128;             // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kPBytes = 128 * 128;            // [128 rows x 64 keys] bf16
-  // PB == 0: P never touches shared memory. The softmax threads store bf16 P into the first 32 TMEM columns of their
-  // S tile (tcgen05.st) and PV is a TS MMA (A = P from TMEM, B = V^T from smem). Shared-memory bandwidth (128 B/clk/SM)
-  // is what held the smem-P variants at 65 % of the ex2 bound: per 4x(128x64) step the SS MMAs read 72 KB (Q, K) +
-  // 88 KB (P, V) and the softmax warps write 64 KB of P = 1750 clk of smem time next to 2048 clk of MUFU time; with P
-  // in TMEM it is 96 KB = 750 clk. The price: S_t(j+1) overwrites P_t(j), so it is issued after PV_t(j) (same thread,
-  // in order) instead of during softmax(j) - covered by the other three query tiles of the sub-partition.
-  static constexpr bool kTS = PB == 0;
   static constexpr int kSmemBytes = 1024 + QT * kQBytes + KST * (kKBytes + kVBytes) + QT * PB * kPBytes + 512;
   static constexpr int kSoftmaxWarps = 4 * QT;
-  static constexpr int kIssue0 = kSoftmaxWarps;
-  static constexpr int kTma = kSoftmaxWarps + QT;
-  // 6 warpgroups: 4 softmax, 1 MMA issue, 1 with the TMA producer warp (+3 idle warps: setmaxnreg is per warpgroup).
-  // Registers are allocated for 24 warps either way (4-warp granularity): launched at 80 per thread, the issue / TMA
-  // warpgroups drop to 32 and hand theirs to the softmax warpgroups (104), which then hold a 64-score row without spills.
+  static constexpr int kIssue0 = kSoftmaxWarps;        // QT MMA-issue warps (one per query tile)
+  static constexpr int kKProd = kSoftmaxWarps + QT;    // TMA producer of Q and the K ring
+  static constexpr int kVProd = kKProd + 1;            // TMA producer of the V ring
+  // 6 warpgroups (setmaxnreg is per warpgroup): 4 softmax, 1 MMA issue, 1 with the two producers + 2 idle warps
   static constexpr int kThreads = 32 * 24;
   static constexpr int kRegsSoftmax = 104, kRegsOther = 32;
   static constexpr int kTmemStride = 128;
@@ -472,30 +472,34 @@ struct Attn4Cfg {
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
-template <int DV, int KST, int PB>
-__global__ void __launch_bounds__(Attn4Cfg<DV, KST, PB>::kThreads, 1)
+template <int DV, int KST>
+__global__ void __launch_bounds__(Attn4Cfg<DV, KST>::kThreads, 1)
 attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                   const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
-  using Cfg = Attn4Cfg<DV, KST, PB>;
-  constexpr int QT = Cfg::QT, BN = Cfg::BN;
+  using Cfg = Attn4Cfg<DV, KST>;
+  constexpr int QT = Cfg::QT, BN = Cfg::BN, PB = Cfg::PB;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-  uint8_t* sQ = smem;                                  // [QT]
-  uint8_t* sK = sQ + QT * Cfg::kQBytes;                // [KST]
-  uint8_t* sV = sK + KST * Cfg::kKBytes;               // [KST]
-  uint8_t* sP = sV + KST * Cfg::kVBytes;               // [QT][PB]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + QT * PB * Cfg::kPBytes);
-  uint64_t* bar_q = bars;
-  uint64_t* bar_k = bars + 1;                          // [KST] K(j) landed
-  uint64_t* bar_v = bar_k + KST;                       // [KST] V(j) landed
-  uint64_t* k_empty = bar_v + KST;                     // [KST] all QT tiles' S(j) have read the stage
-  uint64_t* v_empty = k_empty + KST;                   // [KST] all QT tiles' PV(j) have read the stage
-  uint64_t* bar_s = v_empty + KST;                     // [QT] S_t(j) complete
-  uint64_t* bar_o = bar_s + QT;                        // [QT] PV_t(j) complete
-  uint64_t* bar_sfree = bar_o + QT;                    // [QT] S_t(j) is in registers (4 warp arrivals)
-  uint64_t* bar_pready = bar_sfree + QT;               // [QT] P_t(j) is in smem       (4 warp arrivals)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar_pready + QT);
-  static_assert((1 + 4 * KST + 4 * QT) * 8 + 4 <= 512, "barrier block");
+  // every shared-memory object is a 32-bit shared address: base + compile-time offset
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  constexpr uint32_t oQ = 0;                                       // [QT]
+  constexpr uint32_t oK = oQ + QT * Cfg::kQBytes;                  // [KST]
+  constexpr uint32_t oV = oK + KST * Cfg::kKBytes;                 // [KST]
+  constexpr uint32_t oP = oV + KST * Cfg::kVBytes;                 // [QT][PB]
+  constexpr uint32_t oB = oP + QT * PB * Cfg::kPBytes;             // barriers
+  constexpr uint32_t bQ = oB;
+  constexpr uint32_t bK = bQ + 8;                                  // [KST] K(j) landed
+  constexpr uint32_t bV = bK + 8 * KST;                            // [KST] V(j) landed
+  constexpr uint32_t bKe = bV + 8 * KST;                           // [KST] all QT tiles' S(j) have read the stage
+  constexpr uint32_t bVe = bKe + 8 * KST;                          // [KST] all QT tiles' PV(j) have read the stage
+  constexpr uint32_t bS = bVe + 8 * KST;                           // [QT] S_t(j) complete
+  constexpr uint32_t bO = bS + 8 * QT;                             // [QT][2] PV_t(j) complete, barrier j & 1
+  constexpr uint32_t bSf = bO + 16 * QT;                           // [QT] S_t(j) is in registers (4 warp arrivals)
+  // P_t(j) is written (4 warp arrivals), barrier j & 1: the four warps of a tile run up to one tile apart (nothing but
+  // sfree couples them), so a fast warp's arrival for tile j+1 must not land in the phase the slow warp still owes for
+  // tile j; with two alternating barriers it cannot (sfree keeps the skew below two tiles)
+  constexpr uint32_t bPr = bSf + 8 * QT;                           // [QT][2]
+  constexpr uint32_t oTm = bPr + 16 * QT;                          // TMEM base address
+  static_assert(oTm + 4 - oB <= 512, "barrier block");
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -509,29 +513,35 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     tma_prefetch_desc(&map_q);
     tma_prefetch_desc(&map_k);
     tma_prefetch_desc(&map_vt);
-    mbar_init(bar_q, 1);
+    auto init = [&](uint32_t off, uint32_t count) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(sbase + off), "r"(count));
+    };
+    init(bQ, 1);
     for (int i = 0; i < KST; ++i) {
-      mbar_init(&bar_k[i], 1);
-      mbar_init(&bar_v[i], 1);
-      mbar_init(&k_empty[i], QT);
-      mbar_init(&v_empty[i], QT);
+      init(bK + 8 * i, 1);
+      init(bV + 8 * i, 1);
+      init(bKe + 8 * i, QT);
+      init(bVe + 8 * i, QT);
     }
     for (int t = 0; t < QT; ++t) {
-      mbar_init(&bar_s[t], 1);
-      mbar_init(&bar_o[t], 1);
-      mbar_init(&bar_sfree[t], 4);
-      mbar_init(&bar_pready[t], 4);
+      init(bS + 8 * t, 1);
+      init(bO + 16 * t, 1);
+      init(bO + 16 * t + 8, 1);
+      init(bSf + 8 * t, 4);
+      init(bPr + 16 * t, 4);
+      init(bPr + 16 * t + 8, 4);
     }
     fence_barrier_init();
   }
-  if (warp == Cfg::kTma) {
-    tmem_alloc(tmem_ptr, 512);
+  if (warp == Cfg::kKProd) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sbase + oTm), "r"(512) : "memory");
     tmem_relinquish();
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(sbase + oTm) : "memory");
   pdl_wait();
   pdl_launch_dependents();
 
@@ -541,112 +551,38 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(Cfg::kRegsSoftmax));
   }
 
-  if (warp > Cfg::kTma) {
-    // idle warps of the producer warpgroup
-  } else if (warp == Cfg::kTma) {
-    // ===================== TMA producer: 4 Q tiles once, then KST-stage K and V rings =====================
-    if (lane == 0) {
-      mbar_expect_tx(bar_q, QT * Cfg::kQBytes);
-#pragma unroll
-      for (int t = 0; t < QT; ++t) tma_load_3d(sQ + t * Cfg::kQBytes, &map_q, bar_q, 0, q0 + t * 128, bh);
-      int st = 0, ph = 0;                               // ring position of load j, parity of its (j / KST)-th use
-      for (int j = 0; j < num_kv; ++j) {
-        if (j >= KST) mbar_wait(&k_empty[st], ph ^ 1);
-        mbar_expect_tx(&bar_k[st], Cfg::kKBytes);
-        tma_load_3d(sK + st * Cfg::kKBytes, &map_k, &bar_k[st], 0, j * BN, bh);
-        if (j >= KST) mbar_wait(&v_empty[st], ph ^ 1);
-        mbar_expect_tx(&bar_v[st], Cfg::kVBytes);
-        tma_load_3d(sV + st * Cfg::kVBytes, &map_vt, &bar_v[st], j * BN, 0, bh);
-        if (++st == KST) { st = 0; ph ^= 1; }
-      }
-    }
-  } else if (warp >= Cfg::kIssue0) {
-    // ===================== MMA issue warp of query tile t =====================
-    const int t = warp - Cfg::kIssue0;
-    const uint32_t tm = tmem_base + t * Cfg::kTmemStride;
-    auto issue_s = [&](int st) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, BN);
-      const uint64_t dq = make_desc_sw128(smem_u32(sQ + t * Cfg::kQBytes));
-      const uint64_t dk = make_desc_sw128(smem_u32(sK + st * Cfg::kKBytes));
-      for (int k = 0; k < ksteps; ++k) tc_mma_bf16(tm, dq + 2 * k, dk + 2 * k, idesc, k != 0 ? 1u : 0u);
-      tc_commit(&bar_s[t]);
-      tc_commit(&k_empty[st]);
-    };
-    auto issue_pv = [&](int j, int st) {
-      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
-      const uint64_t dv = make_desc_sw128(smem_u32(sV + st * Cfg::kVBytes));
-      if constexpr (Cfg::kTS) {
-#pragma unroll
-        for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16_ts(tm + BN, tm + 8 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
-      } else {
-        const uint64_t dp = make_desc_sw128(smem_u32(sP + (t * PB + (PB == 2 ? (j & 1) : 0)) * Cfg::kPBytes));
-#pragma unroll
-        for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16(tm + BN, dp + 2 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
-      }
-      tc_commit(&bar_o[t]);
-      tc_commit(&v_empty[st]);
-    };
-    if (lane == 0) {
-      mbar_wait(bar_q, 0);
-      mbar_wait(&bar_k[0], 0);
-      tc_fence_after();
-      issue_s(0);
-    }
-    int st = 0, ph = 0;                                 // ring position / parity of tile j
-    for (int j = 0; j < num_kv; ++j) {
-      int st1 = st + 1, ph1 = ph;
-      if (st1 == KST) { st1 = 0; ph1 ^= 1; }
-      if (!Cfg::kTS && lane == 0 && j + 1 < num_kv) {
-        mbar_wait(&bar_k[st1], ph1);
-        mbar_wait(&bar_sfree[t], j & 1);               // S_t(j) is in registers: its TMEM columns are free
-        tc_fence_after();
-        issue_s(st1);                                   // overlaps the softmax of tile j
-      }
-      __syncwarp();
-      mbar_wait(&bar_v[st], ph);
-      // ones-row: V^T row dv_real := 1.0 (a full 128-byte swizzle row). All four issue warps write the same bytes.
-      if (lane < 8) {
-        st_shared_16(smem_u32(sV + st * Cfg::kVBytes) + p.dv_real * 128 + lane * 16,
-                     make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u));
-      }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        if (Cfg::kTS && j + 1 < num_kv) mbar_wait(&bar_k[st1], ph1);   // so that S(j+1) follows PV(j) without a gap
-        mbar_wait(&bar_pready[t], j & 1);
-        tc_fence_after();
-        issue_pv(j, st);
-        if (Cfg::kTS && j + 1 < num_kv) issue_s(st1);   // overwrites P_t(j): in order behind PV_t(j) (same issuing thread)
-      }
-      __syncwarp();
-      st = st1;
-      ph = ph1;
-    }
-  } else {
+  // (the softmax branch comes first: with the producers in front ptxas 12.9 fails to allocate the 104-register region)
+  if (warp < Cfg::kIssue0) {
     // ===================== softmax warps: one thread per query row =====================
     const int t = warp >> 2;                           // query tile
     const int row = (warp & 3) * 32 + lane;            // query row within the tile == TMEM lane
     const uint32_t s_addr = tmem_base + t * Cfg::kTmemStride + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     const uint32_t o_addr = s_addr + BN;
-    uint64_t* my_bar_o = &bar_o[t];
+    const uint32_t a_bs = sbase + bS + 8 * t, a_bo = sbase + bO + 16 * t, a_sf = sbase + bSf + 8 * t, a_pr = sbase + bPr + 16 * t;
     float m_ref = -INFINITY;                           // reference max (scaled, log2 domain) used for exp2
-    const uint32_t sP_row0 = smem_u32(sP + t * PB * Cfg::kPBytes) + row * 128;
-    const int sw = row & 7;
+    const uint32_t sP_row0 = sbase + oP + t * PB * Cfg::kPBytes + row * 128;
+    const uint32_t sw = (row & 7) << 4;
+    const float sc = p.scale_log2;
+
+    // PV_t(jj) complete? Barrier jj & 1 of the tile; its phases are 2 tiles apart, and the caller always knows that
+    // PV_t(jj - 2) has completed (bar_s(jj + 1) or later was seen), so the parity test is unambiguous.
+    auto wait_pv = [&](int jj) {
+      mbar_wait_a(a_bo + 8 * (jj & 1), (jj >> 1) & 1);
+      tc_fence_after();
+    };
 
     for (int j = 0; j < num_kv; ++j) {
       const int valid = p.Nk - j * BN;                  // keys valid in this tile (may exceed BN)
       const bool full = valid >= BN;                    // CTA-uniform
-      mbar_wait(&bar_s[t], j & 1);
+      mbar_wait_a(a_bs, j & 1);
       tc_fence_after();
       uint32_t s[BN];
       tmem_ld_32x32(s_addr, *reinterpret_cast<uint32_t(*)[32]>(&s[0]));
       tmem_ld_32x32(s_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&s[32]));
       tmem_ld_wait();
-      if constexpr (!Cfg::kTS) {
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bar_sfree[t]);
-      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(a_sf);               // S_t(j) is in registers: S_t(j+1) may overwrite the columns
       float rmax;
       {
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -670,15 +606,8 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         }
         rmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
       }
-      const float tmax = rmax * p.scale_log2;
+      const float tmax = rmax * sc;
 
-      // ---- single P buffer: PV(j-1) must have drained before the P tile is overwritten ----
-      // (TS mode: S_t(j) was issued behind PV_t(j-1) by the same thread and tcgen05.commit covers every earlier MMA of
-      // that thread, so bar_s(j) already implies that PV_t(j-1) has read P_t(j-1) and written O)
-      if (PB == 1 && j > 0) {
-        mbar_wait(my_bar_o, (j - 1) & 1);
-        tc_fence_after();
-      }
       // ---- lazy rescale: refresh the reference max only when it grew by more than 2^8 ----
       const bool need = tmax > m_ref + kRescaleThreshold;
       if (__any_sync(0xffffffffu, need)) {
@@ -686,10 +615,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         const float alpha = need ? fast_exp2(m_ref - m_new) : 1.0f;   // exp2(-inf) = 0 on the first tile
         m_ref = m_new;
         if (j > 0) {
-          if (PB == 2) {                                  // O may only be touched once PV(j-1) has drained
-            mbar_wait(my_bar_o, (j - 1) & 1);
-            tc_fence_after();
-          }
+          wait_pv(j - 1);                                 // O may only be touched once PV(j-1) has drained
 #pragma unroll
           for (int c = 0; c < DV; c += 8) {
             uint32_t r[8];
@@ -703,63 +629,35 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
         }
       }
 
-      // ---- probabilities -> bf16 P: TMEM columns [0,32) of this tile (TS) or the swizzled smem tile ----
+      // ---- probabilities -> bf16 P buffer j & 1 (128B swizzle, K-major): 8 chunks of 8 keys per row ----
       const float neg_m = -m_ref;
-      if constexpr (Cfg::kTS) {
+      const uint32_t sP_row = sP_row0 + (j & 1) * Cfg::kPBytes;
+      auto emit = [&](auto masked) {
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {                     // two 16-column stores: the S registers die as P is produced
-          uint32_t pk[16];
-          if (full) {
+        for (int c = 0; c < BN; c += 8) {
+          uint32_t pk[4];
 #pragma unroll
-            for (int c = 0; c < 32; c += 2)
-              pk[c >> 1] = pack_bf16x2(fast_exp2(fmaf(__uint_as_float(s[32 * h + c]), p.scale_log2, neg_m)),
-                                       fast_exp2(fmaf(__uint_as_float(s[32 * h + c + 1]), p.scale_log2, neg_m)));
-          } else {
-#pragma unroll
-            for (int c = 0; c < 32; c += 2) {
-              const int cc = 32 * h + c;
-              const float p0 = cc < valid ? fast_exp2(fmaf(__uint_as_float(s[cc]), p.scale_log2, neg_m)) : 0.0f;
-              const float p1 = cc + 1 < valid ? fast_exp2(fmaf(__uint_as_float(s[cc + 1]), p.scale_log2, neg_m)) : 0.0f;
-              pk[c >> 1] = pack_bf16x2(p0, p1);
+          for (int i = 0; i < 8; i += 2) {
+            float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), sc, neg_m));
+            float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), sc, neg_m));
+            if constexpr (decltype(masked)::value) {
+              if (c + i >= valid) p0 = 0.0f;
+              if (c + i + 1 >= valid) p1 = 0.0f;
             }
+            pk[i >> 1] = pack_bf16x2(p0, p1);
           }
-          tmem_st_32x16(s_addr + 16 * h, pk);
+          st_shared_16(sP_row + ((c << 1) ^ sw), make_uint4(pk[0], pk[1], pk[2], pk[3]));
         }
-        tmem_st_wait();
-      } else {
-        const uint32_t sP_row = sP_row0 + (PB == 2 ? (j & 1) * Cfg::kPBytes : 0);
-        auto emit = [&](auto masked) {
-#pragma unroll
-          for (int c = 0; c < BN; c += 8) {
-            uint32_t pk[4];
-#pragma unroll
-            for (int i = 0; i < 8; i += 2) {
-              float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
-              float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
-              if constexpr (decltype(masked)::value) {
-                if (c + i >= valid) p0 = 0.0f;
-                if (c + i + 1 >= valid) p1 = 0.0f;
-              }
-              pk[i >> 1] = pack_bf16x2(p0, p1);
-            }
-            st_shared_16(sP_row + (((c >> 3) ^ sw) << 4), make_uint4(pk[0], pk[1], pk[2], pk[3]));
-          }
-        };
-        if (full) emit(std::false_type{}); else emit(std::true_type{});
-        fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
-        // Observe PV(j-1) BEFORE enabling PV(j): every bar_o phase is seen in order (no parity aliasing).
-        if (PB == 2 && j > 0) mbar_wait(my_bar_o, (j - 1) & 1);
-      }
+      };
+      if (full) emit(std::false_type{}); else emit(std::true_type{});
+      fence_proxy_async_smem();   // generic-proxy smem writes -> visible to the tensor-core (async) proxy
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bar_pready[t]);
+      if (lane == 0) mbar_arrive_a(a_pr + 8 * (j & 1));
     }
 
     // ---- normalise and store: out[img, q, head*d + e]; the denominator is O column dv_real ----
-    // (TS mode never looked at bar_o inside the loop, but bar_s(j) implied PV(j-1): every earlier phase of bar_o has
-    // completed before the last softmax tile began, so the parity wait below can only match the final phase)
-    mbar_wait(my_bar_o, (num_kv - 1) & 1);
-    tc_fence_after();
+    wait_pv(num_kv - 1);
     const int q = q0 + t * 128 + row;
     float inv;
     {
@@ -784,22 +682,105 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
                        pack_bf16x2(__uint_as_float(r[6]) * inv, __uint_as_float(r[7]) * inv));
       }
     }
+  } else if (warp < Cfg::kKProd) {
+    // ===================== MMA issue warp of query tile t =====================
+    const int t = warp - Cfg::kIssue0;
+    const uint32_t tm = tmem_base + t * Cfg::kTmemStride;
+    const uint64_t dq = make_desc_sw128(sbase + oQ + t * Cfg::kQBytes);
+    const uint64_t dk0 = make_desc_sw128(sbase + oK);
+    const uint64_t dv0 = make_desc_sw128(sbase + oV);
+    const uint64_t dp0 = make_desc_sw128(sbase + oP + t * PB * Cfg::kPBytes);
+    auto issue_s = [&](int st) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BN);
+      const uint64_t dk = dk0 + static_cast<uint64_t>(st * (Cfg::kKBytes >> 4));
+      for (int k = 0; k < ksteps; ++k) tc_mma_bf16(tm, dq + 2 * k, dk + 2 * k, idesc, k != 0 ? 1u : 0u);
+      tc_commit_a(sbase + bS + 8 * t);
+      tc_commit_a(sbase + bKe + 8 * st);
+    };
+    auto issue_pv = [&](int j, int st) {
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
+      const uint64_t dv = dv0 + static_cast<uint64_t>(st * (Cfg::kVBytes >> 4));
+      const uint64_t dp = dp0 + static_cast<uint64_t>((j & 1) * (Cfg::kPBytes >> 4));
+#pragma unroll
+      for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16(tm + BN, dp + 2 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
+      tc_commit_a(sbase + bO + 16 * t + 8 * (j & 1));
+      tc_commit_a(sbase + bVe + 8 * st);
+    };
+    if (lane == 0) {
+      mbar_wait_a(sbase + bQ, 0);
+      mbar_wait_a(sbase + bK, 0);
+      tc_fence_after();
+      issue_s(0);
+    }
+    int st = 0, ph = 0;                                 // ring position / parity of tile j
+    for (int j = 0; j < num_kv; ++j) {
+      int st1 = st + 1, ph1 = ph;
+      if (st1 == KST) { st1 = 0; ph1 ^= 1; }
+      if (lane == 0 && j + 1 < num_kv) {
+        mbar_wait_a(sbase + bK + 8 * st1, ph1);
+        mbar_wait_a(sbase + bSf + 8 * t, j & 1);        // S_t(j) is in registers: its TMEM columns are free
+        tc_fence_after();
+        issue_s(st1);                                   // overlaps the softmax of tile j
+      }
+      __syncwarp();
+      mbar_wait_a(sbase + bV + 8 * st, ph);
+      // ones-row: V^T row dv_real := 1.0 (a full 128-byte swizzle row). All four issue warps write the same bytes.
+      if (lane < 8) {
+        st_shared_16(sbase + oV + st * Cfg::kVBytes + p.dv_real * 128 + lane * 16,
+                     make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u));
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_wait_a(sbase + bPr + 16 * t + 8 * (j & 1), (j >> 1) & 1);
+        tc_fence_after();
+        issue_pv(j, st);
+      }
+      __syncwarp();
+      st = st1;
+      ph = ph1;
+    }
+  } else if (warp == Cfg::kKProd) {
+    // ===================== TMA producer: 4 Q tiles once, then the KST-stage K ring =====================
+    if (lane == 0) {
+      mbar_expect_tx_a(sbase + bQ, QT * Cfg::kQBytes);
+#pragma unroll
+      for (int t = 0; t < QT; ++t) tma_load_3d_a(sbase + oQ + t * Cfg::kQBytes, &map_q, sbase + bQ, 0, q0 + t * 128, bh);
+      int st = 0, ph = 0;                               // ring position of load j, parity of its (j / KST)-th use
+      for (int j = 0; j < num_kv; ++j) {
+        if (j >= KST) mbar_wait_a(sbase + bKe + 8 * st, ph ^ 1);
+        mbar_expect_tx_a(sbase + bK + 8 * st, Cfg::kKBytes);
+        tma_load_3d_a(sbase + oK + st * Cfg::kKBytes, &map_k, sbase + bK + 8 * st, 0, j * BN, bh);
+        if (++st == KST) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == Cfg::kVProd) {
+    // ===================== TMA producer of the V ring =====================
+    if (lane == 0) {
+      int st = 0, ph = 0;
+      for (int j = 0; j < num_kv; ++j) {
+        if (j >= KST) mbar_wait_a(sbase + bVe + 8 * st, ph ^ 1);
+        mbar_expect_tx_a(sbase + bV + 8 * st, Cfg::kVBytes);
+        tma_load_3d_a(sbase + oV + st * Cfg::kVBytes, &map_vt, sbase + bV + 8 * st, j * BN, 0, bh);
+        if (++st == KST) { st = 0; ph ^= 1; }
+      }
+    }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == Cfg::kTma) {
+  if (warp == Cfg::kKProd) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
 }
 
-template <int DV, int KST, int PB>
+template <int DV, int KST>
 static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams p, int tok_pad, cudaStream_t stream) {
-  using Cfg = Attn4Cfg<DV, KST, PB>;
+  using Cfg = Attn4Cfg<DV, KST>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("attention4: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -827,13 +808,12 @@ static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams
     if (encode_tmap(&mv, vt, 3, dims, strides, box)) return -1;
   }
   dim3 grid((p.Nq + 511) / 512, p.BH, 1);
-  cudaError_t e = launch_pdl(attention4_kernel<DV, KST, PB>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p);
+  cudaError_t e = launch_pdl(attention4_kernel<DV, KST>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p);
   if (e != cudaSuccess) { set_error("attention4_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("attention4_kernel");
 }
 
-// FGDM_ATTN4: 0 = never use attention4_kernel, 1 (default) = P in TMEM (TS MMA), 4-stage K/V ring; 2 / 3 = P through
-// shared memory (2 stages + 2 P buffers / 3 stages + 1 P buffer)
+// FGDM_ATTN4=0: never use attention4_kernel (A/B against attention_kernel)
 static int attn4_mode() {
   static int mode = -1;
   if (mode < 0) {
@@ -880,11 +860,8 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
 
   // small head dims, long self-attention: four query tiles per CTA, one thread per row (attention4_kernel)
   if (KA == 1 && nsplit == 1 && DV <= 64 && !causal && Nq >= 512 && Nk >= 512 && attn4_mode() != 0) {
-    const int mode = attn4_mode();
 #define FGDM_ATTN4_CASE(DV_) \
-    if (DV == DV_) return mode == 2 ? launch_attn4<DV_, 2, 2>(q, k, vt, p, tok_pad, stream) \
-                        : mode == 3 ? launch_attn4<DV_, 3, 1>(q, k, vt, p, tok_pad, stream) \
-                                    : launch_attn4<DV_, 4, 0>(q, k, vt, p, tok_pad, stream);
+    if (DV == DV_) return launch_attn4<DV_, 2>(q, k, vt, p, tok_pad, stream);
     FGDM_ATTN4_CASE(16)
     FGDM_ATTN4_CASE(32)
     FGDM_ATTN4_CASE(48)

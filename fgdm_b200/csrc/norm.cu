@@ -363,8 +363,11 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
   const int rc = try_groupnorm_slab(x0, x1, y, gamma, beta, NB, HW, C0, C1, G, eps, silu, stream);
   if (rc != 0) return rc < 0 ? -1 : 0;
   const GnGeom g = gn_geom(NB, HW, C0, C1, G);
-  const dim3 grid(g.chunks, NB);
   const size_t smem = static_cast<size_t>(2) * g.k * C * sizeof(float);
+  float2* partial = reinterpret_cast<float2*>(workspace);
+  float2* stats = partial + static_cast<size_t>(NB) * kGnMaxChunks * G;
+  if (NB > kGnMaxImages) { set_error("groupnorm: NB=%d > %d", NB, kGnMaxImages); return -1; }
+  const dim3 grid(g.chunks, NB);
   static unsigned int* counters = nullptr;       // per-image tickets, zero between launches (single stream per process)
   if (!counters) {
     if (cudaMalloc(&counters, kGnMaxImages * sizeof(unsigned int)) != cudaSuccess ||
@@ -374,9 +377,6 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
       return -1;
     }
   }
-  if (NB > kGnMaxImages) { set_error("groupnorm: NB=%d > %d", NB, kGnMaxImages); return -1; }
-  float2* partial = reinterpret_cast<float2*>(workspace);
-  float2* stats = partial + static_cast<size_t>(NB) * kGnMaxChunks * G;
   launch_pdl(gn_stats_kernel, grid, dim3(g.threads), smem, stream, reinterpret_cast<const __nv_bfloat16*>(x0),
              reinterpret_cast<const __nv_bfloat16*>(x1), partial, stats, counters, eps, g);
   if (check_launch("gn_stats_kernel")) return -1;
