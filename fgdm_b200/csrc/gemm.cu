@@ -40,24 +40,29 @@ static constexpr int kStgBytes = 32 * kStgRow + 8 * 128;  // per epilogue warp: 
 // CTAS = 2: a CTA pair (2-cluster, cta_group::2) computes a 256 x BN tile; each CTA stages its own 128 rows of A and
 // HALF of the B tile (BN/2 rows), so per-SM operand traffic (TMA writes + MMA reads) drops by the B half.
 // TMA epilogue (single-CTA kernels narrower than 256 columns: the short-K transformer linears, which are epilogue-paced):
-// every epilogue warp owns three rotating 32x32 bf16 panels (64-byte rows, 64B swizzle = what a TMA box {32, 32} reads
-// and writes). The first residual arrives in a panel by cp.async.bulk.tensor two panels ahead (across tile boundaries),
-// the lane that owns a row adds and packs IN PLACE with conflict-free 16-byte accesses, and the panel leaves by a TMA
-// store: no per-lane global access and no smem transposition in the epilogue; TMA clips / zero-fills the M tail.
+// every epilogue warp owns two residual and two output 32x32 bf16 panels (64-byte rows, 64B swizzle = what a TMA box
+// {32, 32} reads and writes). The first residual arrives by cp.async.bulk.tensor two panels ahead (across tile
+// boundaries); the lane that owns a row reads it, adds, packs and writes its output row with conflict-free 16-byte
+// accesses, and the panel leaves by a TMA store: no per-lane global access and no smem transposition in the epilogue;
+// TMA clips / zero-fills the M tail. These kernels run their own lean tile loop (tma_epilogue below): the generic loop
+// spent 2300 of 6300 clk per 128x160x320 tile BETWEEN panels (tile index divisions, bias re-staging, mode flags;
+// clock64 timeline, profiles/r02_gemm_epilogue_timeline.txt).
 static constexpr int kTmaPanelBytes = 32 * 64;
-static constexpr int kTmaPanels = 3;
+static constexpr int kTmaPanels = 4;                     // per epilogue warp: 2 residual (TMA load) + 2 output (TMA store) panels
 static constexpr int kStgBytesTma = kTmaPanels * kTmaPanelBytes + 8 * 128;
 
-template <int BN, int CTAS = 1>
+template <int BN, int CTAS = 1, bool TE = false>
 struct GemmCfg {
-  static constexpr bool kTmaEpi = CTAS == 1 && BN != 256;
+  static constexpr bool kTmaEpi = TE;                  // instantiated for CTAS == 1 && BN != 256 only
   static constexpr int kStg = kTmaEpi ? kStgBytesTma : kStgBytes;   // staging bytes per epilogue warp
   static constexpr int kStgBias = kTmaEpi ? kTmaPanels * kTmaPanelBytes : 32 * kStgRow;   // offset of the bias / LN panels
   static constexpr int kABytes = kBM * kBK * 2;                // 16 KB
   static constexpr int kBBytes = (BN / CTAS) * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  // single CTA: 64: 6 x 24 KB, 128: 5 x 32, 160: 4 x 36, 224: 3 x 44 (+ 56 KB of TMA panels), 256: 4 x 48 (+ 28 KB)
-  static constexpr int kStages1 = (BN <= 64) ? 6 : (BN <= 128) ? 5 : (BN <= 160) ? 4 : (BN <= 224) ? 3 : 4;
+  // single CTA: 64: 8 x 24 KB, 128: 6 x 32, 160: 5 x 36, 224 / 256: 4 x 44 / 48 (+ 28 KB of staging); the TMA-epilogue
+  // instantiations (72 KB of panels; launched for the short-K lean epilogues only) run 6 / 4 / 4 / 3 stages
+  static constexpr int kStages1 = TE ? ((BN <= 64) ? 6 : (BN <= 128) ? 4 : (BN <= 160) ? 4 : 3)
+                                     : ((BN <= 64) ? 8 : (BN <= 128) ? 6 : (BN <= 160) ? 5 : 4);
   static constexpr int kStages = CTAS == 1 ? kStages1 : 6;     // pair: 6 x (16 + <= 16) KB
   static constexpr int kAccStride = (BN <= 64) ? 64 : (BN <= 128) ? 128 : 256;  // TMEM columns
   static constexpr int kTmemCols = 2 * kAccStride;
@@ -108,12 +113,12 @@ struct WorkIter {
 // the 8 epilogue warps only (barrier 0 is the CTA-wide one used at start-up and tear-down)
 FGDM_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
 
-template <int BN, int CTAS>
+template <int BN, int CTAS, bool TE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
                const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_out,
                const __grid_constant__ CUtensorMap map_res, const __grid_constant__ GemmParams p) {
-  using Cfg = GemmCfg<BN, CTAS>;
+  using Cfg = GemmCfg<BN, CTAS, TE>;
   constexpr int kStages = Cfg::kStages;
   const uint32_t cta_rank = CTAS == 2 ? cluster_ctarank() : 0;   // 0 = leader (issues the pair MMAs)
   extern __shared__ uint8_t smem_raw[];
@@ -129,8 +134,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   uint64_t* acc_empty = bars + 2 * kStages + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   volatile uint32_t* split_flag = tmem_ptr + 1;    // epilogue warps: "this CTA finishes the tile"
-  uint64_t* res_bar = bars + 2 * kStages + 5;      // [kEpiWarps][kTmaPanels] residual panel landed (TMA epilogue)
-  static_assert((2 * kStages + 5 + kEpiWarps * kTmaPanels) * 8 <= 512, "barrier block");
+  uint64_t* res_bar = bars + 2 * kStages + 5;      // [kEpiWarps][2] residual panel landed (TMA epilogue)
+  static_assert((2 * kStages + 5 + kEpiWarps * 2) * 8 <= 512, "barrier block");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -150,7 +155,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     if (Cfg::kTmaEpi) {
       tma_prefetch_desc(&map_out);
       tma_prefetch_desc(&map_res);
-      for (int i = 0; i < kEpiWarps * kTmaPanels; ++i) mbar_init(&res_bar[i], 1);
+      for (int i = 0; i < kEpiWarps * 2; ++i) mbar_init(&res_bar[i], 1);
     }
     fence_barrier_init();
   }
@@ -307,32 +312,126 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     int bias_pf_ntile = -1;
 #pragma unroll
     for (int i = 0; i < kMaxP; ++i) bias_pf[i] = 0.0f;
-    // ---- TMA epilogue state (p.tma_epi: classic tile loop, lean epilogue; see GemmCfg) ----
-    uint32_t tg = 0;                                             // panels this warp has processed: panel buffer = tg % 3
-    uint32_t tl = 0;                                             // panels whose residual load has been issued
-    int pf_tile = blockIdx.x, pf_i = 0;                          // prefetch cursor (tile, panel of this warp)
-    uint64_t* my_res_bar = res_bar + ew * kTmaPanels;
-    auto tma_npv = [&](int tl_) {                                // this warp's panels of tile tl_ that lie inside N
-      const int c0 = (tl_ % p.num_n_tiles) * BN + half * 32;
-      return max(0, min(np, (p.N - c0 + 63) / 64));
-    };
-    // keep the residual of the next two panels in flight (across tile boundaries). Called just before panel tg is written
-    // back: the buffer of panel tg + 2 was last read by the TMA store of panel tg - 1, issued most of a panel ago.
-    auto tma_prefetch_res = [&]() {
-      while (tl < tg + 3 && pf_tile < num_tiles) {
-        if (pf_i >= tma_npv(pf_tile)) { pf_tile += gridDim.x; pf_i = 0; continue; }
+    if (Cfg::kTmaEpi && p.tma_epi) {
+      // ===================== TMA epilogue: its own lean tile loop (classic round-robin tiles only) =====================
+      const uint32_t res_u32 = stg_u32, out_u32 = stg_u32 + 2 * kTmaPanelBytes;
+      uint64_t* my_res_bar = res_bar + ew * 2;
+      const int nn = p.num_n_tiles, stride = gridDim.x;
+      const int sdiv = stride / nn, smod = stride - sdiv * nn;    // tile += stride without a division per tile
+      int tile_c = blockIdx.x, m_t = tile_c / nn, n_t = tile_c - m_t * nn;
+      int pf_tile = tile_c, pf_m = m_t, pf_n = n_t, pf_i = 0;      // residual prefetch cursor: (tile, panel of this warp)
+      uint32_t tg = 0, tl = 0;                                     // panels processed / residual loads issued
+      auto npv_of = [&](int n_tile) { return max(0, min(np, (p.N - (n_tile * BN + half * 32) + 63) / 64)); };
+      auto pf_next_tile = [&]() {
+        pf_i = 0; pf_tile += stride; pf_m += sdiv; pf_n += smod;
+        if (pf_n >= nn) { pf_n -= nn; ++pf_m; }
+      };
+      // residual panel of the next unprocessed-but-one panel -> residual buffer tl & 1 (free: its last reader has synced)
+      auto issue_res_load = [&]() {
+        while (pf_tile < num_tiles && pf_i >= npv_of(pf_n)) pf_next_tile();
+        if (pf_tile >= num_tiles) return;
         if (lane == 0) {
-          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-          const uint32_t b = tl % kTmaPanels;
+          const uint32_t b = tl & 1;
           mbar_expect_tx(&my_res_bar[b], kTmaPanelBytes);
-          tma_load_2d(stg + b * kTmaPanelBytes, &map_res, &my_res_bar[b],
-                      (pf_tile % p.num_n_tiles) * BN + half * 32 + 64 * pf_i, (pf_tile / p.num_n_tiles) * kBM + quarter * 32);
+          tma_load_2d(stg + b * kTmaPanelBytes, &map_res, &my_res_bar[b], pf_n * BN + half * 32 + 64 * pf_i,
+                      pf_m * kBM + quarter * 32);
         }
         ++tl;
         ++pf_i;
+      };
+      const bool has_res = p.res0 != nullptr;
+      if (has_res) { issue_res_load(); issue_res_load(); }
+      const uint32_t row_u32 = lane * 64;                          // this lane's row inside a panel
+      const uint32_t swz = (lane >> 1) & 3;                        // 64B swizzle: chunk c of row r sits at c ^ ((r >> 1) & 3)
+      int bias_ntile = -1;
+      while (tile_c < num_tiles) {
+        const int npv = npv_of(n_t);
+        const int col0 = n_t * BN + half * 32;
+        const int m_warp = m_t * kBM + quarter * 32;
+        if (n_t != bias_ntile) {                                   // bias panels -> smem, only when the column tile changes
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < kMaxP; ++i) {
+            if (i < npv)
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + i * 128 + lane * 4), "f"(__ldg(p.bias + col0 + 64 * i + lane)) : "memory");
+          }
+          bias_ntile = n_t;
+          __syncwarp();
+        }
+        mbar_wait(&acc_full[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
+        float rs_sum = 0.0f, rs_sq = 0.0f;
+#pragma unroll 1
+        for (int i = 0; i < npv; ++i) {
+          const uint32_t b = tg & 1;
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
+          if (has_res) mbar_wait(&my_res_bar[b], (tg >> 1) & 1);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const uint4 u = ld_shared_16(sbias_u32 + i * 128 + j * 4);
+            v[j] = __uint_as_float(r[j]) + __uint_as_float(u.x);
+            v[j + 1] = __uint_as_float(r[j + 1]) + __uint_as_float(u.y);
+            v[j + 2] = __uint_as_float(r[j + 2]) + __uint_as_float(u.z);
+            v[j + 3] = __uint_as_float(r[j + 3]) + __uint_as_float(u.w);
+          }
+          if (has_res) {
+            const uint32_t rp = res_u32 + b * kTmaPanelBytes + row_u32;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint4 u = ld_shared_16(rp + ((q ^ swz) << 4));
+              const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack_bf16x2(w4[e]);
+                v[q * 8 + e * 2] += f.x;
+                v[q * 8 + e * 2 + 1] += f.y;
+              }
+            }
+          }
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+          if (p.row_stats) {         // statistics of the ROUNDED values: exactly what the consuming GEMM multiplies
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float2 f = unpack_bf16x2(pk[j]);
+              rs_sum += f.x + f.y;
+              rs_sq = fmaf(f.x, f.x, fmaf(f.y, f.y, rs_sq));
+            }
+          }
+          // output buffer b was read by the TMA store of panel tg - 2: one younger store may still be pending
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();                                            // + every lane has consumed residual buffer b
+          if (has_res) issue_res_load();                           // panel tg + 2 -> residual buffer b
+          const uint32_t op = out_u32 + b * kTmaPanelBytes + row_u32;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            st_shared_16(op + ((q ^ swz) << 4), make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]));
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                             reinterpret_cast<uint64_t>(&map_out)),
+                         "r"(out_u32 + b * kTmaPanelBytes), "r"(col0 + 64 * i), "r"(m_warp)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          ++tg;
+        }
+        if (p.row_stats && m_warp + lane < p.M)
+          p.row_stats[static_cast<size_t>(m_warp + lane) * (2 * nn) + 2 * n_t + half] = make_float2(rs_sum, rs_sq);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        tile_c += stride; m_t += sdiv; n_t += smod;
+        if (n_t >= nn) { n_t -= nn; ++m_t; }
       }
-    };
-    if (Cfg::kTmaEpi && p.tma_epi && p.res0) tma_prefetch_res();
+    } else
     while (it.next(tile, kc_begin, kc_end)) {
       const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
       const int my_slot = first_seg ? 0 : 1;
@@ -468,8 +567,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
           }
         };
         uint4 rres[4];
-        const bool tma_epi = Cfg::kTmaEpi && p.tma_epi;
-        if (pre_res && !tma_epi) load_res(0, rres);
+        if (pre_res) load_res(0, rres);
         if (p.bias) {
           // bias panels -> smem. The loads for this CTA's NEXT tile are issued here and land while this tile is
           // processed (4 registers): an epilogue-bound GEMM otherwise pays this latency on every tile.
@@ -545,72 +643,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         // are hoisted out of the panel loop and every mode test is gone.
         const bool lean = staged && !partial && p.bias != nullptr && p.rowvec == nullptr && p.alpha == 1.0f &&
                           p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr && (p.N & 31) == 0;
-        if (Cfg::kTmaEpi && p.tma_epi) {
-          const int col0 = n_tile * BN + half * 32;
-          const int npv = tma_npv(tile);
-          const uint32_t row_u32 = lane * 64;                    // this lane's row inside a panel
-          const uint32_t swz = (lane >> 1) & 3;                  // 64B swizzle: 16-byte chunk c of row r sits at c ^ ((r >> 1) & 3)
-#pragma unroll 1
-          for (int i = 0; i < npv; ++i) {
-            const uint32_t buf = tg % kTmaPanels;
-            const uint32_t pan = stg_u32 + buf * kTmaPanelBytes + row_u32;
-            uint32_t r[32];
-            tmem_ld_32x32(taddr + half * 32 + 64 * i, r);
-            if (p.res0) mbar_wait(&my_res_bar[buf], (tg / kTmaPanels) & 1);
-            tmem_ld_wait();
-            float v[32];
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const uint4 u = ld_shared_16(sbias_u32 + i * 128 + j * 4);
-              v[j] = __uint_as_float(r[j]) + __uint_as_float(u.x);
-              v[j + 1] = __uint_as_float(r[j + 1]) + __uint_as_float(u.y);
-              v[j + 2] = __uint_as_float(r[j + 2]) + __uint_as_float(u.z);
-              v[j + 3] = __uint_as_float(r[j + 3]) + __uint_as_float(u.w);
-            }
-            if (p.res0) {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const uint4 u = ld_shared_16(pan + ((q ^ swz) << 4));
-                const uint32_t w4[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const float2 f = unpack_bf16x2(w4[e]);
-                  v[q * 8 + e * 2] += f.x;
-                  v[q * 8 + e * 2 + 1] += f.y;
-                }
-              }
-            } else {
-              // no load ordered this buffer behind its last TMA store (panel tg - 3): do it here
-              if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
-              __syncwarp();
-            }
-            uint32_t pk[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
-            if (p.row_stats) {       // statistics of the ROUNDED values: exactly what the consuming GEMM multiplies
-#pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                const float2 f = unpack_bf16x2(pk[j]);
-                rs_sum += f.x + f.y;
-                rs_sq = fmaf(f.x, f.x, fmaf(f.y, f.y, rs_sq));
-              }
-            }
-            if (p.res0) tma_prefetch_res();
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-              st_shared_16(pan + ((q ^ swz) << 4), make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]));
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) {
-              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
-                               reinterpret_cast<uint64_t>(&map_out)),
-                           "r"(stg_u32 + buf * kTmaPanelBytes), "r"(col0 + 64 * i), "r"(m_warp)
-                           : "memory");
-              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            }
-            ++tg;
-          }
-        } else if (lean) {
+        if (lean) {
           const int col0 = n_tile * BN + half * 32;
           const __nv_bfloat16* rptr[4];
           __nv_bfloat16* optr[4];
@@ -910,13 +943,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
   }
 }
 
-template <int BN, int CTAS>
+template <int BN, int CTAS, bool TE = false>
 static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUtensorMap& mb, const CUtensorMap& mo,
                      const CUtensorMap& mr, const GemmParams& p, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, CTAS>;
+  using Cfg = GemmCfg<BN, CTAS, TE>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CTAS, TE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("gemm: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -940,7 +973,7 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = CTAS == 2 ? 2 : 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS>, ma0, ma1, mb, mo, mr, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS, TE>, ma0, ma1, mb, mo, mr, p);
   if (e != cudaSuccess) { set_error("gemm_tc_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("gemm_tc_kernel");
 }
@@ -1120,7 +1153,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   static int tma_epi_on = -1;
   if (tma_epi_on < 0) { const char* e = getenv("FGDM_TMA_EPI"); tma_epi_on = e ? atoi(e) : 1; }
   __nv_bfloat16* obase = reinterpret_cast<__nv_bfloat16*>(p.out) + p.col_off;
-  p.tma_epi = tma_epi_on && ctas == 1 && BN != 256 && p.range_ctas == 0 && p.out_mode == kOutBf16 && p.bias != nullptr &&
+  p.tma_epi = tma_epi_on && ctas == 1 && BN != 256 && num_k_chunks <= 20 && p.range_ctas == 0 && p.out_mode == kOutBf16 && p.bias != nullptr &&
               p.rowvec == nullptr && p.alpha == 1.0f && p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr &&
               (p.N & 31) == 0 && (reinterpret_cast<uintptr_t>(obase) & 15) == 0 && (p.ldo & 7) == 0 &&
               (p.res0 == nullptr || ((reinterpret_cast<uintptr_t>(p.res0) & 15) == 0 && (p.ld_res0 & 7) == 0));
@@ -1141,6 +1174,15 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
       case 224: return launch_bn<224, 2>(ma0, ma1, mb, mo, mr, p, stream);
       case 256: return launch_bn<256, 2>(ma0, ma1, mb, mo, mr, p, stream);
       default: set_error("gemm: unsupported pair BN=%d", BN); return -1;
+    }
+  }
+  if (p.tma_epi) {
+    switch (BN) {
+      case 64: return launch_bn<64, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
+      case 128: return launch_bn<128, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
+      case 160: return launch_bn<160, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
+      case 224: return launch_bn<224, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
+      default: set_error("gemm: unsupported TMA-epilogue BN=%d", BN); return -1;
     }
   }
   switch (BN) {
