@@ -110,6 +110,13 @@ struct WorkIter {
   }
 };
 
+// tile -> (tile / num_n_tiles, tile % num_n_tiles) by a multiply-high with the launcher's magic constant (exact for
+// tile * num_n_tiles < 2^32; a hardware integer division is ~200 clk of dependent instructions per tile)
+FGDM_DEVINL void split_tile(const GemmParams& p, int tile, int& q, int& r) {
+  q = p.nn_magic ? static_cast<int>(__umulhi(static_cast<uint32_t>(tile), p.nn_magic)) : tile;
+  r = tile - q * p.num_n_tiles;
+}
+
 // the 8 epilogue warps only (barrier 0 is the CTA-wide one used at start-up and tear-down)
 FGDM_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
 
@@ -195,8 +202,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     const uint32_t full0 = smem_u32(&full_bar[0]);
     const uint32_t leader_full0 = CTAS == 2 ? mapa_shared(full0, 0) : full0;
     while (it.next(tile, kc_begin, kc_end)) {
-      const int m_tile = (tile / p.num_n_tiles) * CTAS + cta_rank;
-      const int n_tile = tile % p.num_n_tiles;
+      int tq, n_tile;
+      split_tile(p, tile, tq, n_tile);
+      const int m_tile = tq * CTAS + cta_rank;
       const int m0 = m_tile * kBM;
       const int w0 = m0 % p.W;
       const int hw = m0 / p.W;
@@ -310,6 +318,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     bool first_seg = true;
     float bias_pf[kMaxP];                                        // bias panels of the next tile (prefetched)
     int bias_pf_ntile = -1;
+    int bias_smem_ntile = -1;                                    // column tile whose bias (/ LN-fold) panels sit in smem
+    const bool lean_static = p.out_mode == kOutBf16 && p.bias != nullptr && p.rowvec == nullptr && p.alpha == 1.0f &&
+                             p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr && (p.N & 31) == 0;
 #pragma unroll
     for (int i = 0; i < kMaxP; ++i) bias_pf[i] = 0.0f;
     if (Cfg::kTmaEpi && p.tma_epi) {
@@ -436,8 +447,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
       const int my_slot = first_seg ? 0 : 1;
       first_seg = false;
-      const int m_tile = (tile / p.num_n_tiles) * CTAS + cta_rank;
-      const int n_tile = tile % p.num_n_tiles;
+      int tq, n_tile;
+      split_tile(p, tile, tq, n_tile);
+      const int m_tile = tq * CTAS + cta_rank;
       const int m_warp = m_tile * kBM + quarter * 32;   // first row of this warp
       const int m = m_warp + lane;
       const bool row_ok = m < p.M;
@@ -470,8 +482,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         constexpr int kHalf = BN / 2;
         constexpr int kMaxG = (kHalf / 32 + 1) / 2;              // panel pairs per warp
         const int ng = (kHalf / 32 + 1 - half) / 2;
-        // bias panels (value | gate) -> smem before the accumulator is ready
-        if (p.bias) {
+        // bias panels (value | gate) -> smem before the accumulator is ready (only when the column tile changes)
+        if (p.bias && n_tile != bias_smem_ntile) {
+          bias_smem_ntile = n_tile;
 #pragma unroll
           for (int i = 0; i < kMaxG; ++i) {
             if (i < ng) {
@@ -568,9 +581,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         };
         uint4 rres[4];
         if (pre_res) load_res(0, rres);
-        if (p.bias) {
-          // bias panels -> smem. The loads for this CTA's NEXT tile are issued here and land while this tile is
-          // processed (4 registers): an epilogue-bound GEMM otherwise pays this latency on every tile.
+        if (p.bias && n_tile != bias_smem_ntile) {
+          // bias panels -> smem, only when this CTA's column tile changes (148 SMs: never for 2 or 4 column tiles). The
+          // loads for this CTA's NEXT tile are issued here and land while this tile is processed (4 registers): an
+          // epilogue-bound GEMM otherwise pays this latency on every tile.
+          bias_smem_ntile = n_tile;
           float bv[kMaxP], sv[kMaxP];
           const bool have = bias_pf_ntile == n_tile;
 #pragma unroll
@@ -589,8 +604,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
             }
           }
           const int nxt = it.peek_tile();
-          bias_pf_ntile = nxt < 0 ? -1 : nxt % p.num_n_tiles;
-          if (nxt >= 0) {
+          int nq_, nr_ = -1;
+          if (nxt >= 0) split_tile(p, nxt, nq_, nr_);
+          bias_pf_ntile = nr_;
+          if (nxt >= 0 && nr_ != n_tile) {
 #pragma unroll
             for (int i = 0; i < kMaxP; ++i) {
               const int col = bias_pf_ntile * BN + half * 32 + 64 * i;
@@ -641,8 +658,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         // the short-K transformer linears are paced by the INSTRUCTION COUNT of this loop (ncu: 372 per 32x32 panel in
         // the generic loop, ~220 of them address arithmetic, mode tests and constant loads), so pointers and row masks
         // are hoisted out of the panel loop and every mode test is gone.
-        const bool lean = staged && !partial && p.bias != nullptr && p.rowvec == nullptr && p.alpha == 1.0f &&
-                          p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr && (p.N & 31) == 0;
+        const bool lean = lean_static && !partial;
         if (lean) {
           const int col0 = n_tile * BN + half * 32;
           const __nv_bfloat16* rptr[4];
@@ -1116,6 +1132,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   }
   p.num_m_tiles = (p.M + kBM - 1) / kBM;
   p.num_n_tiles = (p.N + BN - 1) / BN;
+  p.nn_magic = p.num_n_tiles > 1 ? 0xFFFFFFFFu / static_cast<uint32_t>(p.num_n_tiles) + 1u : 0u;
   if (stats_slots_out) {             // dry run: how many row_stats slots per row this launch would write
     *stats_slots_out = 2 * p.num_n_tiles;
     return 0;

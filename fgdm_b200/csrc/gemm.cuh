@@ -26,6 +26,7 @@ struct GemmParams {
   // B operand: weights [N, taps*(C0+C1)] bf16, K index = tap*(C0+C1) + c
   int N;
   int num_m_tiles, num_n_tiles;
+  uint32_t nn_magic;   // floor(2^32 / num_n_tiles) + 1 (0: one column tile): tile / num_n_tiles by __umulhi
   // epilogue: v = alpha * (acc + bias[n] + rowvec[img, n]); v = act(v); v += res0[m, n] + res1[m, n]
   const float* bias;
   const float* rowvec;  // [NB_rowvec, ld_rowvec], row = m / rows_per_img
