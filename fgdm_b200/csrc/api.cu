@@ -46,6 +46,22 @@ int num_sms() {
   return n;
 }
 
+// The library owns process-global scratch (split-K partials and tickets, GroupNorm tickets, the cached SM count): it is
+// bound to the device that is current at first use. One process drives ONE device (one rank per GPU under torchrun)
+// and issues range-mode GEMMs / two-launch GroupNorms on one stream at a time; a second device is refused here rather
+// than handed device-0 pointers. (Concurrent streams cannot be detected cheaply: documented in include/fgdm_b200.h.)
+int owner_device_check(const char* what) {
+  static int owner = -1;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { set_error("%s: cudaGetDevice failed", what); return -1; }
+  if (owner < 0) owner = dev;
+  if (dev != owner) {
+    set_error("%s: libfgdm_b200 scratch is bound to device %d, called on device %d (one device per process)", what, owner, dev);
+    return -1;
+  }
+  return 0;
+}
+
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
   if (!fn) {

@@ -18,6 +18,7 @@ int check_launch(const char* what);
 
 static constexpr int kNumSMsDefault = 148;
 int num_sms();
+int owner_device_check(const char* what);   // api.cu: the library's scratch belongs to ONE device per process
 
 // ----------------------------------------------------------------------------------------------
 // Programmatic dependent launch: a kernel launched through launch_pdl() may start while its predecessor in the

@@ -454,7 +454,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       const int m = m_warp + lane;
       const bool row_ok = m < p.M;
       int img = 0;                                             // image of this row: only some epilogues need the division
-      if (row_ok && (p.rowvec || p.out_mode == kOutQkv || p.out_mode == kOutNchwF32)) img = m / p.rows_per_img;
+      if (row_ok && (p.rowvec || p.out_mode == kOutQkv || p.out_mode == kOutNchwF32))
+        img = p.rpi_shift >= 0 ? (m >> p.rpi_shift) : m / p.rows_per_img;
       const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
       // folded LayerNorm: this row's mean / rstd from the producer GEMM's partial sums (fixed slot order)
       float ln_rstd = 1.0f, ln_rm = 0.0f;                      // rstd and rstd * mean
@@ -658,6 +659,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         // the short-K transformer linears are paced by the INSTRUCTION COUNT of this loop (ncu: 372 per 32x32 panel in
         // the generic loop, ~220 of them address arithmetic, mode tests and constant loads), so pointers and row masks
         // are hoisted out of the panel loop and every mode test is gone.
+        // kOutQkv: (section, head, channel) of the panel's first column: two divisions per TILE, then 64 columns per panel
+        int qsect = 0, qhead = 0, qe = 0;
+        if (p.out_mode == kOutQkv) {
+          const int c0 = n_tile * BN + half * 32;
+          qsect = c0 / p.inner;
+          qhead = (c0 - qsect * p.inner) / p.dhead;
+          qe = c0 - qsect * p.inner - qhead * p.dhead;
+        }
         const bool lean = lean_static && !partial;
         if (lean) {
           const int col0 = n_tile * BN + half * 32;
@@ -735,6 +744,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         } else
 #pragma unroll 1
         for (int i = 0; finish && i < np; ++i) {
+          if (i > 0 && p.out_mode == kOutQkv) {
+            qe += 64;
+            while (qe >= p.dhead) {
+              qe -= p.dhead;
+              if (++qhead == p.heads) { qhead = 0; ++qsect; }
+            }
+          }
           {
             uint32_t r[32];
             const int col = n_tile * BN + half * 32 + 64 * i;
@@ -901,9 +917,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                 const int tok = m - img * p.rows_per_img;
                 // (section, head, channel) of the panel's first column by division, then advanced 8 columns at a time
                 // (dhead % 8 == 0: a group of 8 never straddles a head)
-                int sect = col / p.inner;                       // 0 q, 1 k, 2 v (after qkv_first)
-                int head = (col - sect * p.inner) / p.dhead;
-                int e = col - sect * p.inner - head * p.dhead;
+                int sect = qsect, head = qhead, e = qe;         // of this panel's first column (advanced 64 per panel)
                 sect += p.qkv_first;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
@@ -1048,6 +1062,7 @@ static bool tile_box(int NB, int H, int W, int* bn, int* bh, int* bw) {
 // 4*NB images). w: [N, taps*(C0+C1)] bf16. `bn_hint` selects the N tile (0 = automatic).
 int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, const void* w, int bn_hint,
                 cudaStream_t stream, int* stats_slots_out) {
+  if (owner_device_check("gemm")) return -1;
   if (p.C0 <= 0 || p.C0 % kBK != 0 || p.C1 % kBK != 0) {
     set_error("gemm: channel counts must be positive multiples of 64 (C0=%d C1=%d)", p.C0, p.C1);
     return -1;
@@ -1132,6 +1147,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   }
   p.num_m_tiles = (p.M + kBM - 1) / kBM;
   p.num_n_tiles = (p.N + BN - 1) / BN;
+  p.rpi_shift = (p.rows_per_img > 0 && (p.rows_per_img & (p.rows_per_img - 1)) == 0) ? __builtin_ctz(p.rows_per_img) : -1;
   p.nn_magic = p.num_n_tiles > 1 ? 0xFFFFFFFFu / static_cast<uint32_t>(p.num_n_tiles) + 1u : 0u;
   if (stats_slots_out) {             // dry run: how many row_stats slots per row this launch would write
     *stats_slots_out = 2 * p.num_n_tiles;

@@ -32,6 +32,7 @@ struct GemmParams {
   const float* rowvec;  // [NB_rowvec, ld_rowvec], row = m / rows_per_img
   int ld_rowvec;
   int rows_per_img;     // H*W of the OUTPUT view (tokens per image)
+  int rpi_shift;        // log2(rows_per_img) when it is a power of two (set by the launcher), else -1
   const __nv_bfloat16* res0;
   int ld_res0;
   const __nv_bfloat16* res1;

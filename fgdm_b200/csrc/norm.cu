@@ -355,6 +355,7 @@ static int try_groupnorm_slab(const void* x0, const void* x1, void* y, const flo
 // workspace: at least NB * 129 * G float2 (per-chunk partials, then {mean, rstd} per image and group). x1 may be null (C1 = 0). y: [NB, HW, C0+C1] bf16.
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                      int NB, int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream) {
+  if (owner_device_check("groupnorm")) return -1;
   const int C = C0 + C1;
   if (C0 % 8 || C1 % 8 || C % G || C / 8 > 1024 || G > 64) {
     set_error("groupnorm: unsupported channels C0=%d C1=%d G=%d", C0, C1, G);

@@ -16,6 +16,12 @@
  *    thread-local, NUL-terminated description. No C++ exception crosses this boundary.
  *  - no entry point allocates, synchronises or touches the host: all are CUDA-graph capturable.
  *  - there is NO CPU fallback: without an sm_100a device every compute entry point fails.
+ *  - threading / devices: the library owns process-global scratch (split-K partial sums and tile tickets of
+ *    fgdm_conv_gemm, image tickets of fgdm_groupnorm), allocated on the device that is current at the first call.
+ *    ONE process drives ONE device (one rank per GPU): a call made with another device current fails with an error.
+ *    Calls may be issued from any host thread, but launches that use the scratch (fgdm_conv_gemm in split-K /
+ *    stream-K mode, fgdm_groupnorm's two-launch form) must not run CONCURRENTLY on two streams; stream-ordered use,
+ *    including CUDA-graph replay on one stream, is what the host mirror does.
  */
 #ifndef FGDM_B200_H_
 #define FGDM_B200_H_
