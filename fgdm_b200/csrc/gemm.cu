@@ -545,8 +545,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                 const float x2 = fmaf(__uint_as_float(rx[j + 2]), ln_rstd, bx.z), x3 = fmaf(__uint_as_float(rx[j + 3]), ln_rstd, bx.w);
                 const float g0 = fmaf(__uint_as_float(rg[j]), ln_rstd, bg.x), g1 = fmaf(__uint_as_float(rg[j + 1]), ln_rstd, bg.y);
                 const float g2 = fmaf(__uint_as_float(rg[j + 2]), ln_rstd, bg.z), g3 = fmaf(__uint_as_float(rg[j + 3]), ln_rstd, bg.w);
-                packed[j >> 1] = pack_bf16x2(x0 * gelu_erf_f(g0), x1 * gelu_erf_f(g1));
-                packed[(j >> 1) + 1] = pack_bf16x2(x2 * gelu_erf_f(g2), x3 * gelu_erf_f(g3));
+                packed[j >> 1] = pack_bf16x2(x0 * gelu_f(g0), x1 * gelu_f(g1));
+                packed[(j >> 1) + 1] = pack_bf16x2(x2 * gelu_f(g2), x3 * gelu_f(g3));
               }
 #pragma unroll
               for (int q = 0; q < 4; ++q)
