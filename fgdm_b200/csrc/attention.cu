@@ -813,6 +813,292 @@ static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams
   return check_launch("attention4_kernel");
 }
 
+// =====================================================================================================================
+// xattention_kernel: the text cross-attention (attention.py:189-202 with context = the 77-token CLIP embedding): ONE
+// key/value tile (Nk <= 128) against thousands of query tiles. attention_kernel ran it as one CTA per query tile
+// (4096 CTAs at N = 4096): barrier init, TMEM allocation, a K and a V load and a serial S -> softmax -> PV -> store
+// chain per CTA, ~6 us each, two per SM: 83 us for 84 MB of Q / output traffic (13 us at the HBM rate). Here a CTA
+// keeps K, V (with its all-ones row), the barriers and its TMEM for G consecutive query tiles of one (image, head):
+// Q tiles arrive through a 2-deep TMA ring, S(g+1) is issued while the softmax of tile g runs, and only
+// P -> PV -> normalise -> store stays on the per-tile chain. Softmax as in attention_kernel: two threads per query
+// row (64 key columns each), exact row maximum (no lazy rescale: there is only one tile), denominator from the ones-row.
+// =====================================================================================================================
+template <int KA, int DV>
+struct XAttnCfg {
+  static constexpr int BN = 128;
+  static constexpr int kQBytes = KA * 128 * 128;       // per Q buffer
+  static constexpr int kKBytes = KA * BN * 128;
+  static constexpr int kVAtom = DV * 128;
+  static constexpr int kVBytes = 2 * kVAtom;
+  static constexpr int kPBytes = 2 * 128 * 128;
+  static constexpr int kSmemBytes = 1024 + 2 * kQBytes + kKBytes + kVBytes + kPBytes + 2048 /*row max*/ + 256 /*barriers*/;
+  static constexpr int kThreads = 320;                 // 8 softmax warps, MMA-issue warp, TMA warp
+  static constexpr int kMinBlocks = kSmemBytes <= 110 * 1024 ? 2 : 1;
+  static_assert(BN + DV <= 256, "TMEM budget");
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+};
+
+template <int KA, int DV>
+__global__ void __launch_bounds__(XAttnCfg<KA, DV>::kThreads, XAttnCfg<KA, DV>::kMinBlocks)
+xattention_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
+                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p, int tiles_per_cta) {
+  using Cfg = XAttnCfg<KA, DV>;
+  constexpr int BN = Cfg::BN, HB = BN / 2, HV = DV / 2;
+  static_assert(DV % 16 == 0 && HV % 8 == 0, "DV must be a multiple of 16");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* sQ = smem;                                  // [2]
+  uint8_t* sK = sQ + 2 * Cfg::kQBytes;
+  uint8_t* sV = sK + Cfg::kKBytes;
+  uint8_t* sP = sV + Cfg::kVBytes;
+  float* sMax = reinterpret_cast<float*>(sP + Cfg::kPBytes);             // [2 parities][2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sMax + 512);
+  uint64_t* bar_q = bars;            // [2] Q buffer landed
+  uint64_t* q_empty = bars + 2;      // [2] S(g) has read Q buffer g & 1        (tcgen05.commit)
+  uint64_t* bar_k = bars + 4;
+  uint64_t* bar_v = bars + 5;
+  uint64_t* bar_s = bars + 6;        // S(g) complete                           (tcgen05.commit)
+  uint64_t* bar_o = bars + 7;        // PV(g) complete                          (tcgen05.commit)
+  uint64_t* bar_sfree = bars + 8;    // S(g) is in registers everywhere         (8 warp arrivals)
+  uint64_t* bar_pready = bars + 9;   // P(g) is in smem                         (8 warp arrivals)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int bh = blockIdx.y;
+  const int v0 = blockIdx.z * p.dv_per;                // first V column of this CTA
+  const int nqt = (p.Nq + 127) >> 7;
+  const int tile0 = blockIdx.x * tiles_per_cta;
+  const int G = min(tiles_per_cta, nqt - tile0);       // query tiles of this CTA
+  const int nks = (p.Nk + 15) >> 4;                    // 16-key steps of the PV product
+
+  if (tid == 0) {
+    tma_prefetch_desc(&map_q);
+    tma_prefetch_desc(&map_k);
+    tma_prefetch_desc(&map_vt);
+    for (int i = 0; i < 2; ++i) { mbar_init(&bar_q[i], 1); mbar_init(&q_empty[i], 1); }
+    mbar_init(bar_k, 1);
+    mbar_init(bar_v, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_o, 1);
+    mbar_init(bar_sfree, 8);
+    mbar_init(bar_pready, 8);
+    fence_barrier_init();
+  }
+  if (warp == 9) {
+    tmem_alloc(tmem_ptr, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_launch_dependents();
+
+  if (warp == 9) {
+    // ===================== TMA producer: K and V once, then the Q ring =====================
+    if (lane == 0) {
+      mbar_expect_tx(bar_k, Cfg::kKBytes);
+#pragma unroll
+      for (int a = 0; a < KA; ++a) tma_load_3d(sK + a * (BN * 128), &map_k, bar_k, a * 64, 0, bh);
+      mbar_expect_tx(bar_v, Cfg::kVBytes);
+#pragma unroll
+      for (int a = 0; a < 2; ++a) tma_load_3d(sV + a * Cfg::kVAtom, &map_vt, bar_v, a * 64, v0, bh);
+      for (int g = 0; g < G; ++g) {
+        const int b = g & 1;
+        if (g >= 2) mbar_wait(&q_empty[b], ((g >> 1) - 1) & 1);
+        mbar_expect_tx(&bar_q[b], Cfg::kQBytes);
+#pragma unroll
+        for (int a = 0; a < KA; ++a) tma_load_3d(sQ + b * Cfg::kQBytes + a * 16384, &map_q, &bar_q[b], a * 64, (tile0 + g) * 128, bh);
+      }
+    }
+  } else if (warp == 8) {
+    // ===================== MMA issue warp =====================
+    auto issue_s = [&](int g) {
+      const uint32_t idesc = make_idesc_bf16(128, 16 * nks);      // only the key columns that exist
+      const int b = g & 1;
+#pragma unroll
+      for (int a = 0; a < KA; ++a) {
+        const uint64_t dq = make_desc_sw128(smem_u32(sQ + b * Cfg::kQBytes + a * 16384));
+        const uint64_t dk = make_desc_sw128(smem_u32(sK + a * (BN * 128)));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem_base, dq + 2 * k, dk + 2 * k, idesc, (a | k) != 0 ? 1u : 0u);
+      }
+      tc_commit(bar_s);
+      tc_commit(&q_empty[b]);
+    };
+    // ones-row: V^T row dv_real of both key-atoms := 1.0 (stays for the whole CTA: V is loaded once)
+    mbar_wait(bar_v, 0);
+    if (lane < 16) {
+      const uint32_t a = smem_u32(sV + (lane >> 3) * Cfg::kVAtom) + p.dv_real * 128 + (lane & 7) * 16;
+      st_shared_16(a, make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u));
+    }
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      mbar_wait(bar_k, 0);
+      mbar_wait(&bar_q[0], 0);
+      tc_fence_after();
+      issue_s(0);
+      for (int g = 0; g < G; ++g) {
+        if (g + 1 < G) {
+          mbar_wait(&bar_q[(g + 1) & 1], ((g + 1) >> 1) & 1);
+          mbar_wait(bar_sfree, g & 1);                   // S(g) is in registers: its TMEM columns are free
+          tc_fence_after();
+          issue_s(g + 1);                                // overlaps the softmax of tile g
+        }
+        mbar_wait(bar_pready, g & 1);
+        tc_fence_after();
+        constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
+        for (int ks = 0; ks < nks; ++ks) {               // only the 16-key steps that hold keys (77 keys: 5 of 8)
+          const uint64_t dp = make_desc_sw128(smem_u32(sP + (ks >> 2) * 16384)) + 2 * (ks & 3);
+          const uint64_t dv = make_desc_sw128(smem_u32(sV + (ks >> 2) * Cfg::kVAtom)) + 2 * (ks & 3);
+          tc_mma_bf16(tmem_base + BN, dp, dv, idesc_pv, ks != 0 ? 1u : 0u);
+        }
+        tc_commit(bar_o);
+      }
+    }
+  } else {
+    // ===================== softmax warps: two threads per query row =====================
+    const int half = (warp >> 2) & 1;
+    const int row = (warp & 3) * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t s_addr = tmem_base + lane_addr + half * HB;
+    const uint32_t o_base = tmem_base + BN + lane_addr;
+    const uint32_t o_addr = o_base + half * HV;
+    const int pair_bar = 1 + (warp & 3);
+    const int valid = p.Nk - half * HB;                 // keys valid in this thread's half tile
+    const bool full = valid >= HB;
+    const int valid16 = 16 * nks - half * HB;           // columns of this half that the PV product reads
+    const int img = bh / p.heads;
+    const int head = bh - img * p.heads;
+    const uint32_t sP_row = smem_u32(sP) + row * 128;
+
+    for (int g = 0; g < G; ++g) {
+      mbar_wait(bar_s, g & 1);
+      tc_fence_after();
+      uint32_t s[HB];
+#pragma unroll
+      for (int c = 0; c < HB; c += 32) tmem_ld_32x32(s_addr + c, *reinterpret_cast<uint32_t(*)[32]>(&s[c]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_sfree);
+      float hmax;
+      {
+        // four independent chains (a single accumulator made this the longest phase of the tile: 1250 of 4500 clk)
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (full) {
+#pragma unroll
+          for (int c = 0; c < HB; c += 8) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) mx[u] = fmax3(mx[u], __uint_as_float(s[c + 2 * u]), __uint_as_float(s[c + 2 * u + 1]));
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < HB; c += 8) {
+            if (c >= valid) break;                      // warp-uniform
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int cc = c + 2 * u;
+              mx[u] = fmax3(mx[u], cc < valid ? __uint_as_float(s[cc]) : -INFINITY, cc + 1 < valid ? __uint_as_float(s[cc + 1]) : -INFINITY);
+            }
+          }
+        }
+        hmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      }
+      float* mx_buf = sMax + (g & 1) * 256;
+      mx_buf[half * 128 + row] = hmax;
+      named_bar_sync(pair_bar, 64);                     // the two warps that share these 32 rows
+      const float neg_m = -fmaxf(hmax, mx_buf[(half ^ 1) * 128 + row]) * p.scale_log2;   // exact row maximum: one tile
+      // P(g-1) was read by PV(g-1), which this thread saw complete before it read O(g-1): the P tile is free
+#pragma unroll
+      for (int c = 0; c < HB; c += 8) {
+        if (c >= valid16) break;                        // warp-uniform: no keys in this chunk, and PV does not read it
+        uint32_t pk[4];
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+          float p0 = fast_exp2(fmaf(__uint_as_float(s[c + i]), p.scale_log2, neg_m));
+          float p1 = fast_exp2(fmaf(__uint_as_float(s[c + i + 1]), p.scale_log2, neg_m));
+          if (!full) {
+            if (c + i >= valid) p0 = 0.0f;
+            if (c + i + 1 >= valid) p1 = 0.0f;
+          }
+          pk[i >> 1] = pack_bf16x2(p0, p1);
+        }
+        const int cc = half * HB + c;
+        const int chunk = ((cc & 63) >> 3) ^ (row & 7);
+        st_shared_16(sP_row + (cc >> 6) * 16384 + chunk * 16, make_uint4(pk[0], pk[1], pk[2], pk[3]));
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_pready);
+
+      // ---- normalise and store: out[img, q, head*d + v0 + e]; the denominator is O column dv_real ----
+      mbar_wait(bar_o, g & 1);
+      tc_fence_after();
+      const int q = (tile0 + g) * 128 + row;
+      // one TMEM round trip for the denominator and this thread's HV output columns
+      uint32_t r1, ro[HV];
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r1) : "r"(o_base + p.dv_real) : "memory");
+#pragma unroll
+      for (int c = 0; c < HV; c += 8) tmem_ld_32x8(o_addr + c, *reinterpret_cast<uint32_t(*)[8]>(&ro[c]));
+      tmem_ld_wait();
+      const float inv = fast_rcp(__uint_as_float(r1));   // 1 ulp-class: the result is rounded to bf16
+      __nv_bfloat16* dst = p.out + (static_cast<size_t>(img) * p.Nq + q) * p.ld_out + head * p.d + v0 + half * HV;
+#pragma unroll
+      for (int c = 0; c < HV; c += 8) {
+        const int col = half * HV + c;
+        if (q < p.Nq && col < p.dv_real && v0 + col < p.d) {
+          *reinterpret_cast<uint4*>(dst + c) =
+              make_uint4(pack_bf16x2(__uint_as_float(ro[c]) * inv, __uint_as_float(ro[c + 1]) * inv),
+                         pack_bf16x2(__uint_as_float(ro[c + 2]) * inv, __uint_as_float(ro[c + 3]) * inv),
+                         pack_bf16x2(__uint_as_float(ro[c + 4]) * inv, __uint_as_float(ro[c + 5]) * inv),
+                         pack_bf16x2(__uint_as_float(ro[c + 6]) * inv, __uint_as_float(ro[c + 7]) * inv));
+        }
+      }
+      tc_fence_before();                                // O(g) is read: PV(g+1) follows pready(g+1), which follows this
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256);
+  }
+}
+
+template <int KA, int DV>
+static int launch_xattn(const CUtensorMap& mq, const CUtensorMap& mk, const CUtensorMap& mv, const AttnParams& p, int nsplit,
+                        cudaStream_t stream) {
+  using Cfg = XAttnCfg<KA, DV>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(xattention_kernel<KA, DV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    if (e != cudaSuccess) {
+      set_error("xattention: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
+      return -1;
+    }
+    configured = true;
+  }
+  // query tiles per CTA: the power of two that minimises rounds over the resident slots x (tiles + ~1.5 tiles of set-up)
+  const int nqt = (p.Nq + 127) / 128;
+  const int slots = num_sms() * Cfg::kMinBlocks;
+  int best_g = 1;
+  float best = 1e30f;
+  for (int g = 1; g <= 32; g *= 2) {
+    const long long ctas = static_cast<long long>((nqt + g - 1) / g) * p.BH * nsplit;
+    const float cost = static_cast<float>((ctas + slots - 1) / slots) * (g + 1.5f);
+    if (cost < best) { best = cost; best_g = g; }
+  }
+  dim3 grid((nqt + best_g - 1) / best_g, p.BH, nsplit);
+  cudaError_t e = launch_pdl(xattention_kernel<KA, DV>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p, best_g);
+  if (e != cudaSuccess) { set_error("xattention_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
+  return check_launch("xattention_kernel");
+}
+
 // FGDM_ATTN4=0: never use attention4_kernel (A/B against attention_kernel)
 static int attn4_mode() {
   static int mode = -1;
@@ -868,6 +1154,33 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
     FGDM_ATTN4_CASE(48)
     FGDM_ATTN4_CASE(64)
 #undef FGDM_ATTN4_CASE
+  }
+
+  // one key/value tile against many query tiles (text cross-attention): xattention_kernel
+  static int xattn_on = -1;
+  if (xattn_on < 0) { const char* e = getenv("FGDM_XATTN"); xattn_on = (e && e[0] == '0') ? 0 : 1; }
+  if (xattn_on && !causal && Nk <= 128 && Nq >= 256) {
+    CUtensorMap xq, xk, xv;
+    uint64_t dq_[3] = {static_cast<uint64_t>(d), static_cast<uint64_t>(Nq), static_cast<uint64_t>(p.BH)};
+    uint64_t sq_[2] = {static_cast<uint64_t>(d) * 2, static_cast<uint64_t>(Nq) * d * 2};
+    uint64_t dk_[3] = {static_cast<uint64_t>(d), static_cast<uint64_t>(Nk), static_cast<uint64_t>(p.BH)};
+    uint64_t sk_[2] = {static_cast<uint64_t>(d) * 2, static_cast<uint64_t>(Nk) * d * 2};
+    uint64_t dv_[3] = {static_cast<uint64_t>(Nk), static_cast<uint64_t>(d), static_cast<uint64_t>(p.BH)};
+    uint64_t sv_[2] = {static_cast<uint64_t>(tok_pad) * 2, static_cast<uint64_t>(d) * tok_pad * 2};
+    uint32_t bq_[3] = {64, 128, 1};
+    uint32_t bv_[3] = {64, static_cast<uint32_t>(DV), 1};
+    if (encode_tmap(&xq, q, 3, dq_, sq_, bq_) || encode_tmap(&xk, k, 3, dk_, sk_, bq_) || encode_tmap(&xv, vt, 3, dv_, sv_, bv_))
+      return -1;
+#define FGDM_XATTN_CASE(KA_, DV_) \
+    if (KA == KA_ && DV == DV_) return launch_xattn<KA_, DV_>(xq, xk, xv, p, nsplit, stream);
+    FGDM_XATTN_CASE(1, 16)
+    FGDM_XATTN_CASE(1, 32)
+    FGDM_XATTN_CASE(1, 48)
+    FGDM_XATTN_CASE(1, 64)
+    FGDM_XATTN_CASE(1, 80)
+    FGDM_XATTN_CASE(2, 96)
+    FGDM_XATTN_CASE(3, 96)
+#undef FGDM_XATTN_CASE
   }
 
   CUtensorMap mq, mk, mv;

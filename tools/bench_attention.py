@@ -7,7 +7,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from fgdm_b200 import ops  # noqa: E402
 
-shapes = [(16, 8, 4096, 4096, 40), (16, 8, 1024, 1024, 80), (16, 8, 4096, 77, 40)]
+shapes = [(16, 8, 4096, 4096, 40), (16, 8, 1024, 1024, 80), (16, 8, 4096, 77, 40), (16, 8, 1024, 77, 80), (16, 8, 256, 77, 160),
+          (16, 8, 256, 256, 160)]
 if len(sys.argv) > 1:
     shapes = shapes[:int(sys.argv[1])]
 for images, heads, nq, nk, d in shapes:
