@@ -18,7 +18,7 @@ namespace fgdm {
 
 static constexpr int kGnMaxChunks = 128;
 static constexpr int kGnMaxImages = 4096;
-static constexpr int kGnUnroll = 4;
+static constexpr int kGnUnroll = 4;   // 16-byte loads in flight per thread (8: 34.6 us, 16: 48.2 us vs 33.3 us at 16x4096x320)
 
 struct GnGeom {
   int NB, HW, C0, C1, G;
