@@ -125,6 +125,8 @@ int launch_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos
                         int dim, int vocab, cudaStream_t stream);
 int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                      int NB, int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream);
+int launch_groupnorm_noalloc(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, int NB,
+                             int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream);
 int launch_layernorm(const void* x, void* y, const float* gamma, const float* beta, int rows, int C, float eps,
                      cudaStream_t stream);
 int launch_softmax_rows(const float* s, void* p, int rows, int cols, float scale, cudaStream_t stream);
@@ -320,6 +322,14 @@ int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, 
   if (c1 > 0) FGDM_NONNULL(x1, "x1");
   return launch_groupnorm(x0, x1, y, gamma, beta, workspace, nb, hw, c0, c1, groups, eps, silu,
                           reinterpret_cast<cudaStream_t>(stream));
+}
+
+int fgdm_groupnorm_noalloc(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, int nb,
+                           int hw, int c0, int c1, int groups, float eps, int silu, void* stream) {
+  FGDM_NONNULL(x0, "x0"); FGDM_NONNULL(y, "y"); FGDM_NONNULL(gamma, "gamma"); FGDM_NONNULL(beta, "beta");
+  if (c1 > 0) FGDM_NONNULL(x1, "x1");
+  return launch_groupnorm_noalloc(x0, x1, y, gamma, beta, nb, hw, c0, c1, groups, eps, silu,
+                                  reinterpret_cast<cudaStream_t>(stream));
 }
 
 int fgdm_layernorm(const void* x, void* y, const float* gamma, const float* beta, int rows, int c, float eps,

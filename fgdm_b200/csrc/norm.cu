@@ -388,6 +388,80 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
 }
 
 // ---------------------------------------------------------------------------------------------
+// fgdm_groupnorm_noalloc: the two-launch GroupNorm above for callers that may not allocate (CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// Its scratch (chunk partials, {mean, rstd} per image and group, image tickets) is the file-scope
+// array below: kGnStaticBytes (~2.0 MiB) on every GPU that loads the library, until exit. All calls share it and it
+// keeps the last call's contents: the tickets are cleared on the stream before each use, partials / stats are fully
+// rewritten before they are read. Two calls that OVERLAP on the GPU (different streams, no ordering) race on it.
+// ---------------------------------------------------------------------------------------------
+static constexpr int kGnStaticMaxImages = 256;          // nb  <= 256
+static constexpr int kGnStaticMaxImgGroups = 2048;      // nb * groups <= 2048 (e.g. 64 images x 32 groups)
+static constexpr size_t kGnStaticPartialOff = 0;
+static constexpr size_t kGnStaticStatsOff = static_cast<size_t>(kGnStaticMaxImgGroups) * kGnMaxChunks * sizeof(float2);
+static constexpr size_t kGnStaticTicketOff = kGnStaticStatsOff + static_cast<size_t>(kGnStaticMaxImgGroups) * sizeof(float2);
+static constexpr size_t kGnStaticBytes = kGnStaticTicketOff + kGnStaticMaxImages * sizeof(unsigned int);
+static __device__ __align__(256) unsigned char g_gn_static_scratch[kGnStaticBytes];
+
+static constexpr int kGnStaticMaxDevices = 64;
+static unsigned char* g_gn_static_ptr[kGnStaticMaxDevices] = {};   // device address of the array, per device
+
+// In host code `g_gn_static_scratch` is only a handle: the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current (here: the caller's current device).
+static unsigned char* gn_static_scratch_ptr() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kGnStaticMaxDevices) {
+    set_error("groupnorm_noalloc: cudaGetDevice failed or device index %d >= %d", dev, kGnStaticMaxDevices);
+    return nullptr;
+  }
+  unsigned char* p = __atomic_load_n(&g_gn_static_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p) return p;
+  void* addr = nullptr;
+  const cudaError_t e = cudaGetSymbolAddress(&addr, g_gn_static_scratch);
+  if (e != cudaSuccess || addr == nullptr) {
+    set_error("groupnorm_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    return nullptr;
+  }
+  p = static_cast<unsigned char*>(addr);
+  __atomic_store_n(&g_gn_static_ptr[dev], p, __ATOMIC_RELEASE);   // same value from any thread: a benign double set
+  return p;
+}
+
+int launch_groupnorm_noalloc(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, int NB,
+                             int HW, int C0, int C1, int G, float eps, int silu, cudaStream_t stream) {
+  const int C = C0 + C1;
+  if (NB < 1 || HW < 1 || G < 1 || C0 < 0 || C1 < 0 || C < 8 || C0 % 8 || C1 % 8 || C % G || C / 8 > 1024 || G > 64) {
+    set_error("groupnorm_noalloc: unsupported shape NB=%d HW=%d C0=%d C1=%d G=%d", NB, HW, C0, C1, G);
+    return -1;
+  }
+  if (NB > kGnStaticMaxImages || static_cast<long long>(NB) * G > kGnStaticMaxImgGroups) {
+    set_error("groupnorm_noalloc: NB=%d x G=%d exceeds the static scratch (NB <= %d and NB*G <= %d); "
+              "use fgdm_groupnorm with a caller workspace", NB, G, kGnStaticMaxImages, kGnStaticMaxImgGroups);
+    return -1;
+  }
+  unsigned char* base = gn_static_scratch_ptr();
+  if (!base) return -1;
+  float2* partial = reinterpret_cast<float2*>(base + kGnStaticPartialOff);
+  float2* stats = reinterpret_cast<float2*>(base + kGnStaticStatsOff);
+  unsigned int* tickets = reinterpret_cast<unsigned int*>(base + kGnStaticTicketOff);
+  const GnGeom g = gn_geom(NB, HW, C0, C1, G);
+  const size_t smem = static_cast<size_t>(2) * g.k * C * sizeof(float);
+  const dim3 grid(g.chunks, NB);
+  // the array keeps whatever the last call (possibly an aborted one) left: tickets must start at zero
+  if (cudaMemsetAsync(tickets, 0, static_cast<size_t>(NB) * sizeof(unsigned int), stream) != cudaSuccess) {
+    set_error("groupnorm_noalloc: cudaMemsetAsync(tickets) failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return -1;
+  }
+  launch_pdl(gn_stats_kernel, grid, dim3(g.threads), smem, stream, reinterpret_cast<const __nv_bfloat16*>(x0),
+             reinterpret_cast<const __nv_bfloat16*>(x1), partial, stats, tickets, eps, g);
+  if (check_launch("gn_stats_kernel (noalloc)")) return -1;
+  launch_pdl(gn_apply_kernel, grid, dim3(g.threads), 0, stream, reinterpret_cast<const __nv_bfloat16*>(x0),
+             reinterpret_cast<const __nv_bfloat16*>(x1), static_cast<const float2*>(stats), gamma, beta,
+             reinterpret_cast<__nv_bfloat16*>(y), silu, g);
+  return check_launch("gn_apply_kernel (noalloc)");
+}
+
+// ---------------------------------------------------------------------------------------------
 // LayerNorm over the channel dim of [rows, C] bf16 tokens: one warp per token, row kept in registers.
 // ---------------------------------------------------------------------------------------------
 template <int MAXV>

@@ -132,6 +132,17 @@ int fgdm_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_e
 int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                    int nb, int hw, int c0, int c1, int groups, float eps, int silu, void* stream);
 
+/* fgdm_groupnorm without any allocation and without a caller workspace. NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops,
+ * harnesses that forbid it). Same arguments and result as fgdm_groupnorm (always its two-launch form); the scratch
+ * (chunk partials, {mean, rstd}, image tickets) is a static __device__ array inside the library, ~2.0 MiB on every
+ * GPU that loads it, until exit. Limits: nb <= 256 and nb * groups <= 2048 (e.g. 64 images x 32 groups); larger
+ * calls return -1 with a message in fgdm_last_error(). Calls cudaGetSymbolAddress once per device and
+ * cudaMemsetAsync (tickets) per call; no cudaMalloc / cudaFree. All calls share the one array, which keeps the last
+ * call's contents: calls that OVERLAP on the GPU (two streams without ordering) race; stream-ordered calls are safe. */
+int fgdm_groupnorm_noalloc(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, int nb,
+                           int hw, int c0, int c1, int groups, float eps, int silu, void* stream);
+
 /* nn.LayerNorm over channels of [rows, c] tokens: attention.py:226-228. */
 int fgdm_layernorm(const void* x, void* y, const float* gamma, const float* beta, int rows, int c, float eps,
                    void* stream);
