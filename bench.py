@@ -201,8 +201,10 @@ def kernel_rooflines(pipe, dev_in, pk, S):
     unet, cn = img.model.diffusion_model, img.control_model
     kv_s = seg.model.diffusion_model.project_context(ctx)
     kv_u, kv_c, gh = unet.project_context(ctx), cn.project_context(ctx), cn.encode_hint(hint)
-    parts = {"seg_step": lambda: seg.model.diffusion_model.forward(dev_in["xT_seg"], t, kv=kv_s, rows=2 * B),
-             "img_step": lambda: img.control_step(dev_in["xT_img"], t, kv_u, kv_c, gh, 2 * B),
+    from fgdm_b200.ddim import SHARE_CFG_HEAD as share      # the same calls the captured sampler step makes (ddim._eps)
+    parts = {"seg_step": lambda: seg.model.diffusion_model.forward(dev_in["xT_seg"], t, kv=kv_s, rows=2 * B,
+                                                                   shared_halves=share),
+             "img_step": lambda: img.control_step(dev_in["xT_img"], t, kv_u, kv_c, gh, 2 * B, shared_halves=share),
              "decode": lambda: seg.decode_first_stage(dev_in["xT_seg"] * 0.18215)}
     weight = {"seg_step": S, "img_step": S, "decode": 2}
     profs = {}
@@ -271,7 +273,8 @@ def kernel_rooflines(pipe, dev_in, pk, S):
         for k, sh in prof.items():
             for sk, v in sh.items():
                 flat[(part, k, sk)] = v
-    return roof, tables, flat
+    executed = sum(v["flops"] for v in fam.values())      # chain-weighted flops of the kernels actually launched
+    return roof, tables, flat, executed
 
 
 def run_ours(args, rank, world, local_rank):
@@ -450,7 +453,7 @@ def run_ours(args, rank, world, local_rank):
               "vae_decode_ms": ms_of(lambda: seg.decode_first_stage(dev_in["xT_seg"] * 0.18215), 3),
               "rows_per_step": 2 * B, "kernels_per_seg_step": gs.launches_per_step,
               "kernels_per_img_step": gi.launches_per_step}
-    roof, tables, flat = kernel_rooflines(pipe, dev_in, pk, S)
+    roof, tables, flat, executed_flops = kernel_rooflines(pipe, dev_in, pk, S)
     if args.dump_shapes:
         rows = [{"part": part, "kernel": k, "shape": sk, "launches": v[0], "ms": v[1], "flops": v[2], "bytes": v[3]}
                 for (part, k, sk), v in flat.items()]
@@ -471,9 +474,13 @@ def run_ours(args, rank, world, local_rank):
                     "gathered_checksum_rank0": gathered_sum},
             "gpu_launches": launches,
             "roofline": roof,
+            # algorithmic = the reference's work (every CFG row through the whole network); executed = what the launched
+            # kernels did (the context-free encoder head runs once per latent, ddim.SHARE_CFG_HEAD)
             "roofline_step": {"algorithmic_tflop_per_image": flop_img / 1e12, "achieved_tflops_per_gpu": step_tf,
                               "frac_of_bf16_sustained": step_tf / pk["tf_sust"],
-                              "frac_of_nominal_dense_bf16": step_tf / NOMINAL_BF16_TFLOPS},
+                              "frac_of_nominal_dense_bf16": step_tf / NOMINAL_BF16_TFLOPS,
+                              "executed_tflop_per_image": executed_flops / B / 1e12,
+                              "executed_tflops_per_gpu": executed_flops / (ms / args.steps * 1e-3) / 1e12},
             "phases": phases, "kernels": tables["chain_weighted"], "kernels_unet_steps": tables["unet_steps"],
             "kernels_vae_decode": tables["vae_decode"], "c3_strong": c3}
     if keep_sd:

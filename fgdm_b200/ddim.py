@@ -57,6 +57,10 @@ def uncond_hint_matches(cond, uncond, hint_c, hint_u):
     return hint_u is hint_c or (hint_u.shape == hint_c.shape and torch.equal(hint_u, hint_c))
 
 
+# FGDM_SHARE_CFG_HEAD=0: evaluate every CFG row through the whole encoder, like the reference (A/B switch)
+SHARE_CFG_HEAD = os.environ.get("FGDM_SHARE_CFG_HEAD", "1") != "0"
+
+
 class _StepGraph:
     """One captured DDIM step for fixed (model, B, latent shape, context length, CFG on/off)."""
 
@@ -116,9 +120,13 @@ class _StepGraph:
     def _eps(self):
         """The model call of one step on the static buffers: eps for the R CFG rows of (self.x, self.t)."""
         m = self.model
+        # CFG rows r and r + B read the same latent self.x[r], the same timestep (self.t is filled with ONE value per
+        # step) and the same hint: the networks evaluate the context-free head of the encoder once (nets._encode)
+        share = self.cfg and SHARE_CFG_HEAD
         if self.is_control:
-            return m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R)
-        return m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R, adapter_features=self.fa)
+            return m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R, shared_halves=share)
+        return m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R, adapter_features=self.fa,
+                                               shared_halves=share)
 
     def _step(self):
         ops.ddim_advance(self.counter, self.t_table, self.idx_table, self.t, self.index)

@@ -352,6 +352,11 @@ class BasicTransformerBlock(Layer):
         return self.ff.forward(t, stats)
 
 
+def repeat_rows(a, copies):
+    """[n, ...] -> [copies * n, ...] with row r = a[r % n] (one copy kernel; torch.cat([x] * 2) of ddim.py:222)."""
+    return torch.cat([a] * copies, 0)
+
+
 class SpatialTransformer(Layer):
     def __init__(self, ch, heads, d_head, context_dim):
         super().__init__()
@@ -374,6 +379,22 @@ class SpatialTransformer(Layer):
         t, stats = self.proj_in.gemm(xn, want_stats=True) if blk.wants_stats else (self.proj_in.gemm(xn), None)
         t = blk.forward(t.view(nb * h * w, -1), stats, nb, h * w, kvs[self.kv_slot])
         return self.proj_out.gemm(t.view(nb, h, w, -1), res0=x, res1=res1)
+
+    def forward_shared(self, x, kvs, copies=2):
+        """forward() for `copies` x nb output rows whose inputs x are IDENTICAL across the copies (the uncond / cond CFG
+        halves of one latent, ddim.py:222-226) and differ only in their text context: GroupNorm, proj_in, LayerNorm, the
+        q/k/v projection, the self-attention and its output projection see no context (attention.py:234-236), so they
+        run once on the nb unique rows; the rows are repeated in front of the cross-attention (attention.py:237)."""
+        nb, h, w, c = x.shape
+        xn = ops.groupnorm(x, self.norm.g, self.norm.b, eps=1e-6, silu=False)
+        blk = self.blocks[0]
+        t, stats = self.proj_in.gemm(xn, want_stats=True) if blk.wants_stats else (self.proj_in.gemm(xn), None)
+        t, stats = blk.attn1.forward(t.view(nb * h * w, -1), stats, nb, h * w, want_stats=blk.attn2.ln_fold)
+        t = repeat_rows(t, copies)
+        stats = None if stats is None else repeat_rows(stats, copies)
+        t, stats = blk.attn2.forward(t, stats, copies * nb, h * w, kvs[self.kv_slot], want_stats=blk.ff.net[0].ln_fold)
+        t = blk.ff.forward(t, stats)
+        return self.proj_out.gemm(t.view(copies * nb, h, w, -1), res0=repeat_rows(x, copies))
 
 
 class Downsample(Layer):

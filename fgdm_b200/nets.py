@@ -17,7 +17,8 @@ import torch
 
 from . import _lib, ops
 from .layers import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, OUT_F32, OUT_QKV, Conv2d, Downsample, Layer,
-                     Linear, Norm, ResBlock, Seq, SpatialTransformer, TimeEmbed, Upsample, batch_emb_layers, bf16)
+                     Linear, Norm, ResBlock, Seq, SpatialTransformer, TimeEmbed, Upsample, batch_emb_layers, bf16,
+                     repeat_rows)
 
 
 def _unsupported(**flags):
@@ -249,13 +250,36 @@ class _UNetBase(_Net):
             self.trace.append(h)
         return h
 
-    def _encode(self, x, rows, emb_all, kvs, fa=None, after_conv_in=None):
-        h = self.input_blocks[0][0].from_nchw(x, rows)
-        if after_conv_in is not None:
-            h = after_conv_in(h)
-        hs = [h]
+    def _shareable(self, x, rows):
+        """Can the CFG halves share the context-free head of the encoder? rows == 2 * unique latents, input block 1 is
+        [ResBlock, SpatialTransformer], and no block trace is being recorded."""
+        if rows != 2 * x.shape[0] or self.trace is not None or len(self.input_blocks.children) < 2:
+            return False
+        kinds = [type(c) for c in self.input_blocks[1].children.values()]
+        return kinds == [ResBlock, SpatialTransformer]
+
+    def _encode(self, x, rows, emb_all, kvs, fa=None, after_conv_in=None, shared_halves=False):
+        """shared_halves: the caller guarantees that rows r and r + rows/2 have the same latent x[r % nb_in] AND the
+        same timestep (the sampler's CFG batch, ddim.py:222-226: x_in = cat([x] * 2), t_in = cat([t] * 2)). Until the
+        first cross-attention nothing depends on the text context, so conv_in, the first ResBlock and the first
+        transformer's GroupNorm / proj_in / self-attention are evaluated once per unique latent and repeated."""
+        start = 1
+        if shared_halves and self._shareable(x, rows):
+            nb = x.shape[0]
+            h0 = self.input_blocks[0][0].from_nchw(x, nb)
+            if after_conv_in is not None:
+                h0 = after_conv_in(h0)
+            res, st = self.input_blocks[1].children.values()
+            h = st.forward_shared(res.forward(h0, None, emb_all[:nb]), kvs, copies=2)
+            hs = [repeat_rows(h0, 2), h]
+            start = 2
+        else:
+            h = self.input_blocks[0][0].from_nchw(x, rows)
+            if after_conv_in is not None:
+                h = after_conv_in(h)
+            hs = [h]
         k = 0
-        for idx in range(1, len(self.input_blocks.children)):
+        for idx in range(start, len(self.input_blocks.children)):
             r1 = None
             if fa is not None and (idx + 1) % 3 == 0:
                 r1 = fa[k]
@@ -307,7 +331,7 @@ class UNetModel(_UNetBase):
         return self.adapter.forward(pc, pc.shape[0])
 
     def forward(self, x, timesteps=None, context=None, y=None, pcond=None, kv=None, rows=None, adapter_features=None,
-                **kwargs):
+                shared_halves=False, **kwargs):
         """x: fp32 [nb_in, 4, h, w]; rows >= nb_in output rows (row r reads x[r % nb_in] — lets the sampler
         feed ONE copy of x for the cond and uncond halves instead of the reference's torch.cat([x]*2),
         ddim.py:222). timesteps: int64 [rows]; context [rows, L, 768] or kv = project_context(context).
@@ -327,7 +351,7 @@ class UNetModel(_UNetBase):
             fa = self.encode_prompt(pcond) if pcond is not None else self.adapter.forward(x, x.shape[0])
         else:
             fa = None
-        h, hs = self._encode(x, rows, emb_all, kvs, fa)
+        h, hs = self._encode(x, rows, emb_all, kvs, fa, shared_halves=shared_halves)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
         return self._decode(h, hs, emb_all, kvs)
 
@@ -379,7 +403,7 @@ class ControlNet(_UNetBase):
         return self.input_hint_block.forward(hint)
 
     def forward(self, x, hint=None, timesteps=None, context=None, kv=None, rows=None, guided_hint=None,
-                scales=None, add_to=None, only_mid=False, **kwargs):
+                scales=None, add_to=None, only_mid=False, shared_halves=False, **kwargs):
         """Returns the 13 tensors `zero_conv(h) * scale` (cldm.py:801-811, scaling of :846 folded into the
         epilogue). With add_to = [hs..., h_mid] of the UNet encoder, returns `add_to[k] + scale*control[k]`
         instead (the adds of cldm.py:39-47 ride the same epilogue). Outputs are NHWC bf16."""
@@ -392,11 +416,13 @@ class ControlNet(_UNetBase):
         gb = guided_hint.shape[0]
 
         def add_hint(h):                                          # h += guided_hint, cldm.py:803-805
-            for r0 in range(0, rows, gb):
+            for r0 in range(0, h.shape[0], gb):
                 ops.add_bf16(h[r0:r0 + gb], guided_hint, out=h[r0:r0 + gb])
             return h
 
-        h, hs = self._encode(x, rows, emb_all, kvs, None, after_conv_in=add_hint)
+        # the halves may only share the encoder head if they also share the hint (guided_hint rows repeat modulo gb)
+        share = shared_halves and (rows // 2) % gb == 0
+        h, hs = self._encode(x, rows, emb_all, kvs, None, after_conv_in=add_hint, shared_halves=share)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
         scales = scales or [1.0] * (len(hs) + 1)
         outs = []
@@ -426,12 +452,12 @@ class ControlledUnetModel(_UNetBase):
         self._build(in_channels, model_channels, out_channels, num_res_blocks, list(attention_resolutions),
                     list(channel_mult), num_heads, context_dim)
 
-    def encode(self, x, timesteps, context=None, kv=None, rows=None):
+    def encode(self, x, timesteps, context=None, kv=None, rows=None, shared_halves=False):
         x = x.float().contiguous()
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
         emb_all = self._emb(timesteps)
-        h, hs = self._encode(x, rows, emb_all, kvs)
+        h, hs = self._encode(x, rows, emb_all, kvs, shared_halves=shared_halves)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
         return h, hs, emb_all, kvs
 

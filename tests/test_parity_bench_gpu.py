@@ -116,6 +116,42 @@ def test_control_step_R16_vs_oracle(control):
     assert relmax(eps, ref) < EPS_TOL
 
 
+def test_shared_cfg_head_matches_full_evaluation(fgdm, control):
+    """The sampler's CFG step evaluates the context-free encoder head (conv_in, first ResBlock, first self-attention)
+    once per latent (nets._encode, shared_halves=True). Against the same step with every row evaluated (what
+    apply_model on torch.cat([x] * 2) does) and against the oracle at the bench's R = 16."""
+    import fgdm_oracle as orc
+    B = 8
+    x, t, ctx = _cfg_rows(B, 900)
+    model, sd = fgdm
+    unet = model.model.diffusion_model
+    kv = unet.project_context(ctx)
+    full = unet.forward(x, t, kv=kv, rows=2 * B)
+    shared = unet.forward(x, t, kv=kv, rows=2 * B, shared_halves=True)
+    x2 = torch.cat([x, x])
+    ref = torch.cat([orc.unet_forward(sd, x2[i:i + 2], t[i:i + 2], ctx[i:i + 2], prefix="model.diffusion_model.")
+                     for i in range(0, 2 * B, 2)])
+    print("unet shared head: vs full", relmax(shared, full), "vs oracle", relmax(shared, ref), "(full vs oracle",
+          relmax(full, ref), ")")
+    # two bf16 evaluations with different tile shapes (M halves in the shared head) sit as far from each other as
+    # each sits from the fp32 oracle: the bar is the eps tolerance for both
+    assert relmax(shared, full) < EPS_TOL
+    assert relmax(shared, ref) < EPS_TOL
+    # ControlLDM: ControlNet and the controlled UNet both share their heads; the hint is shared too
+    model, sd = control
+    hint = gc._hint(B, 512, 77).to(DEV)
+    unet, cn = model.model.diffusion_model, model.control_model
+    args = (x, t, unet.project_context(ctx), cn.project_context(ctx), cn.encode_hint(hint), 2 * B)
+    full = model.control_step(*args)
+    shared = model.control_step(*args, shared_halves=True)
+    h2 = torch.cat([hint, hint])
+    ref = torch.cat([orc.control_ldm_apply(sd, x2[i:i + 2], t[i:i + 2], h2[i:i + 2], ctx[i:i + 2])
+                     for i in range(0, 2 * B, 2)])
+    print("control shared head: vs full", relmax(shared, full), "vs oracle", relmax(shared, ref))
+    assert relmax(shared, full) < EPS_TOL
+    assert relmax(shared, ref) < EPS_TOL
+
+
 def test_batch_invariance_B8_vs_B1(fgdm, control):
     """Prompts 0..7 in one B=8 chain (the bench's step) against eight B=1 chains with the same per-prompt x_T:
     PSNR >= 35 dB per image (tile widths / split-K change with M, so bit equality is reported, not required)."""
