@@ -201,10 +201,17 @@ def kernel_rooflines(pipe, dev_in, pk, S):
     unet, cn = img.model.diffusion_model, img.control_model
     kv_s = seg.model.diffusion_model.project_context(ctx)
     kv_u, kv_c, gh = unet.project_context(ctx), cn.project_context(ctx), cn.encode_hint(hint)
-    from fgdm_b200.ddim import SHARE_CFG_HEAD as share      # the same calls the captured sampler step makes (ddim._eps)
+    # the same calls the captured sampler step makes (ddim._StepGraph._eps): shared CFG head, time-embedding vectors
+    # from the per-schedule table
+    from fgdm_b200.ddim import EMB_TABLES, SHARE_CFG_HEAD as share
+    es = eu = ec = None
+    if EMB_TABLES:
+        es = seg.model.diffusion_model.emb_table(t[:1]).expand(2 * B, -1)
+        eu, ec = unet.emb_table(t[:1]).expand(2 * B, -1), cn.emb_table(t[:1]).expand(2 * B, -1)
     parts = {"seg_step": lambda: seg.model.diffusion_model.forward(dev_in["xT_seg"], t, kv=kv_s, rows=2 * B,
-                                                                   shared_halves=share),
-             "img_step": lambda: img.control_step(dev_in["xT_img"], t, kv_u, kv_c, gh, 2 * B, shared_halves=share),
+                                                                   shared_halves=share, emb_all=es),
+             "img_step": lambda: img.control_step(dev_in["xT_img"], t, kv_u, kv_c, gh, 2 * B, shared_halves=share,
+                                                  emb_unet=eu, emb_ctrl=ec),
              "decode": lambda: seg.decode_first_stage(dev_in["xT_seg"] * 0.18215)}
     weight = {"seg_step": S, "img_step": S, "decode": 2}
     profs = {}

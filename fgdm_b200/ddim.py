@@ -57,6 +57,10 @@ def uncond_hint_matches(cond, uncond, hint_c, hint_u):
     return hint_u is hint_c or (hint_u.shape == hint_c.shape and torch.equal(hint_u, hint_c))
 
 
+# FGDM_EMB_TABLE=0: time_embed + emb_layers run inside every step (default: once per schedule, before the loop)
+EMB_TABLES = os.environ.get("FGDM_EMB_TABLE", "1") != "0"
+EMB_TABLE_STEPS = 256
+
 # FGDM_SHARE_CFG_HEAD=0: evaluate every CFG row through the whole encoder, like the reference (A/B switch)
 SHARE_CFG_HEAD = os.environ.get("FGDM_SHARE_CFG_HEAD", "1") != "0"
 
@@ -92,6 +96,12 @@ class _StepGraph:
         self.fa = None
         if pcond_rows:
             self.fa = unet.encode_prompt(torch.zeros((pcond_rows, C, H, W), device=dev, dtype=torch.float32))
+        # time-embedding vectors of a whole schedule, one row per DDIM index (filled by run(); the captured step picks
+        # row `index` on the device), for schedules of up to EMB_TABLE_STEPS steps
+        self.emb_unet = torch.zeros((EMB_TABLE_STEPS, unet.w_emb.shape[0]), device=dev, dtype=torch.float32)
+        self.emb_ctrl = (torch.zeros((EMB_TABLE_STEPS, model.control_model.w_emb.shape[0]), device=dev,
+                                     dtype=torch.float32) if self.is_control else None)
+        self.use_emb_table = False
         self.graph = None
         self.launches_per_step = 0
 
@@ -117,20 +127,25 @@ class _StepGraph:
             self._refill(self.kv_ctrl, self.model.control_model.project_context(self.ctx))
             self.guided.copy_(self.model.control_model.encode_hint(hint))
 
-    def _eps(self):
+    def _eps(self, emb_table=False):
         """The model call of one step on the static buffers: eps for the R CFG rows of (self.x, self.t)."""
         m = self.model
         # CFG rows r and r + B read the same latent self.x[r], the same timestep (self.t is filled with ONE value per
         # step) and the same hint: the networks evaluate the context-free head of the encoder once (nets._encode)
         share = self.cfg and SHARE_CFG_HEAD
+        eu = ec = None
+        if emb_table:        # row `index` of the precomputed tables, broadcast to the R rows (stride-0 view)
+            eu = torch.index_select(self.emb_unet, 0, self.index).expand(self.R, -1)
+            ec = torch.index_select(self.emb_ctrl, 0, self.index).expand(self.R, -1) if self.is_control else None
         if self.is_control:
-            return m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R, shared_halves=share)
+            return m.control_step(self.x, self.t, self.kv_unet, self.kv_ctrl, self.guided, self.R, shared_halves=share,
+                                  emb_unet=eu, emb_ctrl=ec)
         return m.model.diffusion_model.forward(self.x, self.t, kv=self.kv_unet, rows=self.R, adapter_features=self.fa,
-                                               shared_halves=share)
+                                               shared_halves=share, emb_all=eu)
 
     def _step(self):
         ops.ddim_advance(self.counter, self.t_table, self.idx_table, self.t, self.index)
-        eps = self._eps()
+        eps = self._eps(self.use_emb_table)
         e_u = eps[:self.B]
         e_c = eps[self.B:] if self.cfg else None
         ops.cfg_ddim_step(e_u, e_c, self.x, self.coef, 0, self.scale, index_ptr=self.index, x_prev=self.x,
@@ -156,8 +171,9 @@ class _StepGraph:
         ops.count_launches(self.eps_launches)
         return self.eps_out[:self.B], (self.eps_out[self.B:] if self.cfg else None)
 
-    def capture(self, scale):
+    def capture(self, scale, use_emb_table=False):
         self.scale = float(scale)
+        self.use_emb_table = use_emb_table
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -174,9 +190,15 @@ class _StepGraph:
     def run(self, x_T, ts, coef, scale):
         """ts: int64 numpy [S] in visiting order; coef: fp32 [S,5] rows indexed by `index`."""
         S = len(ts)
-        if self.graph is None or scale != self.scale:
-            self.capture(scale)
+        table = EMB_TABLES and S <= EMB_TABLE_STEPS
+        if self.graph is None or scale != self.scale or table != self.use_emb_table:
+            self.capture(scale, table)
         dev = self.x.device
+        if table:            # index S-1-i belongs to the i-th visited timestep: rows in ascending DDIM index
+            t_by_index = torch.as_tensor(np.ascontiguousarray(ts[::-1]), dtype=torch.int64).to(dev)
+            self.emb_unet[:S].copy_(self.model.model.diffusion_model.emb_table(t_by_index))
+            if self.is_control:
+                self.emb_ctrl[:S].copy_(self.model.control_model.emb_table(t_by_index))
         self.t_table[:S].copy_(torch.as_tensor(np.ascontiguousarray(ts), dtype=torch.int64), non_blocking=True)
         self.idx_table[:S].copy_(torch.arange(S - 1, -1, -1, dtype=torch.int32), non_blocking=True)
         self.coef[:S].copy_(coef, non_blocking=True)

@@ -315,17 +315,19 @@ class ControlLDM(LatentDiffusion):
                                         self.control_model.encode_hint(hint), x_noisy.shape[0])
         return eps.to(x_noisy.dtype)
 
-    def control_step(self, x, t, kv_unet, kv_ctrl, guided_hint, rows, shared_halves=False):
+    def control_step(self, x, t, kv_unet, kv_ctrl, guided_hint, rows, shared_halves=False, emb_unet=None,
+                     emb_ctrl=None):
         """One ControlNet + controlled-UNet evaluation on `rows` rows (x may hold rows/2 images). shared_halves: rows r
         and r + rows/2 share latent, timestep and hint (the sampler's CFG batch), see _UNetBase._encode."""
         unet, cn = self.model.diffusion_model, self.control_model
-        h, hs, emb_all, kvs = unet.encode(x, t, kv=kv_unet, rows=rows, shared_halves=shared_halves)
+        h, hs, emb_all, kvs = unet.encode(x, t, kv=kv_unet, rows=rows, shared_halves=shared_halves, emb_all=emb_unet)
         n = len(hs)
         if self.only_mid_control:
             ctrl = cn.forward(x, timesteps=t, kv=kv_ctrl, rows=rows, guided_hint=guided_hint,
                               scales=self.control_scales, add_to=[None] * n + [h], only_mid=True,
-                              shared_halves=shared_halves)
+                              shared_halves=shared_halves, emb_all=emb_ctrl)
             return unet.decode(ctrl[-1], hs, emb_all, kvs)
         ctrl = cn.forward(x, timesteps=t, kv=kv_ctrl, rows=rows, guided_hint=guided_hint,
-                          scales=self.control_scales, add_to=hs + [h], shared_halves=shared_halves)
+                          scales=self.control_scales, add_to=hs + [h], shared_halves=shared_halves,
+                          emb_all=emb_ctrl)
         return unet.decode(ctrl[-1], ctrl[:-1], emb_all, kvs)

@@ -226,6 +226,12 @@ class _UNetBase(_Net):
         ctx = context.to(bf16).contiguous()
         return [s.project_context(ctx) for s in self._sts]
 
+    def emb_table(self, timesteps):
+        """[S] timesteps -> [S, total] fp32: every ResBlock's emb_layers(time_embed(timestep_embedding(t))) for a whole
+        sampling schedule at once (openaimodel.py:538-542,238-244 depend on t only, so the sampler evaluates them
+        before the loop instead of once per step). Row-wise identical to _emb on the same timestep."""
+        return self._emb(timesteps)
+
     def _emb(self, timesteps):
         # int64 steps (DDIM/PLMS) or DPM-Solver's fractional float32 timesteps (util.py:160-180 takes either)
         ts = timesteps.to(torch.float32 if timesteps.is_floating_point() else torch.int64).contiguous()
@@ -331,7 +337,7 @@ class UNetModel(_UNetBase):
         return self.adapter.forward(pc, pc.shape[0])
 
     def forward(self, x, timesteps=None, context=None, y=None, pcond=None, kv=None, rows=None, adapter_features=None,
-                shared_halves=False, **kwargs):
+                shared_halves=False, emb_all=None, **kwargs):
         """x: fp32 [nb_in, 4, h, w]; rows >= nb_in output rows (row r reads x[r % nb_in] — lets the sampler
         feed ONE copy of x for the cond and uncond halves instead of the reference's torch.cat([x]*2),
         ddim.py:222). timesteps: int64 [rows]; context [rows, L, 768] or kv = project_context(context).
@@ -342,7 +348,8 @@ class UNetModel(_UNetBase):
         x = x.float().contiguous()
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
-        emb_all = self._emb(timesteps)
+        if emb_all is None:             # else: the per-ResBlock time-embedding vectors of these timesteps, precomputed
+            emb_all = self._emb(timesteps)
         # prompt = h (:836-844): the adapter sees only the latent, so its features are identical for the cond and
         # uncond CFG rows -> computed once per unique latent, added modulo by the GEMM epilogue (res1_rows)
         if adapter_features is not None:
@@ -403,14 +410,15 @@ class ControlNet(_UNetBase):
         return self.input_hint_block.forward(hint)
 
     def forward(self, x, hint=None, timesteps=None, context=None, kv=None, rows=None, guided_hint=None,
-                scales=None, add_to=None, only_mid=False, shared_halves=False, **kwargs):
+                scales=None, add_to=None, only_mid=False, shared_halves=False, emb_all=None, **kwargs):
         """Returns the 13 tensors `zero_conv(h) * scale` (cldm.py:801-811, scaling of :846 folded into the
         epilogue). With add_to = [hs..., h_mid] of the UNet encoder, returns `add_to[k] + scale*control[k]`
         instead (the adds of cldm.py:39-47 ride the same epilogue). Outputs are NHWC bf16."""
         x = x.float().contiguous()
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
-        emb_all = self._emb(timesteps)
+        if emb_all is None:
+            emb_all = self._emb(timesteps)
         if guided_hint is None:
             guided_hint = self.encode_hint(hint)
         gb = guided_hint.shape[0]
@@ -452,11 +460,12 @@ class ControlledUnetModel(_UNetBase):
         self._build(in_channels, model_channels, out_channels, num_res_blocks, list(attention_resolutions),
                     list(channel_mult), num_heads, context_dim)
 
-    def encode(self, x, timesteps, context=None, kv=None, rows=None, shared_halves=False):
+    def encode(self, x, timesteps, context=None, kv=None, rows=None, shared_halves=False, emb_all=None):
         x = x.float().contiguous()
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
-        emb_all = self._emb(timesteps)
+        if emb_all is None:
+            emb_all = self._emb(timesteps)
         h, hs = self._encode(x, rows, emb_all, kvs, shared_halves=shared_halves)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
         return h, hs, emb_all, kvs
