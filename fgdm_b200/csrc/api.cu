@@ -77,7 +77,7 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
   return fn;
 }
 
-// bf16 tensor, 128-byte swizzle, zero fill out of bounds.
+// bf16 tensor, 128-byte swizzle (64: 64-byte, 0: none), zero fill out of bounds.
 int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                 const uint32_t* box, int swizzle_bytes) {
   PFN_cuTensorMapEncodeTiled_v12000 enc = get_encode();
@@ -103,7 +103,8 @@ int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dim
   }
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank), const_cast<void*>(ptr), gdim,
                    gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   swizzle_bytes == 0 ? CU_TENSOR_MAP_SWIZZLE_NONE
+                   : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed: CUresult %d (rank %d dims %llu,%llu,.. box %u,%u,..)", (int)r, rank,

@@ -117,6 +117,28 @@ FGDM_DEVINL void split_tile(const GemmParams& p, int tile, int& q, int& r) {
   r = tile - q * p.num_n_tiles;
 }
 
+// Folded LayerNorm: mean / rstd of row m from the producer GEMM's per-row partial {sum, sumsq} slots, summed in slot
+// order. Explicit roundings (no compiler-chosen contraction): every epilogue variant gets the same bits for a row.
+FGDM_DEVINL void ln_row_stats(const GemmParams& p, int m, bool row_ok, float& rstd, float& rstd_mean) {
+  float s1 = 0.0f, s2 = 0.0f;
+  if (row_ok) {
+    // slots come in pairs (one per column half of a producer tile): 16-byte loads, four in flight
+    const float4* st = reinterpret_cast<const float4*>(p.ln_stats + static_cast<size_t>(m) * p.ln_slots);
+    const int nq = p.ln_slots >> 1;
+    for (int q0 = 0; q0 < nq; q0 += 4) {
+      float4 f[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) f[q] = q0 + q < nq ? __ldg(st + q0 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { s1 += f[q].x; s1 += f[q].z; s2 += f[q].y; s2 += f[q].w; }
+    }
+  }
+  const float mean = __fmul_rn(s1, p.ln_inv_c);
+  const float var = fmaxf(fmaf(s2, p.ln_inv_c, -__fmul_rn(mean, mean)), 0.0f);
+  rstd = rsqrtf(__fadd_rn(var, p.ln_eps));
+  rstd_mean = __fmul_rn(rstd, mean);
+}
+
 // the 8 epilogue warps only (barrier 0 is the CTA-wide one used at start-up and tear-down)
 FGDM_DEVINL void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory"); }
 
@@ -124,7 +146,8 @@ template <int BN, int CTAS, bool TE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant__ CUtensorMap map_a1,
                const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_out,
-               const __grid_constant__ CUtensorMap map_res, const __grid_constant__ GemmParams p) {
+               const __grid_constant__ CUtensorMap map_res, const __grid_constant__ CUtensorMap map_v,
+               const __grid_constant__ GemmParams p) {
   using Cfg = GemmCfg<BN, CTAS, TE>;
   constexpr int kStages = Cfg::kStages;
   const uint32_t cta_rank = CTAS == 2 ? cluster_ctarank() : 0;   // 0 = leader (issues the pair MMAs)
@@ -323,7 +346,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                              p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr && (p.N & 31) == 0;
 #pragma unroll
     for (int i = 0; i < kMaxP; ++i) bias_pf[i] = 0.0f;
-    if (Cfg::kTmaEpi && p.tma_epi) {
+    if (Cfg::kTmaEpi && p.tma_epi == 1) {
       // ===================== TMA epilogue: its own lean tile loop (classic round-robin tiles only) =====================
       const uint32_t res_u32 = stg_u32, out_u32 = stg_u32 + 2 * kTmaPanelBytes;
       uint64_t* my_res_bar = res_bar + ew * 2;
@@ -442,6 +465,123 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
         tile_c += stride; m_t += sdiv; n_t += smod;
         if (n_t >= nn) { n_t -= nn; ++m_t; }
       }
+    } else if (Cfg::kTmaEpi && BN == 160 && p.tma_epi == 2) {
+      // ===================== head-aligned QKV epilogue (kOutQkv, dhead in {40, 80, 160}) =====================
+      // A 160-column tile is four 40-column groups and every group lies inside ONE head of ONE section (q / k / v):
+      // the two warps of a lane quarter take groups {0, 2} and {1, 3}. A group of a q / k section is staged as
+      // [32 tokens][40 channels] (80-byte rows) and leaves by ONE TMA store into the head-split [img*head*tok, d]
+      // tensor; a group of the v section is staged transposed, [40 channels][32 tokens] (64-byte rows), and leaves by
+      // one TMA store into the transposed [img*head*d, tok_pad] tensor. No per-lane global store (the generic QKV path
+      // issues 32 two-byte stores per 32-column panel for V and spends ~370 instructions per panel on mode tests).
+      // Three staging buffers per warp: a buffer is rewritten once the store issued two groups earlier has read it.
+      constexpr int kG = 40, kBuf = 32 * kG * 2;
+      static_assert(3 * kBuf <= kTmaPanels * kTmaPanelBytes, "QKV staging");
+      const int nn = p.num_n_tiles, stride = gridDim.x;
+      const int sdiv = stride / nn, smod = stride - sdiv * nn;
+      int tile_c = blockIdx.x, m_t = tile_c / nn, n_t = tile_c - m_t * nn;
+      int bias_ntile = -1;
+      uint32_t bsel = 0;                                           // staging buffer of the next group (0, 1, 2, 0, ..)
+      const uint32_t sln_u32 = sbias_u32 + 320;                    // [2 groups][40] ln_s behind [2 groups][40] bias
+      while (tile_c < num_tiles) {
+        const int col0 = n_t * BN;
+        const int m_warp = m_t * kBM + quarter * 32;               // M % 128 == 0: every row is real
+        if (n_t != bias_ntile) {                                   // bias (/ ln_s) of this warp's two groups -> smem
+          __syncwarp();
+#pragma unroll
+          for (int sg = 0; sg < 2; ++sg) {
+            const int c = col0 + kG * (half + 2 * sg);
+            const float b0 = p.bias ? __ldg(p.bias + c + lane) : 0.0f;
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + sg * 160 + lane * 4), "f"(b0) : "memory");
+            if (lane < 8) {
+              const float b1 = p.bias ? __ldg(p.bias + c + 32 + lane) : 0.0f;
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias_u32 + sg * 160 + 128 + lane * 4), "f"(b1) : "memory");
+            }
+            if (p.ln_stats) {
+              asm volatile("st.shared.f32 [%0], %1;" ::"r"(sln_u32 + sg * 160 + lane * 4), "f"(__ldg(p.ln_s + c + lane)) : "memory");
+              if (lane < 8)
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(sln_u32 + sg * 160 + 128 + lane * 4), "f"(__ldg(p.ln_s + c + 32 + lane)) : "memory");
+            }
+          }
+          bias_ntile = n_t;
+          __syncwarp();
+        }
+        // folded LayerNorm: this row's mean / rstd from the producer GEMM's partial sums (fixed slot order)
+        float ln_rstd = 1.0f, ln_rm = 0.0f;
+        if (p.ln_stats) ln_row_stats(p, m_warp + lane, true, ln_rstd, ln_rm);
+        const int img = m_warp >> p.rpi_shift;                     // rows_per_img is a power of two >= 128
+        const int tok0 = m_warp - (img << p.rpi_shift);
+        const int sect = col0 / p.inner;                           // inner % 160 == 0: one section per tile
+        const int rem0 = col0 - sect * p.inner;
+        const int se = sect + p.qkv_first;                         // 0: q, 1: k, 2: v
+        mbar_wait(&acc_full[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll 1
+        for (int sg = 0; sg < 2; ++sg) {
+          const int g = half + 2 * sg;
+          const int rem = rem0 + kG * g;
+          const int head = rem / p.dhead;
+          const int e0 = rem - head * p.dhead;
+          uint32_t ra[32], rb[8];
+          tmem_ld_32x32(taddr + kG * g, ra);
+          tmem_ld_32x8(taddr + kG * g + 32, rb);
+          tmem_ld_wait();
+          float v[kG];
+#pragma unroll
+          for (int j = 0; j < kG; j += 4) {
+            const uint4 ub = ld_shared_16(sbias_u32 + sg * 160 + j * 4);
+            const float bb[4] = {__uint_as_float(ub.x), __uint_as_float(ub.y), __uint_as_float(ub.z), __uint_as_float(ub.w)};
+            float ss[4] = {0.f, 0.f, 0.f, 0.f};
+            if (p.ln_stats) {
+              const uint4 us = ld_shared_16(sln_u32 + sg * 160 + j * 4);
+              ss[0] = __uint_as_float(us.x); ss[1] = __uint_as_float(us.y); ss[2] = __uint_as_float(us.z); ss[3] = __uint_as_float(us.w);
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float a = __uint_as_float(j + e < 32 ? ra[(j + e) & 31] : rb[(j + e) & 7]);
+              v[j + e] = fmaf(a, ln_rstd, -ln_rm * ss[e]) + bb[e];          // same roundings as the generic epilogue (ln off: a + bias)
+            }
+          }
+          const uint32_t buf = stg_u32 + bsel * kBuf;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          __syncwarp();
+          if (se < 2) {
+            const uint32_t rowp = buf + lane * (kG * 2);
+#pragma unroll
+            for (int q = 0; q < kG / 8; ++q)
+              st_shared_16(rowp + q * 16, make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                                     pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7])));
+          } else {
+            const uint32_t colp = buf + lane * 2;
+#pragma unroll
+            for (int e = 0; e < kG; ++e) {
+              const uint16_t h = __bfloat16_as_ushort(__float2bfloat16(v[e]));
+              asm volatile("st.shared.u16 [%0], %1;" ::"r"(colp + e * 64), "h"(h) : "memory");
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            const int ih = img * p.heads + head;
+            if (se < 2) {
+              const CUtensorMap* mp = se == 0 ? &map_out : &map_res;
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                               reinterpret_cast<uint64_t>(mp)), "r"(buf), "r"(e0), "r"((ih << p.rpi_shift) + tok0) : "memory");
+            } else {
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                               reinterpret_cast<uint64_t>(&map_v)), "r"(buf), "r"(tok0), "r"(ih * p.dhead + e0) : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          bsel = bsel == 2 ? 0 : bsel + 1;
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        tile_c += stride; m_t += sdiv; n_t += smod;
+        if (n_t >= nn) { n_t -= nn; ++m_t; }
+      }
     } else
     while (it.next(tile, kc_begin, kc_end)) {
       const bool partial = kc_begin != 0 || kc_end != num_k;   // this CTA holds only part of the tile's K range
@@ -459,25 +599,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
       const uint32_t taddr = tmem_base + acc * Cfg::kAccStride + (static_cast<uint32_t>(quarter * 32) << 16);
       // folded LayerNorm: this row's mean / rstd from the producer GEMM's partial sums (fixed slot order)
       float ln_rstd = 1.0f, ln_rm = 0.0f;                      // rstd and rstd * mean
-      if (p.ln_stats) {
-        float s1 = 0.0f, s2 = 0.0f;
-        if (row_ok) {
-          // slots come in pairs (one per column half of a producer tile): 16-byte loads, four in flight
-          const float4* st = reinterpret_cast<const float4*>(p.ln_stats + static_cast<size_t>(m) * p.ln_slots);
-          const int nq = p.ln_slots >> 1;
-          for (int q0 = 0; q0 < nq; q0 += 4) {
-            float4 f[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) f[q] = q0 + q < nq ? __ldg(st + q0 + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int q = 0; q < 4; ++q) { s1 += f[q].x; s1 += f[q].z; s2 += f[q].y; s2 += f[q].w; }
-          }
-        }
-        const float mean = s1 * p.ln_inv_c;
-        const float var = fmaxf(s2 * p.ln_inv_c - mean * mean, 0.0f);
-        ln_rstd = rsqrtf(var + p.ln_eps);
-        ln_rm = ln_rstd * mean;
-      }
+      if (p.ln_stats) ln_row_stats(p, m, row_ok, ln_rstd, ln_rm);
 
       if (p.out_mode == kOutGeglu) {
         constexpr int kHalf = BN / 2;
@@ -975,7 +1097,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
 
 template <int BN, int CTAS, bool TE = false>
 static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUtensorMap& mb, const CUtensorMap& mo,
-                     const CUtensorMap& mr, const GemmParams& p, cudaStream_t stream) {
+                     const CUtensorMap& mr, const CUtensorMap& mv, const GemmParams& p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, CTAS, TE>;
   static bool configured = false;
   if (!configured) {
@@ -1003,7 +1125,7 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = CTAS == 2 ? 2 : 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS, TE>, ma0, ma1, mb, mo, mr, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CTAS, TE>, ma0, ma1, mb, mo, mr, mv, p);
   if (e != cudaSuccess) { set_error("gemm_tc_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("gemm_tc_kernel");
 }
@@ -1119,6 +1241,23 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     } else if (p.N <= 64) BN = 64;
     else BN = 128;
   }
+  // Head-aligned QKV epilogue (gemm_tc_kernel, tma_epi == 2): 160-column tiles of four 40-column groups, each inside one
+  // head of one section, stored by TMA (q / k as [token][d] runs, v transposed). FGDM_QKV_TMA=0 switches it off.
+  static int qkv_tma_on = -1, qkv_max_chunks = 10;   // K = 1280 (20 chunks): the CTA-pair kernel with the generic epilogue is faster (37.7 vs 43.9 us at 4096x1280->3840)
+  if (qkv_tma_on < 0) {
+    const char* e = getenv("FGDM_QKV_TMA");
+    qkv_tma_on = e ? atoi(e) : 1;
+    const char* c = getenv("FGDM_QKV_TMA_MAX_CHUNKS");
+    if (c) qkv_max_chunks = atoi(c);
+  }
+  const bool qkv_lean =
+      qkv_tma_on && p.out_mode == kOutQkv && (bn_hint == 0 || bn_hint == 160) && !force_pair && p.N % 160 == 0 &&
+      p.inner % 160 == 0 && (p.dhead == 40 || p.dhead == 80 || p.dhead == 160) && p.rows_per_img >= 128 &&
+      (p.rows_per_img & (p.rows_per_img - 1)) == 0 && p.M % p.rows_per_img == 0 && num_k_chunks <= qkv_max_chunks &&
+      p.rowvec == nullptr && p.alpha == 1.0f && p.act == kActNone && p.res0 == nullptr && p.res1 == nullptr &&
+      p.row_stats == nullptr && (p.tok_pad & 7) == 0 && p.tok_pad >= p.rows_per_img &&
+      ((reinterpret_cast<uintptr_t>(p.q_out) | reinterpret_cast<uintptr_t>(p.k_out) | reinterpret_cast<uintptr_t>(p.vt_out)) & 15) == 0;
+  if (qkv_lean) { BN = 160; p.range_ctas = 0; }
   {
     static int force = -1;
     if (force < 0) { const char* e = getenv("FGDM_RANGE_FORCE"); force = e ? atoi(e) : 0; }
@@ -1139,7 +1278,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   static int pair_min = -1;
   if (pair_min < 0) { const char* e = getenv("FGDM_PAIR_MIN"); pair_min = e ? atoi(e) : 20; }
   const bool want_pair = force_pair || pair_mode == 1 || (pair_mode == -1 && num_k_chunks >= pair_min);
-  const int ctas = (want_pair && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
+  const int ctas = (want_pair && !qkv_lean && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
   if (p.range_ctas) {
     if (static_cast<size_t>(p.range_ctas) * 2 * kBM * BN * 4 > kSplitWsBytes) { set_error("gemm: range scratch too small"); return -1; }
     p.split_ws = g_split_ws;
@@ -1190,8 +1329,23 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
               p.rowvec == nullptr && p.alpha == 1.0f && p.act == kActNone && p.res1 == nullptr && p.ln_stats == nullptr &&
               (p.N & 31) == 0 && (reinterpret_cast<uintptr_t>(obase) & 15) == 0 && (p.ldo & 7) == 0 &&
               (p.res0 == nullptr || ((reinterpret_cast<uintptr_t>(p.res0) & 15) == 0 && (p.ld_res0 & 7) == 0));
-  CUtensorMap mo = mb, mr = mb;
-  if (p.tma_epi) {
+  CUtensorMap mo = mb, mr = mb, mv = mb;
+  if (qkv_lean) {
+    p.tma_epi = 2;
+    const int images = p.M / p.rows_per_img;
+    const uint64_t qrows = static_cast<uint64_t>(images) * p.heads * p.rows_per_img;
+    uint64_t dq[2] = {static_cast<uint64_t>(p.dhead), qrows};
+    uint64_t sq[1] = {static_cast<uint64_t>(p.dhead) * 2};
+    uint32_t bq[2] = {40, 32};
+    const void* qp = p.q_out ? p.q_out : p.k_out;            // qkv_first = 1 ([k | v] weights): no q section
+    if (encode_tmap(&mo, qp, 2, dq, sq, bq, 0)) return -1;
+    if (encode_tmap(&mr, p.k_out ? p.k_out : qp, 2, dq, sq, bq, 0)) return -1;
+    uint64_t dv[2] = {static_cast<uint64_t>(p.tok_pad), static_cast<uint64_t>(images) * p.heads * p.dhead};
+    uint64_t sv[1] = {static_cast<uint64_t>(p.tok_pad) * 2};
+    uint32_t bv[2] = {32, 40};
+    if (encode_tmap(&mv, p.vt_out ? p.vt_out : qp, 2, dv, sv, bv, 0)) return -1;
+  }
+  if (p.tma_epi == 1) {
     uint64_t dims[2] = {static_cast<uint64_t>(p.N), static_cast<uint64_t>(p.M)};
     uint32_t box[2] = {32, 32};
     uint64_t so[1] = {static_cast<uint64_t>(p.ldo) * 2};
@@ -1203,27 +1357,28 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   }
   if (ctas == 2) {
     switch (BN) {
-      case 160: return launch_bn<160, 2>(ma0, ma1, mb, mo, mr, p, stream);
-      case 224: return launch_bn<224, 2>(ma0, ma1, mb, mo, mr, p, stream);
-      case 256: return launch_bn<256, 2>(ma0, ma1, mb, mo, mr, p, stream);
+      case 160: return launch_bn<160, 2>(ma0, ma1, mb, mo, mr, mv, p, stream);
+      case 224: return launch_bn<224, 2>(ma0, ma1, mb, mo, mr, mv, p, stream);
+      case 256: return launch_bn<256, 2>(ma0, ma1, mb, mo, mr, mv, p, stream);
       default: set_error("gemm: unsupported pair BN=%d", BN); return -1;
     }
   }
+  if (p.tma_epi == 2) return launch_bn<160, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
   if (p.tma_epi) {
     switch (BN) {
-      case 64: return launch_bn<64, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
-      case 128: return launch_bn<128, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
-      case 160: return launch_bn<160, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
-      case 224: return launch_bn<224, 1, true>(ma0, ma1, mb, mo, mr, p, stream);
+      case 64: return launch_bn<64, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
+      case 128: return launch_bn<128, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
+      case 160: return launch_bn<160, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
+      case 224: return launch_bn<224, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
       default: set_error("gemm: unsupported TMA-epilogue BN=%d", BN); return -1;
     }
   }
   switch (BN) {
-    case 64: return launch_bn<64, 1>(ma0, ma1, mb, mo, mr, p, stream);
-    case 128: return launch_bn<128, 1>(ma0, ma1, mb, mo, mr, p, stream);
-    case 160: return launch_bn<160, 1>(ma0, ma1, mb, mo, mr, p, stream);
-    case 224: return launch_bn<224, 1>(ma0, ma1, mb, mo, mr, p, stream);
-    case 256: return launch_bn<256, 1>(ma0, ma1, mb, mo, mr, p, stream);
+    case 64: return launch_bn<64, 1>(ma0, ma1, mb, mo, mr, mv, p, stream);
+    case 128: return launch_bn<128, 1>(ma0, ma1, mb, mo, mr, mv, p, stream);
+    case 160: return launch_bn<160, 1>(ma0, ma1, mb, mo, mr, mv, p, stream);
+    case 224: return launch_bn<224, 1>(ma0, ma1, mb, mo, mr, mv, p, stream);
+    case 256: return launch_bn<256, 1>(ma0, ma1, mb, mo, mr, mv, p, stream);
     default: set_error("gemm: unsupported BN=%d", BN); return -1;
   }
 }

@@ -282,6 +282,64 @@ def test_qkv_projection_layouts():
     assert relerr(vt, ref[:, :, 2].permute(0, 2, 3, 1)) < 1e-2
 
 
+@pytest.mark.parametrize("images,n,c,mode", [(2, 4096, 320, "qkv"), (3, 1024, 640, "qkv_ln"), (2, 256, 1280, "qkv_ln"),
+                                             (2, 1024, 320, "q_ln"), (2, 128, 640, "kv_pad"), (16, 4096, 320, "qkv")])
+def test_qkv_head_aligned_tma_epilogue(images, n, c, mode):
+    """The head-aligned TMA epilogue of the q/k/v projections (160-column tiles, dhead 40 / 80 / 160; gemm.cu tma_epi == 2)
+    against the fp32 reference and BIT-equal to the generic per-lane epilogue (forced with bn_hint = 128)."""
+    from types import SimpleNamespace
+    from fgdm_b200.layers import LN_EPS, fold_layernorm
+    heads, d = 8, c // 8
+    m = images * n
+    torch.manual_seed(images * 7 + n)
+    x = (torch.randn(m, c, device=DEV) * 1.5 + 0.3).to(torch.bfloat16)
+    sections = {"qkv": 3, "qkv_ln": 3, "q_ln": 1, "kv_pad": 2}[mode]
+    w = torch.randn(sections * c, c, device=DEV) / math.sqrt(c)
+    tp = n + 8 if mode == "kv_pad" else n
+    kw, xref = {}, x.float()
+    if mode.endswith("_ln"):
+        # statistics as a producing GEMM writes them: per-row {sum, sumsq} partials in 2 slots
+        xf = x.float()
+        half = c // 2
+        stats = torch.stack([torch.stack([xf[:, :half].sum(1), (xf[:, :half] ** 2).sum(1)], -1),
+                             torch.stack([xf[:, half:].sum(1), (xf[:, half:] ** 2).sum(1)], -1)], 1).contiguous()
+        norm = SimpleNamespace(g=torch.randn(c, device=DEV) * 0.3 + 1.0, b=torch.randn(c, device=DEV) * 0.2)
+        wf, s, tb = fold_layernorm(w, None, norm)
+        kw = dict(bias=tb, ln=(stats, s, c, LN_EPS))
+        xref = F.layer_norm(xf, (c,), norm.g, norm.b, LN_EPS)
+    else:
+        wf = w.to(torch.bfloat16)
+        w = wf.float()
+    ref = (xref @ w.t()).view(images, n, sections, heads, d)
+
+    def run(bn_hint):
+        q = torch.full((images, heads, n, d), float("nan"), device=DEV, dtype=torch.bfloat16)
+        k = torch.full_like(q, float("nan"))
+        vt = torch.zeros(images, heads, d, tp, device=DEV, dtype=torch.bfloat16)
+        first = 1 if mode == "kv_pad" else 0
+        outs = (q, q, q) if sections == 1 else (None, k, vt) if first else (q, k, vt)
+        ops.conv_gemm(x, wf, sections * c, rows_per_img=n, out_mode=ops.OUT_QKV, qkv=outs + (first, heads, d, tp),
+                      bn_hint=bn_hint, **kw)
+        return q, k, vt
+
+    q, k, vt = run(0)
+    q2, k2, vt2 = run(128)
+    tol = 1.5e-2 if kw else 1e-2
+    if sections == 3:
+        assert relerr(q, ref[:, :, 0].permute(0, 2, 1, 3)) < tol
+        assert relerr(k, ref[:, :, 1].permute(0, 2, 1, 3)) < tol
+        assert relerr(vt, ref[:, :, 2].permute(0, 2, 3, 1)) < tol
+        assert torch.equal(q, q2) and torch.equal(k, k2) and torch.equal(vt, vt2)
+    elif sections == 1:
+        assert relerr(q, ref[:, :, 0].permute(0, 2, 1, 3)) < tol
+        assert torch.equal(q, q2)
+    else:
+        assert relerr(k, ref[:, :, 0].permute(0, 2, 1, 3)) < tol
+        assert relerr(vt[..., :n], ref[:, :, 1].permute(0, 2, 3, 1)) < tol
+        assert float(vt[..., n:].abs().max()) == 0.0                   # the padding columns stay untouched
+        assert torch.equal(k, k2) and torch.equal(vt, vt2)
+
+
 @pytest.mark.parametrize("nb,h,w,c0,c1,silu,eps", [(2, 64, 64, 320, 0, True, 1e-5), (2, 16, 16, 1280, 640, True, 1e-5),
                                                    (1, 8, 8, 64, 0, False, 1e-6), (1, 128, 128, 128, 0, True, 1e-6),
                                                    (3, 32, 32, 640, 320, False, 1e-5)])
