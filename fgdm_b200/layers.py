@@ -327,13 +327,16 @@ class BasicTransformerBlock(Layer):
     # epilogues; the K = 320 projections of the 64x64 level are epilogue-bound already, and there the fold into the wide
     # q/k/v and GEGLU projections costs more than the LayerNorm kernel it removes (tools/bench_lnfold.py).
     FOLD_MIN_DIM = int(os.environ.get("FGDM_LN_FOLD_MIN", "640"))
+    # norm1 -> q/k/v on its own switch: the head-aligned QKV epilogue (gemm.cu tma_epi == 2) is lean enough to carry it
+    FOLD_MIN_DIM_ATTN1 = int(os.environ.get("FGDM_LN_FOLD_MIN_ATTN1", str(FOLD_MIN_DIM)))
 
     def load(self, sd, prefix, dev):
         for n in ("norm1", "norm2", "norm3"):
             self.children[n].load(sd, prefix + n + ".", dev)
         on = os.environ.get("FGDM_LN_FOLD", "1") != "0"           # 0: every LayerNorm runs as its own kernel
         wide = on and self.norm1.c >= self.FOLD_MIN_DIM
-        for consumer, norm, fold in ((self.attn1, self.norm1, wide), (self.attn2, self.norm2, on),
+        wide1 = on and self.norm1.c >= self.FOLD_MIN_DIM_ATTN1
+        for consumer, norm, fold in ((self.attn1, self.norm1, wide1), (self.attn2, self.norm2, on),
                                      (self.ff.net[0], self.norm3, wide)):
             consumer.ln, consumer.ln_fold = norm, fold
         for n in ("attn1", "ff", "attn2"):
