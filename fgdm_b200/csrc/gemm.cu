@@ -1250,12 +1250,15 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     const char* c = getenv("FGDM_QKV_TMA_MAX_CHUNKS");
     if (c) qkv_max_chunks = atoi(c);
   }
+  // a v section exists only when the columns reach it (the cross-attention q projection has N == inner: tok_pad is then
+  // the CONTEXT's padded length and plays no role)
+  const bool qkv_has_v = p.out_mode == kOutQkv && p.inner > 0 && p.N / p.inner + p.qkv_first >= 3;
   const bool qkv_lean =
       qkv_tma_on && p.out_mode == kOutQkv && (bn_hint == 0 || bn_hint == 160) && !force_pair && p.N % 160 == 0 &&
       p.inner % 160 == 0 && (p.dhead == 40 || p.dhead == 80 || p.dhead == 160) && p.rows_per_img >= 128 &&
       (p.rows_per_img & (p.rows_per_img - 1)) == 0 && p.M % p.rows_per_img == 0 && num_k_chunks <= qkv_max_chunks &&
       p.rowvec == nullptr && p.alpha == 1.0f && p.act == kActNone && p.res0 == nullptr && p.res1 == nullptr &&
-      p.row_stats == nullptr && (p.tok_pad & 7) == 0 && p.tok_pad >= p.rows_per_img &&
+      p.row_stats == nullptr && (!qkv_has_v || ((p.tok_pad & 7) == 0 && p.tok_pad >= p.rows_per_img)) &&
       ((reinterpret_cast<uintptr_t>(p.q_out) | reinterpret_cast<uintptr_t>(p.k_out) | reinterpret_cast<uintptr_t>(p.vt_out)) & 15) == 0;
   if (qkv_lean) { BN = 160; p.range_ctas = 0; }
   {
@@ -1343,7 +1346,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     uint64_t dv[2] = {static_cast<uint64_t>(p.tok_pad), static_cast<uint64_t>(images) * p.heads * p.dhead};
     uint64_t sv[1] = {static_cast<uint64_t>(p.tok_pad) * 2};
     uint32_t bv[2] = {32, 40};
-    if (encode_tmap(&mv, p.vt_out ? p.vt_out : qp, 2, dv, sv, bv, 0)) return -1;
+    if (qkv_has_v && encode_tmap(&mv, p.vt_out, 2, dv, sv, bv, 0)) return -1;
   }
   if (p.tma_epi == 1) {
     uint64_t dims[2] = {static_cast<uint64_t>(p.N), static_cast<uint64_t>(p.M)};

@@ -143,7 +143,10 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
         args.row_stats = _p(stats)
     kdim = (9 if conv != CONV_1X1 else 1) * (c0 + c1)
     nres = (res0 is not None) + (res1 is not None)
-    _call("fgdm_conv_gemm", ("gemm taps=%d m=%d k=%d n=%d" % (9 if conv != CONV_1X1 else 1, m, kdim, n), 2.0 * m * n * kdim,
+    # profile key: shape + the epilogue variant (out mode, residuals, rowvec, LayerNorm fold consumer / producer)
+    var = "".join(("" if out_mode == OUT_BF16 else " o%d" % out_mode, " r%d" % nres if nres else "", " rv" if rowvec is not None else "",
+                   " ln" if ln is not None else "", " st" if want_stats else ""))
+    _call("fgdm_conv_gemm", ("gemm taps=%d m=%d k=%d n=%d%s" % (9 if conv != CONV_1X1 else 1, m, kdim, n, var), 2.0 * m * n * kdim,
                              2.0 * (m * (c0 + c1) + n * kdim + m * n * (1 + nres))), C.byref(args), _stream())
     return (out, stats) if want_stats else out
 

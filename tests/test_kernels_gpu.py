@@ -318,7 +318,9 @@ def test_qkv_head_aligned_tma_epilogue(images, n, c, mode):
         vt = torch.zeros(images, heads, d, tp, device=DEV, dtype=torch.bfloat16)
         first = 1 if mode == "kv_pad" else 0
         outs = (q, q, q) if sections == 1 else (None, k, vt) if first else (q, k, vt)
-        ops.conv_gemm(x, wf, sections * c, rows_per_img=n, out_mode=ops.OUT_QKV, qkv=outs + (first, heads, d, tp),
+        # the cross-attention q projection passes the CONTEXT's padded length (80 for 77 tokens) as tok_pad
+        ops.conv_gemm(x, wf, sections * c, rows_per_img=n, out_mode=ops.OUT_QKV,
+                      qkv=outs + (first, heads, d, 80 if sections == 1 else tp),
                       bn_hint=bn_hint, **kw)
         return q, k, vt
 
