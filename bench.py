@@ -215,14 +215,20 @@ def kernel_rooflines(pipe, dev_in, pk, S):
              "decode": lambda: seg.decode_first_stage(dev_in["xT_seg"] * 0.18215)}
     weight = {"seg_step": S, "img_step": S, "decode": 2}
     profs = {}
-    for name, fn in parts.items():
-        fn()                                               # warm
-        # let the host run ahead of the device: with every launch already queued, the event intervals are
-        # kernel execution time, not Python launch latency
-        torch.cuda._sleep(int(0.12 * 1.9e9))
-        ops.profile_start()
-        fn()
-        profs[name] = ops.profile_stop()
+    import fgdm_b200.ldm as ldm_mod
+    overlap = ldm_mod.OVERLAP_CONTROL
+    ldm_mod.OVERLAP_CONTROL = False      # per-kernel times need ONE stream: the captured step forks the ControlNet aside
+    try:
+        for name, fn in parts.items():
+            fn()                                               # warm
+            # let the host run ahead of the device: with every launch already queued, the event intervals are
+            # kernel execution time, not Python launch latency
+            torch.cuda._sleep(int(0.12 * 1.9e9))
+            ops.profile_start()
+            fn()
+            profs[name] = ops.profile_stop()
+    finally:
+        ldm_mod.OVERLAP_CONTROL = overlap
 
     def families(select, weighted):
         fam = {}

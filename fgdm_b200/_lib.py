@@ -48,6 +48,7 @@ SIGNATURES = {
     "fgdm_attention_causal": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp],
     "fgdm_embed_tokens": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp],
     "fgdm_groupnorm": [vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp],
+    "fgdm_set_scratch_slot": [C.c_int],
     "fgdm_groupnorm_noalloc": [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, vp],
     "fgdm_layernorm": [vp, vp, vp, vp, C.c_int, C.c_int, C.c_float, vp],
     "fgdm_softmax_rows": [vp, vp, C.c_int, C.c_int, C.c_float, vp],

@@ -10,6 +10,7 @@
 namespace fgdm {
 
 static thread_local char g_err[512] = "";
+static int g_scratch_slot = 0;     // see fgdm_set_scratch_slot
 static long long g_launches = 0;   // kernels launched through this library (single host thread per process)
 
 void set_error(const char* fmt, ...) {
@@ -34,6 +35,8 @@ bool pdl_enabled() {
   if (on < 0) { const char* e = getenv("FGDM_PDL"); on = (e && e[0] == '1') ? 1 : 0; }   // measured: no gain under CUDA-graph replay, so off unless FGDM_PDL=1
   return on == 1;
 }
+
+int scratch_slot() { return g_scratch_slot; }
 
 int num_sms() {
   static int n = 0;
@@ -176,6 +179,12 @@ extern "C" {
 const char* fgdm_last_error(void) { return g_err; }
 int fgdm_abi_version(void) { return FGDM_ABI_VERSION; }
 long long fgdm_launch_count(void) { return g_launches; }
+
+int fgdm_set_scratch_slot(int slot) {
+  if (slot < 0 || slot >= kScratchSlots) { set_error("fgdm_set_scratch_slot: slot %d out of range [0, %d)", slot, kScratchSlots); return -2; }
+  g_scratch_slot = slot;
+  return 0;
+}
 
 int fgdm_device_check(void) {
   int count = 0;

@@ -18,6 +18,8 @@ int check_launch(const char* what);
 
 static constexpr int kNumSMsDefault = 148;
 int num_sms();
+static constexpr int kScratchSlots = 2;
+int scratch_slot();                         // api.cu: which of the library's scratch sets the next launches use (0 / 1)
 int owner_device_check(const char* what);   // api.cu: the library's scratch belongs to ONE device per process
 
 // ----------------------------------------------------------------------------------------------

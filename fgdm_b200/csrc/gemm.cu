@@ -1133,8 +1133,10 @@ static int launch_bn(const CUtensorMap& ma0, const CUtensorMap& ma1, const CUten
 // split-K scratch owned by the library: allocated on first use (the eager warm-up pass, never inside a graph capture)
 static constexpr size_t kSplitWsBytes = static_cast<size_t>(2) * 160 * 128 * 256 * 4;   // 160 CTAs x 2 slots x (128 x 256) fp32 = 42 MB
 static constexpr int kSplitMaxTiles = 16384;
-static float* g_split_ws = nullptr;
-static unsigned int* g_split_tickets = nullptr;
+// one scratch set per "slot" (fgdm_set_scratch_slot): launches that may run CONCURRENTLY on two streams (the ControlNet
+// next to the UNet encoder inside one step) use different slots
+static float* g_split_ws[kScratchSlots] = {};
+static unsigned int* g_split_tickets[kScratchSlots] = {};
 static bool split_buffers_ready() {
   static int state = 0;   // 0 untried, 1 ready, -1 unavailable (then split-K is simply not used)
   if (state == 0) {
@@ -1142,11 +1144,16 @@ static bool split_buffers_ready() {
     cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
     if (e && e[0] == '0') {
       state = -1;
-    } else if (cudaMalloc(&g_split_ws, kSplitWsBytes) == cudaSuccess &&
-               cudaMalloc(&g_split_tickets, kSplitMaxTiles * sizeof(unsigned int)) == cudaSuccess &&
-               cudaMemset(g_split_tickets, 0, kSplitMaxTiles * sizeof(unsigned int)) == cudaSuccess) {
-      state = 1;
     } else {
+      state = 1;
+      for (int sl = 0; sl < kScratchSlots && state == 1; ++sl) {
+        if (cudaMalloc(&g_split_ws[sl], kSplitWsBytes) != cudaSuccess ||
+            cudaMalloc(&g_split_tickets[sl], kSplitMaxTiles * sizeof(unsigned int)) != cudaSuccess ||
+            cudaMemset(g_split_tickets[sl], 0, kSplitMaxTiles * sizeof(unsigned int)) != cudaSuccess)
+          state = 0;
+      }
+    }
+    if (state == 0) {
       (void)cudaGetLastError();
       state = -1;
     }
@@ -1284,8 +1291,8 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
   const int ctas = (want_pair && !qkv_lean && p.range_ctas == 0 && m_tiles >= 2 && (BN == 160 || BN == 224 || BN == 256)) ? 2 : 1;
   if (p.range_ctas) {
     if (static_cast<size_t>(p.range_ctas) * 2 * kBM * BN * 4 > kSplitWsBytes) { set_error("gemm: range scratch too small"); return -1; }
-    p.split_ws = g_split_ws;
-    p.split_tickets = g_split_tickets;
+    p.split_ws = g_split_ws[scratch_slot()];
+    p.split_tickets = g_split_tickets[scratch_slot()];
   }
   p.num_m_tiles = (p.M + kBM - 1) / kBM;
   p.num_n_tiles = (p.N + BN - 1) / BN;

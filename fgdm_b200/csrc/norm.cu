@@ -369,15 +369,17 @@ int launch_groupnorm(const void* x0, const void* x1, void* y, const float* gamma
   float2* stats = partial + static_cast<size_t>(NB) * kGnMaxChunks * G;
   if (NB > kGnMaxImages) { set_error("groupnorm: NB=%d > %d", NB, kGnMaxImages); return -1; }
   const dim3 grid(g.chunks, NB);
-  static unsigned int* counters = nullptr;       // per-image tickets, zero between launches (single stream per process)
-  if (!counters) {
-    if (cudaMalloc(&counters, kGnMaxImages * sizeof(unsigned int)) != cudaSuccess ||
-        cudaMemset(counters, 0, kGnMaxImages * sizeof(unsigned int)) != cudaSuccess) {
+  // per-image tickets, zero between launches; one set per scratch slot (launches of different slots may overlap)
+  static unsigned int* counters_all = nullptr;
+  if (!counters_all) {
+    if (cudaMalloc(&counters_all, kScratchSlots * kGnMaxImages * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(counters_all, 0, kScratchSlots * kGnMaxImages * sizeof(unsigned int)) != cudaSuccess) {
       set_error("groupnorm: cannot allocate ticket counters");
-      counters = nullptr;
+      counters_all = nullptr;
       return -1;
     }
   }
+  unsigned int* counters = counters_all + scratch_slot() * kGnMaxImages;
   launch_pdl(gn_stats_kernel, grid, dim3(g.threads), smem, stream, reinterpret_cast<const __nv_bfloat16*>(x0),
              reinterpret_cast<const __nv_bfloat16*>(x1), partial, stats, counters, eps, g);
   if (check_launch("gn_stats_kernel")) return -1;

@@ -22,6 +22,9 @@ from .nets import (AutoencoderKL, ControlledUnetModel, ControlNet, IncompatibleK
                    UNetModel)
 
 # reference target string -> our class, so the reference's own YAMLs can be used verbatim
+# FGDM_OVERLAP_CONTROL=0: ControlNet after the UNet encoder on one stream, like the reference (A/B switch)
+OVERLAP_CONTROL = os.environ.get("FGDM_OVERLAP_CONTROL", "1") != "0"
+
 TARGET_ALIASES = {
     "ldm.models.diffusion.ddpm.LatentDiffusion": "fgdm_b200.ldm.LatentDiffusion",
     "ldm.modules.diffusionmodules.openaimodel.UNetModel": "fgdm_b200.nets.UNetModel",
@@ -318,16 +321,32 @@ class ControlLDM(LatentDiffusion):
     def control_step(self, x, t, kv_unet, kv_ctrl, guided_hint, rows, shared_halves=False, emb_unet=None,
                      emb_ctrl=None):
         """One ControlNet + controlled-UNet evaluation on `rows` rows (x may hold rows/2 images). shared_halves: rows r
-        and r + rows/2 share latent, timestep and hint (the sampler's CFG batch), see _UNetBase._encode."""
+        and r + rows/2 share latent, timestep and hint (the sampler's CFG batch), see _UNetBase._encode.
+        The ControlNet's encoder does not depend on the UNet's (cldm.py:836-849 runs them one after the other): it is
+        issued on a forked side stream under the library's second scratch set, so the ~150 kernels of each overlap the
+        other's launch gaps and tails; the zero convolutions, which add the UNet's skips, join the two."""
         unet, cn = self.model.diffusion_model, self.control_model
-        h, hs, emb_all, kvs = unet.encode(x, t, kv=kv_unet, rows=rows, shared_halves=shared_halves, emb_all=emb_unet)
+        cn_args = dict(timesteps=t, kv=kv_ctrl, rows=rows, guided_hint=guided_hint, shared_halves=shared_halves,
+                       emb_all=emb_ctrl)
+        if OVERLAP_CONTROL and x.is_cuda:
+            main = torch.cuda.current_stream()
+            if getattr(self, "_side", None) is None:
+                self._side = torch.cuda.Stream()
+            self._side.wait_stream(main)
+            with torch.cuda.stream(self._side):
+                ops.set_scratch_slot(1)
+                try:
+                    feats = cn.features(x, **cn_args)
+                finally:
+                    ops.set_scratch_slot(0)
+            h, hs, emb_all, kvs = unet.encode(x, t, kv=kv_unet, rows=rows, shared_halves=shared_halves, emb_all=emb_unet)
+            main.wait_stream(self._side)
+        else:
+            h, hs, emb_all, kvs = unet.encode(x, t, kv=kv_unet, rows=rows, shared_halves=shared_halves, emb_all=emb_unet)
+            feats = cn.features(x, **cn_args)
         n = len(hs)
         if self.only_mid_control:
-            ctrl = cn.forward(x, timesteps=t, kv=kv_ctrl, rows=rows, guided_hint=guided_hint,
-                              scales=self.control_scales, add_to=[None] * n + [h], only_mid=True,
-                              shared_halves=shared_halves, emb_all=emb_ctrl)
+            ctrl = cn.control_outputs(feats, self.control_scales, [None] * n + [h], only_mid=True)
             return unet.decode(ctrl[-1], hs, emb_all, kvs)
-        ctrl = cn.forward(x, timesteps=t, kv=kv_ctrl, rows=rows, guided_hint=guided_hint,
-                          scales=self.control_scales, add_to=hs + [h], shared_halves=shared_halves,
-                          emb_all=emb_ctrl)
+        ctrl = cn.control_outputs(feats, self.control_scales, hs + [h])
         return unet.decode(ctrl[-1], ctrl[:-1], emb_all, kvs)

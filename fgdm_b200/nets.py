@@ -409,11 +409,10 @@ class ControlNet(_UNetBase):
     def encode_hint(self, hint):
         return self.input_hint_block.forward(hint)
 
-    def forward(self, x, hint=None, timesteps=None, context=None, kv=None, rows=None, guided_hint=None,
-                scales=None, add_to=None, only_mid=False, shared_halves=False, emb_all=None, **kwargs):
-        """Returns the 13 tensors `zero_conv(h) * scale` (cldm.py:801-811, scaling of :846 folded into the
-        epilogue). With add_to = [hs..., h_mid] of the UNet encoder, returns `add_to[k] + scale*control[k]`
-        instead (the adds of cldm.py:39-47 ride the same epilogue). Outputs are NHWC bf16."""
+    def features(self, x, hint=None, timesteps=None, context=None, kv=None, rows=None, guided_hint=None,
+                 shared_halves=False, emb_all=None):
+        """The encoder + middle block (cldm.py:796-811 without the zero convolutions): the 12 skip tensors and the middle
+        tensor, NHWC bf16. Independent of the UNet it controls, so a caller may run it next to the UNet's encoder."""
         x = x.float().contiguous()
         rows = rows or x.shape[0]
         kvs = kv if kv is not None else self.project_context(context)
@@ -432,15 +431,28 @@ class ControlNet(_UNetBase):
         share = shared_halves and (rows // 2) % gb == 0
         h, hs = self._encode(x, rows, emb_all, kvs, None, after_conv_in=add_hint, shared_halves=share)
         h = self._run(self.middle_block, h, None, emb_all, kvs)
-        scales = scales or [1.0] * (len(hs) + 1)
+        return hs + [h]
+
+    def control_outputs(self, feats, scales=None, add_to=None, only_mid=False):
+        """The 13 tensors `zero_conv(h) * scale` (cldm.py:801-811, scaling of :846 folded into the epilogue). With
+        add_to = [hs..., h_mid] of the UNet encoder, `add_to[k] + scale*control[k]` instead (the adds of cldm.py:39-47
+        ride the same epilogue)."""
+        n = len(feats) - 1
+        scales = scales or [1.0] * (n + 1)
         outs = []
-        for k, hk in enumerate(hs + [h]):
-            if only_mid and k < len(hs):
+        for k, hk in enumerate(feats):
+            if only_mid and k < n:
                 outs.append(None)
                 continue
-            zc = self.zero_convs[k][0] if k < len(hs) else self.middle_block_out[0]
+            zc = self.zero_convs[k][0] if k < n else self.middle_block_out[0]
             outs.append(zc.gemm(hk, alpha=float(scales[k]), res0=None if add_to is None else add_to[k]))
         return outs
+
+    def forward(self, x, hint=None, timesteps=None, context=None, kv=None, rows=None, guided_hint=None,
+                scales=None, add_to=None, only_mid=False, shared_halves=False, emb_all=None, **kwargs):
+        """Returns the 13 control tensors (see control_outputs). Outputs are NHWC bf16."""
+        feats = self.features(x, hint, timesteps, context, kv, rows, guided_hint, shared_halves, emb_all)
+        return self.control_outputs(feats, scales, add_to, only_mid)
 
 
 class ControlledUnetModel(_UNetBase):

@@ -69,6 +69,13 @@ def launch_count() -> int:
     return int(_lib.load().fgdm_launch_count()) + _REPLAYED
 
 
+def set_scratch_slot(slot: int) -> None:
+    """Scratch set (0 / 1) of the launches that follow; see fgdm_set_scratch_slot in include/fgdm_b200.h."""
+    rc = _lib.load().fgdm_set_scratch_slot(int(slot))
+    if rc:
+        raise RuntimeError(_lib.load().fgdm_last_error().decode())
+
+
 def count_launches(n: int) -> None:
     """Account for `n` of our kernels executed by a CUDA-graph replay."""
     global _REPLAYED

@@ -20,8 +20,9 @@
  *    fgdm_conv_gemm, image tickets of fgdm_groupnorm), allocated on the device that is current at the first call.
  *    ONE process drives ONE device (one rank per GPU): a call made with another device current fails with an error.
  *    Calls may be issued from any host thread, but launches that use the scratch (fgdm_conv_gemm in split-K /
- *    stream-K mode, fgdm_groupnorm's two-launch form) must not run CONCURRENTLY on two streams; stream-ordered use,
- *    including CUDA-graph replay on one stream, is what the host mirror does.
+ *    stream-K mode, fgdm_groupnorm's two-launch form) must not run CONCURRENTLY on two streams unless they were
+ *    issued under different scratch slots (fgdm_set_scratch_slot: two sets exist); stream-ordered use, including
+ *    CUDA-graph replay, and ONE forked side stream on slot 1 is what the host mirror does.
  */
 #ifndef FGDM_B200_H_
 #define FGDM_B200_H_
@@ -39,6 +40,11 @@ const char* fgdm_last_error(void);
 int fgdm_abi_version(void);
 /* Number of kernels this library has launched (or captured into a CUDA graph) so far in this process. */
 long long fgdm_launch_count(void);
+/* Which of the library's two scratch sets (split-K partials + tickets, GroupNorm image tickets) the FOLLOWING launches of
+ * this host thread use: 0 (default) or 1. Launches that may overlap on the GPU (two streams forked inside one step: the
+ * ControlNet next to the UNet encoder, cldm.py:836-849 evaluates them one after the other) must use different sets. No
+ * reference counterpart: the reference never runs two kernels at once. */
+int fgdm_set_scratch_slot(int slot);
 /* 0 when device 0 is an sm_100 class GPU and the driver exposes cuTensorMapEncodeTiled. */
 int fgdm_device_check(void);
 
