@@ -152,6 +152,29 @@ def test_shared_cfg_head_matches_full_evaluation(fgdm, control):
     assert relmax(shared, ref) < EPS_TOL
 
 
+def test_forked_controlnet_is_bit_equal_to_sequential(control, monkeypatch):
+    """ControlLDM.control_step runs the ControlNet encoder on a side stream under the library's second scratch set
+    (fgdm_set_scratch_slot) next to the UNet encoder: same kernels, same fixed-order reductions -> the eps of the forked
+    step must equal the sequential step bit for bit (8x8 / 16x16 convs use split-K scratch, GroupNorm uses tickets)."""
+    import fgdm_b200.ldm as ldm_mod
+    model, _ = control
+    B = 8
+    x, t, ctx = _cfg_rows(B, 1100)
+    hint = gc._hint(B, 512, 77).to(DEV)
+    unet, cn = model.model.diffusion_model, model.control_model
+    args = (x, t, unet.project_context(ctx), cn.project_context(ctx), cn.encode_hint(hint), 2 * B)
+    monkeypatch.setattr(ldm_mod, "OVERLAP_CONTROL", False)
+    seq = model.control_step(*args, shared_halves=True).clone()
+    monkeypatch.setattr(ldm_mod, "OVERLAP_CONTROL", True)
+    for _ in range(3):                                   # different interleavings of the two streams
+        forked = model.control_step(*args, shared_halves=True)
+        torch.cuda.synchronize()
+        assert torch.equal(forked, seq)
+    with pytest.raises(RuntimeError):
+        ops.set_scratch_slot(2)
+    ops.set_scratch_slot(0)
+
+
 def test_batch_invariance_B8_vs_B1(fgdm, control):
     """Prompts 0..7 in one B=8 chain (the bench's step) against eight B=1 chains with the same per-prompt x_T:
     PSNR >= 35 dB per image (tile widths / split-K change with M, so bit equality is reported, not required)."""
