@@ -452,11 +452,14 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
 // MUFU ping-pong between tile pairs through named barriers (760 us), the softmax warps issuing their own MMAs behind
 // 128-thread named barriers (1023 us), mbarrier suspend-time hints (935 us). This form: 707 us (attention_kernel: 745).
 // =====================================================================================================================
-template <int DV, int KST>
+// QT query tiles per CTA, KA 64-column atoms of the head dim (Q / K rows), PB P buffers per tile. d <= 56: <DV, 2, 4, 1, 2>.
+// d = 80 (round 2): <96, 2, 3, 2, 1> - three tiles (TMEM 3 x (64 + 96) = 480 columns), Q / K tiles of two atoms, ONE P
+// buffer per tile (200 KB of shared memory), so P(j) waits for PV(j-1).
+template <int DV, int KST, int QT_ = 4, int KA_ = 1, int PB_ = 2>
 struct Attn4Cfg {
-  static constexpr int QT = 4, BN = 64, PB = 2;
-  static constexpr int kQBytes = 128 * 128;            // one swizzle atom [128 rows x 128 B] per query tile
-  static constexpr int kKBytes = BN * 128;
+  static constexpr int QT = QT_, BN = 64, PB = PB_, KA = KA_;
+  static constexpr int kQBytes = KA * 128 * 128;       // KA swizzle atoms [128 rows x 128 B] per query tile
+  static constexpr int kKBytes = KA * BN * 128;
   static constexpr int kVBytes = DV * 128;             // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kPBytes = 128 * 128;            // [128 rows x 64 keys] bf16
   static constexpr int kSmemBytes = 1024 + QT * kQBytes + KST * (kKBytes + kVBytes) + QT * PB * kPBytes + 512;
@@ -464,20 +467,21 @@ struct Attn4Cfg {
   static constexpr int kIssue0 = kSoftmaxWarps;        // QT MMA-issue warps (one per query tile)
   static constexpr int kKProd = kSoftmaxWarps + QT;    // TMA producer of Q and the K ring
   static constexpr int kVProd = kKProd + 1;            // TMA producer of the V ring
-  // 6 warpgroups (setmaxnreg is per warpgroup): 4 softmax, 1 MMA issue, 1 with the two producers + 2 idle warps
-  static constexpr int kThreads = 32 * 24;
+  // warpgroups (setmaxnreg is per warpgroup): QT softmax, then two with the issue warps, the two producers and idle warps
+  static constexpr int kThreads = 32 * (kSoftmaxWarps + 8);
   static constexpr int kRegsSoftmax = 104, kRegsOther = 32;
-  static constexpr int kTmemStride = 128;
-  static_assert(BN + DV <= kTmemStride, "TMEM budget");
+  static constexpr int kTmemStride = (BN + DV <= 128) ? 128 : 160;
+  static_assert(QT + 2 <= 8, "issue + producer warps fit the two trailing warpgroups");
+  static_assert(BN + DV <= kTmemStride && QT * kTmemStride <= 512, "TMEM budget");
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
-template <int DV, int KST>
-__global__ void __launch_bounds__(Attn4Cfg<DV, KST>::kThreads, 1)
+template <int DV, int KST, int QT_, int KA_, int PB_>
+__global__ void __launch_bounds__(Attn4Cfg<DV, KST, QT_, KA_, PB_>::kThreads, 1)
 attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                   const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
-  using Cfg = Attn4Cfg<DV, KST>;
-  constexpr int QT = Cfg::QT, BN = Cfg::BN, PB = Cfg::PB;
+  using Cfg = Attn4Cfg<DV, KST, QT_, KA_, PB_>;
+  constexpr int QT = Cfg::QT, BN = Cfg::BN, PB = Cfg::PB, KA = Cfg::KA;
   extern __shared__ uint8_t smem_raw[];
   // every shared-memory object is a 32-bit shared address: base + compile-time offset
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -631,7 +635,8 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 
       // ---- probabilities -> bf16 P buffer j & 1 (128B swizzle, K-major): 8 chunks of 8 keys per row ----
       const float neg_m = -m_ref;
-      const uint32_t sP_row = sP_row0 + (j & 1) * Cfg::kPBytes;
+      const uint32_t sP_row = sP_row0 + (PB == 2 ? (j & 1) : 0) * Cfg::kPBytes;
+      if (PB == 1 && j > 0) wait_pv(j - 1);             // the single P buffer is still being read by PV(j-1)
       auto emit = [&](auto masked) {
 #pragma unroll
         for (int c = 0; c < BN; c += 8) {
@@ -693,14 +698,17 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     auto issue_s = [&](int st) {
       constexpr uint32_t idesc = make_idesc_bf16(128, BN);
       const uint64_t dk = dk0 + static_cast<uint64_t>(st * (Cfg::kKBytes >> 4));
-      for (int k = 0; k < ksteps; ++k) tc_mma_bf16(tm, dq + 2 * k, dk + 2 * k, idesc, k != 0 ? 1u : 0u);
+      for (int k = 0; k < ksteps; ++k) {                // K-step k lives in atom k / 4 (64 columns = 4 steps of 16)
+        const uint32_t a = k >> 2, kk = k & 3;
+        tc_mma_bf16(tm, dq + a * ((128 * 128) >> 4) + 2 * kk, dk + a * ((BN * 128) >> 4) + 2 * kk, idesc, k != 0 ? 1u : 0u);
+      }
       tc_commit_a(sbase + bS + 8 * t);
       tc_commit_a(sbase + bKe + 8 * st);
     };
     auto issue_pv = [&](int j, int st) {
       constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV);
       const uint64_t dv = dv0 + static_cast<uint64_t>(st * (Cfg::kVBytes >> 4));
-      const uint64_t dp = dp0 + static_cast<uint64_t>((j & 1) * (Cfg::kPBytes >> 4));
+      const uint64_t dp = dp0 + static_cast<uint64_t>((PB == 2 ? (j & 1) : 0) * (Cfg::kPBytes >> 4));
 #pragma unroll
       for (int ks = 0; ks < BN / 16; ++ks) tc_mma_bf16(tm + BN, dp + 2 * ks, dv + 2 * ks, idesc_pv, (j | ks) != 0 ? 1u : 0u);
       tc_commit_a(sbase + bO + 16 * t + 8 * (j & 1));
@@ -745,12 +753,17 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     if (lane == 0) {
       mbar_expect_tx_a(sbase + bQ, QT * Cfg::kQBytes);
 #pragma unroll
-      for (int t = 0; t < QT; ++t) tma_load_3d_a(sbase + oQ + t * Cfg::kQBytes, &map_q, sbase + bQ, 0, q0 + t * 128, bh);
+      for (int t = 0; t < QT; ++t)
+#pragma unroll
+        for (int a = 0; a < KA; ++a)
+          tma_load_3d_a(sbase + oQ + t * Cfg::kQBytes + a * (128 * 128), &map_q, sbase + bQ, a * 64, q0 + t * 128, bh);
       int st = 0, ph = 0;                               // ring position of load j, parity of its (j / KST)-th use
       for (int j = 0; j < num_kv; ++j) {
         if (j >= KST) mbar_wait_a(sbase + bKe + 8 * st, ph ^ 1);
         mbar_expect_tx_a(sbase + bK + 8 * st, Cfg::kKBytes);
-        tma_load_3d_a(sbase + oK + st * Cfg::kKBytes, &map_k, sbase + bK + 8 * st, 0, j * BN, bh);
+#pragma unroll
+        for (int a = 0; a < KA; ++a)
+          tma_load_3d_a(sbase + oK + st * Cfg::kKBytes + a * (BN * 128), &map_k, sbase + bK + 8 * st, a * 64, j * BN, bh);
         if (++st == KST) { st = 0; ph ^= 1; }
       }
     }
@@ -775,12 +788,12 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
   }
 }
 
-template <int DV, int KST>
+template <int DV, int KST, int QT = 4, int KA = 1, int PB = 2>
 static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams p, int tok_pad, cudaStream_t stream) {
-  using Cfg = Attn4Cfg<DV, KST>;
+  using Cfg = Attn4Cfg<DV, KST, QT, KA, PB>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST, QT, KA, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("attention4: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -807,8 +820,8 @@ static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams
     uint32_t box[3] = {64, static_cast<uint32_t>(DV), 1};
     if (encode_tmap(&mv, vt, 3, dims, strides, box)) return -1;
   }
-  dim3 grid((p.Nq + 511) / 512, p.BH, 1);
-  cudaError_t e = launch_pdl(attention4_kernel<DV, KST>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p);
+  dim3 grid((p.Nq + 128 * QT - 1) / (128 * QT), p.BH, 1);
+  cudaError_t e = launch_pdl(attention4_kernel<DV, KST, QT, KA, PB>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p);
   if (e != cudaSuccess) { set_error("attention4_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("attention4_kernel");
 }
@@ -1099,6 +1112,12 @@ static int launch_xattn(const CUtensorMap& mq, const CUtensorMap& mk, const CUte
   return check_launch("xattention_kernel");
 }
 
+// FGDM_ATTN4_D80=0: d = 80 stays on attention_kernel<2, 96, 64, 2> (A/B)
+static int attn4_d80() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("FGDM_ATTN4_D80"); v = e ? atoi(e) : 1; }
+  return v;
+}
 // FGDM_ATTN4=0: never use attention4_kernel (A/B against attention_kernel)
 static int attn4_mode() {
   static int mode = -1;
@@ -1154,6 +1173,11 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
     FGDM_ATTN4_CASE(48)
     FGDM_ATTN4_CASE(64)
 #undef FGDM_ATTN4_CASE
+  }
+  // d = 80 (the 32x32 level): the same kernel with three query tiles per CTA, two head-dim atoms and one P buffer per tile
+  if (KA == 2 && nsplit == 1 && DV == 96 && !causal && Nq >= 384 && Nk >= 512 && attn4_mode() != 0 && attn4_d80()) {
+    if (attn4_d80() == 2) return launch_attn4<96, 2, 2, 2, 2>(q, k, vt, p, tok_pad, stream);
+    return launch_attn4<96, 2, 3, 2, 1>(q, k, vt, p, tok_pad, stream);
   }
 
   // one key/value tile against many query tiles (text cross-attention): xattention_kernel
