@@ -453,13 +453,15 @@ static int launch_attn_q(const CUtensorMap& mq, const CUtensorMap& mk, const CUt
 // 128-thread named barriers (1023 us), mbarrier suspend-time hints (935 us). This form: 707 us (attention_kernel: 745).
 // =====================================================================================================================
 // QT query tiles per CTA, KA 64-column atoms of the head dim (Q / K rows), PB P buffers per tile. d <= 56: <DV, 2, 4, 1, 2>.
-// d = 80 (round 2): <96, 2, 3, 2, 1> - three tiles (TMEM 3 x (64 + 96) = 480 columns), Q / K tiles of two atoms, ONE P
-// buffer per tile (200 KB of shared memory), so P(j) waits for PV(j-1).
-template <int DV, int KST, int QT_ = 4, int KA_ = 1, int PB_ = 2>
+// d = 80 (round 2): <96, 2, 3, 1, 2, 1> - three tiles (TMEM 3 x (64 + 96) = 480 columns), Q / K tiles of one 64-column atom
+// and a 16-column tail atom, two P buffers per tile: 200 KB of shared memory.
+template <int DV, int KST, int QT_ = 4, int KA_ = 1, int PB_ = 2, int TAIL_ = 0>
 struct Attn4Cfg {
-  static constexpr int QT = QT_, BN = 64, PB = PB_, KA = KA_;
-  static constexpr int kQBytes = KA * 128 * 128;       // KA swizzle atoms [128 rows x 128 B] per query tile
-  static constexpr int kKBytes = KA * BN * 128;
+  static constexpr int QT = QT_, BN = 64, PB = PB_, KA = KA_, TAIL = TAIL_;
+  // KA swizzle atoms [rows x 128 B] per Q / K tile (64 head-dim columns each) + TAIL atoms [rows x 32 B] (16 columns, 32-byte
+  // swizzle): d = 80 is one full atom and one tail, 20 KB per query tile instead of 32
+  static constexpr int kQBytes = KA * 128 * 128 + TAIL * 128 * 32;
+  static constexpr int kKBytes = KA * BN * 128 + TAIL * BN * 32;
   static constexpr int kVBytes = DV * 128;             // one key-atom (64 keys) of [DV rows x 128 B]
   static constexpr int kPBytes = 128 * 128;            // [128 rows x 64 keys] bf16
   static constexpr int kSmemBytes = 1024 + QT * kQBytes + KST * (kKBytes + kVBytes) + QT * PB * kPBytes + 512;
@@ -476,12 +478,13 @@ struct Attn4Cfg {
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 };
 
-template <int DV, int KST, int QT_, int KA_, int PB_>
-__global__ void __launch_bounds__(Attn4Cfg<DV, KST, QT_, KA_, PB_>::kThreads, 1)
+template <int DV, int KST, int QT_, int KA_, int PB_, int TAIL_>
+__global__ void __launch_bounds__(Attn4Cfg<DV, KST, QT_, KA_, PB_, TAIL_>::kThreads, 1)
 attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
-                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ AttnParams p) {
-  using Cfg = Attn4Cfg<DV, KST, QT_, KA_, PB_>;
-  constexpr int QT = Cfg::QT, BN = Cfg::BN, PB = Cfg::PB, KA = Cfg::KA;
+                  const __grid_constant__ CUtensorMap map_vt, const __grid_constant__ CUtensorMap map_q2,
+                  const __grid_constant__ CUtensorMap map_k2, const __grid_constant__ AttnParams p) {
+  using Cfg = Attn4Cfg<DV, KST, QT_, KA_, PB_, TAIL_>;
+  constexpr int QT = Cfg::QT, BN = Cfg::BN, PB = Cfg::PB, KA = Cfg::KA, TAIL = Cfg::TAIL;
   extern __shared__ uint8_t smem_raw[];
   // every shared-memory object is a 32-bit shared address: base + compile-time offset
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -693,15 +696,20 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
     const uint32_t tm = tmem_base + t * Cfg::kTmemStride;
     const uint64_t dq = make_desc_sw128(sbase + oQ + t * Cfg::kQBytes);
     const uint64_t dk0 = make_desc_sw128(sbase + oK);
+    const uint64_t dq2 = make_desc_sw32(sbase + oQ + t * Cfg::kQBytes + KA * 128 * 128);
+    const uint64_t dk20 = make_desc_sw32(sbase + oK + KA * BN * 128);
     const uint64_t dv0 = make_desc_sw128(sbase + oV);
     const uint64_t dp0 = make_desc_sw128(sbase + oP + t * PB * Cfg::kPBytes);
     auto issue_s = [&](int st) {
       constexpr uint32_t idesc = make_idesc_bf16(128, BN);
       const uint64_t dk = dk0 + static_cast<uint64_t>(st * (Cfg::kKBytes >> 4));
-      for (int k = 0; k < ksteps; ++k) {                // K-step k lives in atom k / 4 (64 columns = 4 steps of 16)
+      const int kfull = min(ksteps, 4 * KA);
+      for (int k = 0; k < kfull; ++k) {                 // K-step k lives in atom k / 4 (64 columns = 4 steps of 16)
         const uint32_t a = k >> 2, kk = k & 3;
         tc_mma_bf16(tm, dq + a * ((128 * 128) >> 4) + 2 * kk, dk + a * ((BN * 128) >> 4) + 2 * kk, idesc, k != 0 ? 1u : 0u);
       }
+      if (TAIL && ksteps > 4 * KA)                      // the 16 columns past the full atoms: one K-step from the tail atoms
+        tc_mma_bf16(tm, dq2, dk20 + static_cast<uint64_t>(st * (Cfg::kKBytes >> 4)), idesc, 1u);
       tc_commit_a(sbase + bS + 8 * t);
       tc_commit_a(sbase + bKe + 8 * st);
     };
@@ -757,6 +765,9 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 #pragma unroll
         for (int a = 0; a < KA; ++a)
           tma_load_3d_a(sbase + oQ + t * Cfg::kQBytes + a * (128 * 128), &map_q, sbase + bQ, a * 64, q0 + t * 128, bh);
+      if (TAIL)
+        for (int t = 0; t < QT; ++t)
+          tma_load_3d_a(sbase + oQ + t * Cfg::kQBytes + KA * 128 * 128, &map_q2, sbase + bQ, KA * 64, q0 + t * 128, bh);
       int st = 0, ph = 0;                               // ring position of load j, parity of its (j / KST)-th use
       for (int j = 0; j < num_kv; ++j) {
         if (j >= KST) mbar_wait_a(sbase + bKe + 8 * st, ph ^ 1);
@@ -764,6 +775,7 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
 #pragma unroll
         for (int a = 0; a < KA; ++a)
           tma_load_3d_a(sbase + oK + st * Cfg::kKBytes + a * (BN * 128), &map_k, sbase + bK + 8 * st, a * 64, j * BN, bh);
+        if (TAIL) tma_load_3d_a(sbase + oK + st * Cfg::kKBytes + KA * BN * 128, &map_k2, sbase + bK + 8 * st, KA * 64, j * BN, bh);
         if (++st == KST) { st = 0; ph ^= 1; }
       }
     }
@@ -788,12 +800,12 @@ attention4_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_consta
   }
 }
 
-template <int DV, int KST, int QT = 4, int KA = 1, int PB = 2>
+template <int DV, int KST, int QT = 4, int KA = 1, int PB = 2, int TAIL = 0>
 static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams p, int tok_pad, cudaStream_t stream) {
-  using Cfg = Attn4Cfg<DV, KST, QT, KA, PB>;
+  using Cfg = Attn4Cfg<DV, KST, QT, KA, PB, TAIL>;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST, QT, KA, PB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(attention4_kernel<DV, KST, QT, KA, PB, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::kSmemBytes);
     if (e != cudaSuccess) {
       set_error("attention4: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::kSmemBytes, cudaGetErrorString(e));
@@ -820,8 +832,20 @@ static int launch_attn4(const void* q, const void* k, const void* vt, AttnParams
     uint32_t box[3] = {64, static_cast<uint32_t>(DV), 1};
     if (encode_tmap(&mv, vt, 3, dims, strides, box)) return -1;
   }
+  CUtensorMap mq2 = mq, mk2 = mk;
+  if (TAIL) {       // the 16 head-dim columns past the full atoms: 32-byte rows, 32-byte swizzle
+    uint64_t dq_[3] = {static_cast<uint64_t>(p.d), static_cast<uint64_t>(p.Nq), static_cast<uint64_t>(p.BH)};
+    uint64_t sq_[2] = {static_cast<uint64_t>(p.d) * 2, static_cast<uint64_t>(p.Nq) * p.d * 2};
+    uint32_t bq_[3] = {16, 128, 1};
+    if (encode_tmap(&mq2, q, 3, dq_, sq_, bq_, 32)) return -1;
+    uint64_t dk_[3] = {static_cast<uint64_t>(p.d), static_cast<uint64_t>(p.Nk), static_cast<uint64_t>(p.BH)};
+    uint64_t sk_[2] = {static_cast<uint64_t>(p.d) * 2, static_cast<uint64_t>(p.Nk) * p.d * 2};
+    uint32_t bk_[3] = {16, 64, 1};
+    if (encode_tmap(&mk2, k, 3, dk_, sk_, bk_, 32)) return -1;
+  }
   dim3 grid((p.Nq + 128 * QT - 1) / (128 * QT), p.BH, 1);
-  cudaError_t e = launch_pdl(attention4_kernel<DV, KST, QT, KA, PB>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv, p);
+  cudaError_t e = launch_pdl(attention4_kernel<DV, KST, QT, KA, PB, TAIL>, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, mq, mk, mv,
+                             mq2, mk2, p);
   if (e != cudaSuccess) { set_error("attention4_kernel: launch failed: %s", cudaGetErrorString(e)); return -1; }
   return check_launch("attention4_kernel");
 }
@@ -1176,8 +1200,8 @@ int launch_attention(const void* q, const void* k, const void* vt, void* out, in
   }
   // d = 80 (the 32x32 level): the same kernel with three query tiles per CTA, two head-dim atoms and one P buffer per tile
   if (KA == 2 && nsplit == 1 && DV == 96 && !causal && Nq >= 384 && Nk >= 512 && attn4_mode() != 0 && attn4_d80()) {
-    if (attn4_d80() == 2) return launch_attn4<96, 2, 2, 2, 2>(q, k, vt, p, tok_pad, stream);
-    return launch_attn4<96, 2, 3, 2, 1>(q, k, vt, p, tok_pad, stream);
+    if (attn4_d80() == 2) return launch_attn4<96, 2, 3, 2, 1>(q, k, vt, p, tok_pad, stream);   // two full atoms, one P buffer
+    return launch_attn4<96, 2, 3, 1, 2, 1>(q, k, vt, p, tok_pad, stream);
   }
 
   // one key/value tile against many query tiles (text cross-attention): xattention_kernel

@@ -282,6 +282,18 @@ FGDM_DEVINL uint64_t make_desc_sw128(uint32_t smem_addr) {
   return d;
 }
 
+// The same for rows of 32 bytes (16 bf16 = ONE K-step) with the 32-byte swizzle (TMA box with inner extent 16 bf16 and
+// CU_TENSOR_MAP_SWIZZLE_32B): 8-row groups are 256 B apart. Used for the 16 head-dim columns past 64 when d = 80.
+FGDM_DEVINL uint64_t make_desc_sw32(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(256 >> 4) << 32;              // SBO = 256 B
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(6) << 61;                     // layout type: SWIZZLE_32B
+  return d;
+}
+
 // Instruction descriptor: bf16 x bf16 -> fp32, both operands K-major, tile M x N.
 FGDM_DEVINL constexpr uint32_t make_idesc_bf16(int M, int N) {
   return (1u << 4)                         // c_format = F32
