@@ -191,7 +191,7 @@ __global__ void gn_apply_kernel(const __nv_bfloat16* __restrict__ x0, const __nv
         const float2 f = unpack_bf16x2(w[e]);
         float r0 = f.x * a[2 * e] + b[2 * e];
         float r1 = f.y * a[2 * e + 1] + b[2 * e + 1];
-        if (silu) { r0 = silu_f(r0); r1 = silu_f(r1); }
+        if (silu == 1) { r0 = silu_f(r0); r1 = silu_f(r1); } else if (silu) { r0 = silu_exact_f(r0); r1 = silu_exact_f(r1); }
         o[e] = pack_bf16x2(r0, r1);
       }
       *reinterpret_cast<uint4*>(y + (base + pq) * C + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);
@@ -309,7 +309,7 @@ gn_slab_kernel(const __nv_bfloat16* __restrict__ x0, const __nv_bfloat16* __rest
       const float2 f = unpack_bf16x2(w[e]);
       float r0 = f.x * a[2 * e] + b[2 * e];
       float r1 = f.y * a[2 * e + 1] + b[2 * e + 1];
-      if (silu) { r0 = silu_f(r0); r1 = silu_f(r1); }
+      if (silu == 1) { r0 = silu_f(r0); r1 = silu_f(r1); } else if (silu) { r0 = silu_exact_f(r0); r1 = silu_exact_f(r1); }
       o[e] = pack_bf16x2(r0, r1);
     }
     *reinterpret_cast<uint4*>(y + (base + pix) * C + v * 8) = make_uint4(o[0], o[1], o[2], o[3]);

@@ -551,8 +551,8 @@ class _VaeRes(Layer):
         self.nin = self.add("nin_shortcut", Conv2d(cin, cout, 1)) if cin != cout else None
 
     def forward(self, x):
-        h = self.conv1.gemm(ops.groupnorm(x, self.norm1.g, self.norm1.b, eps=1e-6, silu=True))
-        h = ops.groupnorm(h, self.norm2.g, self.norm2.b, eps=1e-6, silu=True)
+        h = self.conv1.gemm(ops.groupnorm(x, self.norm1.g, self.norm1.b, eps=1e-6, silu="exact"))
+        h = ops.groupnorm(h, self.norm2.g, self.norm2.b, eps=1e-6, silu="exact")
         s = self.nin.gemm(x) if self.nin is not None else x
         return self.conv2.gemm(h, res0=s)
 
@@ -646,7 +646,7 @@ class Decoder(Layer):
                 h = blk.forward(h)
             if up.upsample is not None:
                 h = up.upsample.forward(h)
-        h = ops.groupnorm(h, self.norm_out.g, self.norm_out.b, eps=1e-6, silu=True)
+        h = ops.groupnorm(h, self.norm_out.g, self.norm_out.b, eps=1e-6, silu="exact")
         return self.conv_out.to_nchw(h)
 
 

@@ -190,7 +190,8 @@ def _gn_workspace(device, nb, groups):
 
 
 def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=None):
-    """x0 (and x1): NHWC bf16 [nb, h, w, c]; returns [nb, h, w, c0+c1] bf16."""
+    """x0 (and x1): NHWC bf16 [nb, h, w, c]; returns [nb, h, w, c0+c1] bf16. silu: False, True (one-MUFU tanh form) or
+    "exact" (rcp + ex2 form: the VAE decoder)."""
     nb = x0.shape[0]
     c0 = x0.shape[-1]
     c1 = x1.shape[-1] if x1 is not None else 0
@@ -199,7 +200,7 @@ def groupnorm(x0, gamma, beta, *, x1=None, groups=32, eps=1e-5, silu=False, out=
         out = torch.empty(tuple(x0.shape[:-1]) + (c0 + c1,), device=x0.device, dtype=bf16)
     ws = _gn_workspace(x0.device, nb, groups)
     _call("fgdm_groupnorm", ("gn c=%d hw=%d" % (c0 + c1, hw), 0.0, 4.0 * nb * hw * (c0 + c1)), _p(x0), _p(x1), _p(out), _p(gamma), _p(beta), _p(ws), nb, hw, c0, c1,
-                                         groups, eps, 1 if silu else 0, _stream())
+                                         groups, eps, (2 if silu == "exact" else 1) if silu else 0, _stream())
     return out
 
 

@@ -134,7 +134,8 @@ int fgdm_embed_tokens(const int64_t* ids, const void* tok_emb, const void* pos_e
                       int dim, int vocab, void* stream);
 
 /* GroupNorm32 (+SiLU): util.py:223-225, openaimodel.py:221-224; attention.py:76-77; model.py:33-39.
- * x0/x1 virtual channel concat; workspace >= nb*129*groups*8 bytes. */
+ * x0/x1 virtual channel concat; workspace >= nb*129*groups*8 bytes. silu: 0 none, 1 x*sigmoid(x) as h + h*tanh(h), h = x/2
+ * (one MUFU; |error| <= |h| 4.9e-4), 2 x / (1 + exp(-x)) with ex2 + rcp (the VAE decoder's thirty norm + swish layers). */
 int fgdm_groupnorm(const void* x0, const void* x1, void* y, const float* gamma, const float* beta, void* workspace,
                    int nb, int hw, int c0, int c1, int groups, float eps, int silu, void* stream);
 
