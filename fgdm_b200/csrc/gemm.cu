@@ -670,6 +670,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
                 packed[j >> 1] = pack_bf16x2(x0 * gelu_f(g0), x1 * gelu_f(g1));
                 packed[(j >> 1) + 1] = pack_bf16x2(x2 * gelu_f(g2), x3 * gelu_f(g3));
               }
+              if (p.tma_epi == 3) {
+                // TMA store of the 32x32 panel (64-byte rows, 64B swizzle): the staged per-lane path below costs a
+                // shared-memory round trip and four global stores per lane and panel (27 % of the K = 320 kernel)
+                if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the staging panel is free again
+                __syncwarp();
+                const uint32_t swz = (lane >> 1) & 3;
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  st_shared_16(stg_u32 + lane * 64 + ((q ^ swz) << 4),
+                               make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]));
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                                   reinterpret_cast<uint64_t>(&map_out)), "r"(stg_u32), "r"(ocol), "r"(m_warp) : "memory");
+                  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                continue;
+              }
 #pragma unroll
               for (int q = 0; q < 4; ++q)
                 st_shared_16(stg_u32 + lane * kStgRow + q * 16,
@@ -1084,7 +1103,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a0, const __grid_constant
     }
   }
 
-  if (Cfg::kTmaEpi && p.tma_epi && warp >= 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  if ((Cfg::kTmaEpi || p.tma_epi == 3) && p.tma_epi && warp >= 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   if (CTAS == 2) cluster_sync_all();   // the peer may still be signalling this CTA's barriers / reading its smem
@@ -1355,6 +1374,15 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     uint32_t bv[2] = {32, 40};
     if (qkv_has_v && encode_tmap(&mv, p.vt_out, 2, dv, sv, bv, 0)) return -1;
   }
+  static int geglu_tma_on = -1;
+  if (geglu_tma_on < 0) { const char* e = getenv("FGDM_GEGLU_TMA"); geglu_tma_on = e ? atoi(e) : 1; }
+  if (geglu_tma_on && p.out_mode == kOutGeglu && p.range_ctas == 0 && (reinterpret_cast<uintptr_t>(obase) & 15) == 0 && (p.ldo & 7) == 0) {
+    p.tma_epi = 3;                          // GEGLU output panels leave by TMA store (any kernel instantiation)
+    uint64_t dims[2] = {static_cast<uint64_t>(p.N / 2), static_cast<uint64_t>(p.M)};
+    uint32_t box[2] = {32, 32};
+    uint64_t so[1] = {static_cast<uint64_t>(p.ldo) * 2};
+    if (encode_tmap(&mo, obase, 2, dims, so, box, 64)) return -1;
+  }
   if (p.tma_epi == 1) {
     uint64_t dims[2] = {static_cast<uint64_t>(p.N), static_cast<uint64_t>(p.M)};
     uint32_t box[2] = {32, 32};
@@ -1374,7 +1402,7 @@ int launch_gemm(GemmParams p, const void* a0, const void* a1, int a_images, cons
     }
   }
   if (p.tma_epi == 2) return launch_bn<160, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
-  if (p.tma_epi) {
+  if (p.tma_epi == 1) {
     switch (BN) {
       case 64: return launch_bn<64, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
       case 128: return launch_bn<128, 1, true>(ma0, ma1, mb, mo, mr, mv, p, stream);
