@@ -358,7 +358,7 @@ def test_groupnorm(nb, h, w, c0, c1, silu, eps):
     assert relerr(nchw(y), ref) < 1e-2
 
 
-@pytest.mark.parametrize("rows,c", [(4096, 320), (1024, 640), (256, 1280), (100, 64)])
+@pytest.mark.parametrize("rows,c", [(4096, 320), (1001, 320), (1024, 640), (256, 1280), (100, 64)])
 def test_layernorm(rows, c):
     x = (torch.randn(rows, c, device=DEV) * 3 + 1).to(torch.bfloat16)
     g = torch.randn(c, device=DEV)
