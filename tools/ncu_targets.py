@@ -46,6 +46,15 @@ def qkv(images, n, c):
     return lambda: ops.conv_gemm(x, wt, 3 * c, rows_per_img=n, out_mode=ops.OUT_QKV, qkv=(q, k, vt, 0, heads, d, n))
 
 
+def geglu(m, k):
+    n = 8 * k
+    x = torch.randn(m, k, device="cuda").to(bf)
+    wt = (torch.randn(n, k, device="cuda") / k ** 0.5).to(bf)
+    b = torch.randn(n, device="cuda")
+    out = torch.empty(m, n // 2, device="cuda", dtype=bf)
+    return lambda: ops.conv_gemm(x, wt, n, bias=b, out_mode=ops.OUT_GEGLU, out=out)
+
+
 def gn(nb, hw, c):
     s = int(hw ** 0.5)
     x = torch.randn(nb, s, s, c, device="cuda").to(bf)
@@ -63,7 +72,7 @@ def ln(rows, c):
 targets = [conv(16, 64, 64, 320, 320), conv(16, 32, 32, 640, 640), conv(16, 16, 16, 1280, 1280), conv(16, 8, 8, 1280, 1280),
            lin(65536, 320, 320), lin(4096, 1280, 1280), attn(16, 8, 4096, 4096, 40), attn(16, 8, 1024, 1024, 80),
            attn(16, 8, 4096, 77, 40), gn(16, 4096, 320), gn(16, 1024, 640), gn(16, 64, 1280), ln(65536, 320),
-           qkv(16, 4096, 320), qkv(16, 1024, 640)]
+           qkv(16, 4096, 320), qkv(16, 1024, 640), geglu(65536, 320)]
 for rep in range(2):      # pass 0 warms (function attributes, scratch allocation); profile pass 1 (ncu -s <n>)
     for t in targets:
         t()
