@@ -13,7 +13,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libfgdm_b200.so")
-SOURCES = ["api.cu", "gemm.cu", "attention.cu", "norm.cu", "elementwise.cu", "smallconv.cu"]
+SOURCES = ["api.cu", "gemm.cu", "attention.cu", "attention_wide.cu", "norm.cu", "elementwise.cu", "smallconv.cu"]
 HEADERS = ["common.cuh", "gemm.cuh", os.path.join("..", "..", "include", "fgdm_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [

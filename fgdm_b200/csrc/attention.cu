@@ -24,6 +24,9 @@ namespace fgdm {
 int encode_tmap(CUtensorMap* map, const void* ptr, int rank, const uint64_t* dims,
                 const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes = 128);
 
+int launch_attention_wide(const void* q, const void* k, const void* vt, void* out, int images, int heads, int Nq, int Nk,
+                          int d, int tok_pad, float scale, cudaStream_t stream);   // attention_wide.cu
+
 struct AttnParams {
   int BH;           // images * heads
   int heads;
@@ -1166,6 +1169,8 @@ static int launch_attn(const CUtensorMap& mq, const CUtensorMap& mk, const CUten
 // out: [images, Nq, heads*d]; all bf16.
 int launch_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int Nq, int Nk,
                      int d, int tok_pad, float scale, int causal, cudaStream_t stream) {
+  // wide heads (the VAE mid-block's single head of 512 channels): nothing of width d stays resident (attention_wide.cu)
+  if (d > 192 && !causal) return launch_attention_wide(q, k, vt, out, images, heads, Nq, Nk, d, tok_pad, scale, stream);
   if (d % 8 != 0 || d < 8 || d > 192) { set_error("attention: head dim %d unsupported (multiple of 8, <= 192)", d); return -1; }
   if (tok_pad % 8 != 0 || tok_pad < Nk) { set_error("attention: tok_pad=%d must be a multiple of 8 and >= Nk=%d", tok_pad, Nk); return -1; }
   AttnParams p;

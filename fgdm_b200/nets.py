@@ -11,6 +11,7 @@ bf16 and every arithmetic op is a kernel of libfgdm_b200.so. Only inference (`no
 """
 from __future__ import annotations
 
+import os
 from collections import namedtuple
 
 import torch
@@ -19,6 +20,10 @@ from . import _lib, ops
 from .layers import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, OUT_F32, OUT_QKV, Conv2d, Downsample, Layer,
                      Linear, Norm, ResBlock, Seq, SpatialTransformer, TimeEmbed, Upsample, batch_emb_layers, bf16,
                      repeat_rows)
+
+
+# FGDM_VAE_FLASH=0: the VAE mid-block attention materialises S and P per image as the reference does (A/B switch)
+VAE_FLASH = os.environ.get("FGDM_VAE_FLASH", "1") != "0"
 
 
 def _unsupported(**flags):
@@ -586,7 +591,11 @@ class _VaeAttn(Layer):
         ops.conv_gemm(xn.view(nb * n, c), self.w_qkv, 3 * c, bias=self.b_qkv, out_mode=OUT_QKV, rows_per_img=n,
                       qkv=(q, k, vt, 0, 1, c, n))
         o = torch.empty((nb, n, c), device=dev, dtype=bf16)
-        s = torch.empty((n, n), device=dev, dtype=torch.float32)
+        if VAE_FLASH and c % 128 == 0 and 256 <= c <= 1024 and n % 8 == 0:
+            # one launch for every image, S and P never leave the SM (csrc/attention_wide.cu)
+            ops.attention(q, k, vt, o, nb, 1, n, n, c, n, scale=float(c) ** -0.5)
+            return self.proj_out.gemm(o.view(nb, h, w, c), res0=x)
+        s = torch.empty((n, n), device=dev, dtype=torch.float32)                         # the reference's form: N x N in HBM
         p = torch.empty((n, n), device=dev, dtype=bf16)
         for i in range(nb):
             ops.conv_gemm(q[i, 0], k[i, 0], n, out_mode=OUT_F32, out=s)                 # S = Q K^T

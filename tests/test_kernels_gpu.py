@@ -227,6 +227,45 @@ def test_attention(images, heads, nq, nk, d):
     assert relerr(out, ref) < 1.5e-2
 
 
+@pytest.mark.parametrize("images,heads,nq,nk,d", [(2, 1, 4096, 4096, 512), (1, 1, 1024, 1024, 512), (1, 2, 256, 256, 256),
+                                                  (1, 1, 200, 300, 384), (2, 1, 128, 77, 512), (1, 1, 64, 64, 1024)])
+def test_attention_wide_heads(images, heads, nq, nk, d):
+    """d > 192 (the VAE mid-block AttnBlock, model.py:178-202: one head of 512 channels): csrc/attention_wide.cu streams
+    Q / K chunks, no N x N buffer. Ragged key / query counts exercise the TMA zero-fill + mask path."""
+    torch.manual_seed(11)
+    q = torch.randn(images, heads, nq, d, device=DEV).to(torch.bfloat16)
+    k = torch.randn(images, heads, nk, d, device=DEV).to(torch.bfloat16)
+    v = torch.randn(images, heads, nk, d, device=DEV).to(torch.bfloat16)
+    tok_pad = (nk + 7) // 8 * 8
+    vt = torch.zeros(images, heads, d, tok_pad, device=DEV, dtype=torch.bfloat16)
+    vt[..., :nk] = v.transpose(-1, -2)
+    out = torch.full((images, nq, heads * d), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.attention(q, k, vt, out, images, heads, nq, nk, d, tok_pad)
+    ref = _attn_ref(q, k, v, d ** -0.5).permute(0, 2, 1, 3).reshape(images, nq, heads * d)
+    assert torch.isfinite(out.float()).all()
+    assert relerr(out, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("scale_q,step", [(3.0, 0.0), (0.3, 12.0), (0.3, 3.0)])
+def test_attention_wide_heads_adversarial(scale_q, step):
+    """Wide logits (softmax nearly one-hot) and a row maximum that rises on every key tile: the lazy rescale of O in
+    TMEM and the running sum of attention_wide.cu."""
+    torch.manual_seed(12)
+    n, d = 1024, 512
+    u = F.normalize(torch.randn(d, device=DEV), dim=0)
+    ramp = (torch.arange(n, device=DEV) // 128).float() * (step * 0.6931)
+    q = torch.randn(1, 1, n, d, device=DEV) * scale_q + (u * (d ** 0.5) if step else 0.0)
+    k = torch.randn(1, 1, n, d, device=DEV) * scale_q + u[None, None, None, :] * ramp[None, None, :, None]
+    v = torch.randn(1, 1, n, d, device=DEV)
+    q, k, v = q.to(torch.bfloat16), k.to(torch.bfloat16), v.to(torch.bfloat16)
+    vt = v.transpose(-1, -2).contiguous()
+    out = torch.empty(1, n, d, device=DEV, dtype=torch.bfloat16)
+    ops.attention(q, k, vt, out, 1, 1, n, n, d, n)
+    ref = _attn_ref(q, k, v, d ** -0.5).permute(0, 2, 1, 3).reshape(1, n, d)
+    assert torch.isfinite(out.float()).all()
+    assert relerr(out, ref) < 1.5e-2
+
+
 def test_attention_causal_and_text_kernels():
     """Causal mask (CLIP text transformer), token+position gather, quick-GELU epilogue."""
     images, heads, n, d = 3, 12, 77, 64

@@ -217,6 +217,29 @@ def test_vae_decode_vs_reference_golden(fgdm):
     assert psnr(img, ref, 2.0) > 35.0
 
 
+def test_vae_decode_flash_vs_materialised_attention(fgdm, monkeypatch):
+    """K10: the mid-block AttnBlock (model.py:178-202) through csrc/attention_wide.cu (no N x N buffer) and in the
+    reference's form (S = QK^T in fp32, softmax, PV through HBM), both against the fp32 oracle, at the benchmark's 64x64
+    latent (N = 4096 tokens, d = 512) for two images at once. Same bars as the 16x16 golden; the two bf16 forms differ
+    from each other by their rounding noise only (P unnormalised <= 2^8 vs normalised)."""
+    import fgdm_oracle as orc
+    from fgdm_b200 import nets
+    model, sd = fgdm
+    z = (synth.randn((2, 4, 64, 64), 43) * 0.18215 * 3.0).to(DEV)
+    assert nets.VAE_FLASH
+    img = model.decode_first_stage(z)
+    monkeypatch.setattr(nets, "VAE_FLASH", False)
+    mat = model.decode_first_stage(z)
+    ref = orc.vae_decode(sd, z)
+    e_f, e_m = relmax(img, ref), relmax(mat, ref)
+    print("vae decode 512^2 vs oracle: flash relmax", e_f, "psnr", psnr(img, ref, 2.0), "| materialised relmax", e_m, "psnr",
+          psnr(mat, ref, 2.0), "| flash vs materialised relmax", relmax(img, mat))
+    assert torch.isfinite(img).all()
+    assert e_f < 3e-2 and psnr(img, ref, 2.0) > 35.0
+    assert e_f < 1.5 * e_m + 5e-3            # the flash form is no worse than the form it replaces
+    assert relmax(img, mat) < 3e-2
+
+
 def test_controlldm_apply_model_vs_reference_golden(control):
     model, _ = control
     c, g = gc.control_case(), gold("control_apply")
