@@ -118,8 +118,11 @@ int fgdm_conv_gemm(const fgdm_gemm_args* args, void* stream);
 /* number of row_stats slots per row that fgdm_conv_gemm will write for these args (2 x the number of N tiles it picks) */
 int fgdm_gemm_stats_slots(const fgdm_gemm_args* args);
 
-/* CrossAttention core (attention.py:189-202; controlnet/ldm/modules/attention.py:171-190).
- * q [images, heads, nq, d], k [images, heads, nk, d], vt [images, heads, d, tok_pad], out [images, nq, heads*d]. */
+/* CrossAttention core (attention.py:189-202; controlnet/ldm/modules/attention.py:171-190) and the VAE AttnBlock core
+ * (ldm/modules/diffusionmodules/model.py:178-202: one head of 512 channels).
+ * q [images, heads, nq, d], k [images, heads, nk, d], vt [images, heads, d, tok_pad], out [images, nq, heads*d].
+ * d: a multiple of 8 up to 192, or a multiple of 128 in [256, 1024] (streamed Q / K chunks, csrc/attention_wide.cu);
+ * tok_pad: a multiple of 8, >= nk. Neither form writes the nq x nk logits or probabilities to memory. */
 int fgdm_attention(const void* q, const void* k, const void* vt, void* out, int images, int heads, int nq, int nk,
                    int d, int tok_pad, float scale, void* stream);
 
