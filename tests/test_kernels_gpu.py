@@ -383,7 +383,11 @@ def test_qkv_head_aligned_tma_epilogue(images, n, c, mode):
 
 @pytest.mark.parametrize("nb,h,w,c0,c1,silu,eps", [(2, 64, 64, 320, 0, True, 1e-5), (2, 16, 16, 1280, 640, True, 1e-5),
                                                    (1, 8, 8, 64, 0, False, 1e-6), (1, 128, 128, 128, 0, True, 1e-6),
-                                                   (3, 32, 32, 640, 320, False, 1e-5)])
+                                                   (3, 32, 32, 640, 320, False, 1e-5),
+                                                   # the benchmark's 64x64 level (single-launch re-read kernel, 8 / 16-byte slabs)
+                                                   (16, 64, 64, 320, 0, True, 1e-5), (16, 64, 64, 640, 320, True, 1e-5),
+                                                   (8, 64, 64, 320, 0, False, 1e-5), (8, 64, 64, 512, 0, "exact", 1e-6),
+                                                   (16, 64, 64, 320, 320, True, 1e-5), (12, 48, 48, 320, 0, True, 1e-5)])
 def test_groupnorm(nb, h, w, c0, c1, silu, eps):
     x0 = nhwc(torch.randn(nb, c0, h, w, device=DEV) * 2 + 0.5)
     x1 = nhwc(torch.randn(nb, c1, h, w, device=DEV)) if c1 else None

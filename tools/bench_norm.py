@@ -29,8 +29,11 @@ def timeit(fn, n=20):
     return e0.elapsed_time(e1) * 1e3 / n
 
 
-for nb, hw, c in [(16, 4096, 320), (16, 4096, 640), (16, 1024, 640), (16, 1024, 1280), (16, 256, 1280), (16, 64, 1280),
-                  (16, 64, 2560), (16, 256, 2560), (8, 65536, 256), (8, 262144, 128)]:
+shapes = [(16, 4096, 320), (8, 4096, 320), (8, 4096, 512), (16, 4096, 640), (16, 1024, 640), (16, 1024, 1280), (16, 256, 1280),
+          (16, 64, 1280), (16, 64, 2560), (16, 256, 2560), (8, 65536, 256), (8, 262144, 128)]
+if len(sys.argv) > 1:
+    shapes = shapes[:int(sys.argv[1])]
+for nb, hw, c in shapes:
     h = int(hw ** 0.5)
     x = torch.randn(nb, h, h, c, device="cuda").to(torch.bfloat16)
     g = torch.randn(c, device="cuda")
@@ -38,7 +41,7 @@ for nb, hw, c in [(16, 4096, 320), (16, 4096, 640), (16, 1024, 640), (16, 1024, 
     out = torch.empty_like(x)
     us = timeit(lambda: ops.groupnorm(x, g, b, silu=True, out=out))
     print(f"gn nb={nb} hw={hw} c={c}: {us:8.1f} us  {4.0 * x.numel() / us / 1e3:7.0f} GB/s (algorithmic 4 B/elem)")
-for rows, c in [(65536, 320), (16384, 640), (4096, 1280)]:
+for rows, c in ([(65536, 320), (16384, 640), (4096, 1280)] if len(sys.argv) <= 1 else []):
     x = torch.randn(rows, c, device="cuda").to(torch.bfloat16)
     g = torch.randn(c, device="cuda")
     b = torch.randn(c, device="cuda")
