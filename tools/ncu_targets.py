@@ -72,7 +72,8 @@ def ln(rows, c):
 targets = [conv(16, 64, 64, 320, 320), conv(16, 32, 32, 640, 640), conv(16, 16, 16, 1280, 1280), conv(16, 8, 8, 1280, 1280),
            lin(65536, 320, 320), lin(4096, 1280, 1280), attn(16, 8, 4096, 4096, 40), attn(16, 8, 1024, 1024, 80),
            attn(16, 8, 4096, 77, 40), gn(16, 4096, 320), gn(16, 1024, 640), gn(16, 64, 1280), ln(65536, 320),
-           qkv(16, 4096, 320), qkv(16, 1024, 640), geglu(65536, 320)]
+           qkv(16, 4096, 320), qkv(16, 1024, 640), geglu(65536, 320),
+           attn(8, 1, 4096, 4096, 512)]      # VAE mid-block: wide_attention_kernel<256>
 for rep in range(2):      # pass 0 warms (function attributes, scratch allocation); profile pass 1 (ncu -s <n>)
     for t in targets:
         t()
