@@ -17,6 +17,7 @@ ABI_VERSION = 5
 OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32, OUT_NCHW_F32 = 0, 1, 2, 3, 4
 ACT_NONE, ACT_SILU, ACT_RELU, ACT_QUICK_GELU = 0, 1, 2, 3
 CONV_1X1, CONV_3X3, CONV_3X3_S2 = 0, 1, 2
+CONV_UP2_P0 = 3          # + 2a + b: sub-pixel phase (a, b) of nearest-2x + conv3x3 (include/fgdm_b200.h)
 
 vp, fp, ip = C.c_void_p, C.c_void_p, C.c_void_p  # all device pointers travel as integers
 

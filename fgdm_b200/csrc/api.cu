@@ -229,6 +229,10 @@ static int conv_gemm_impl(const fgdm_gemm_args* a, void* stream, int* stats_slot
       p.tap_dw[t] = (s == 0) ? -1 : 0;
       p.tap_dn[t] = (pr * 2 + pc) * a->nb;
     }
+  } else if (a->conv >= FGDM_CONV_UP2_P0 && a->conv <= FGDM_CONV_UP2_P3) {
+    const int ph = a->conv - FGDM_CONV_UP2_P0, pa = ph >> 1, pb = ph & 1;   // output pixel (2i + pa, 2j + pb)
+    p.taps = 4;
+    for (int t = 0; t < 4; ++t) { p.tap_dh[t] = pa - 1 + (t >> 1); p.tap_dw[t] = pb - 1 + (t & 1); }
   } else {
     set_error("fgdm_conv_gemm: conv=%d unknown", a->conv);
     return -2;
@@ -401,7 +405,7 @@ int fgdm_skinny_linear(const float* x, const void* w, const float* b, float* y, 
 
 int fgdm_resample(const void* in, void* out, int nb, int h, int w, int c, int mode, void* stream) {
   FGDM_NONNULL(in, "in"); FGDM_NONNULL(out, "out");
-  if (mode < 0 || mode > 2) { set_error("fgdm_resample: mode=%d unknown", mode); return -2; }
+  if (mode < 0 || mode > 3) { set_error("fgdm_resample: mode=%d unknown", mode); return -2; }
   return launch_resample(in, out, nb, h, w, c, mode, reinterpret_cast<cudaStream_t>(stream));
 }
 

@@ -306,6 +306,8 @@ int launch_skinny_linear(const float* x, const void* w, const float* b, float* y
 //                                                         in [NB,H,W,C] -> out [NB,H/2,W/2,C]
 //  mode 2: phase split for stride-2 convs                 in [NB,H,W,C] -> out [4,NB,H/2,W/2,C],
 //          phase = (h&1)*2 + (w&1); a 3x3/s2/p1 conv becomes 9 unit-stride shifted loads.
+//  mode 3: pixel shuffle of the four sub-pixel convs of an Upsample (FGDM_CONV_UP2_P*, include/fgdm_b200.h)
+//                                                         in [NB,H,W,4,C/4] -> out [NB,2H,2W,C/4]
 // ---------------------------------------------------------------------------------------------
 __global__ void resample_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int NB, int H,
                                 int W, int C, int mode) {
@@ -349,6 +351,20 @@ __global__ void resample_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloa
     *reinterpret_cast<uint4*>(out + i * 8) =
         make_uint4(pack_bf16x2(acc[0] * 0.25f, acc[1] * 0.25f), pack_bf16x2(acc[2] * 0.25f, acc[3] * 0.25f),
                    pack_bf16x2(acc[4] * 0.25f, acc[5] * 0.25f), pack_bf16x2(acc[6] * 0.25f, acc[7] * 0.25f));
+  } else if (mode == 3) {
+    // pixel shuffle: in [NB,H,W,4,C'] (C = 4 C' channels per input pixel) -> out [NB,2H,2W,C'], phase = (oh&1)*2 + (ow&1)
+    const int CO = C / 4, VO = CO / 8;
+    const size_t total = static_cast<size_t>(NB) * 4 * H * W * VO;
+    if (i >= total) return;
+    const int v = i % VO;
+    size_t p = i / VO;
+    const int ow = p % (2 * W); p /= (2 * W);
+    const int oh = p % (2 * H);
+    const int n = p / (2 * H);
+    const int phase = (oh & 1) * 2 + (ow & 1);
+    const uint4 u = *reinterpret_cast<const uint4*>(
+        in + ((static_cast<size_t>(n) * H + oh / 2) * W + ow / 2) * C + phase * CO + v * 8);
+    *reinterpret_cast<uint4*>(out + i * 8) = u;
   } else {
     const size_t total = static_cast<size_t>(NB) * H * W * V;
     if (i >= total) return;
@@ -366,7 +382,8 @@ __global__ void resample_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloa
 
 int launch_resample(const void* in, void* out, int NB, int H, int W, int C, int mode, cudaStream_t stream) {
   if (C % 8) { set_error("resample: C=%d must be a multiple of 8", C); return -1; }
-  if (mode != 0 && ((H | W) & 1)) { set_error("resample: odd H/W (%d,%d)", H, W); return -1; }
+  if (mode != 0 && mode != 3 && ((H | W) & 1)) { set_error("resample: odd H/W (%d,%d)", H, W); return -1; }
+  if (mode == 3 && C % 32) { set_error("resample: pixel shuffle needs C %% 32 == 0 (C=%d)", C); return -1; }
   size_t total = static_cast<size_t>(NB) * H * W * (C / 8);
   if (mode == 0) total *= 4;
   if (mode == 1) total /= 4;

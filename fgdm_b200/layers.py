@@ -13,7 +13,7 @@ import os
 import torch
 
 from . import ops
-from .ops import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU,
+from .ops import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, CONV_UP2_P0, OUT_BF16, OUT_F32, OUT_GEGLU,
                   OUT_NCHW_F32, OUT_QKV)
 
 bf16 = torch.bfloat16
@@ -411,14 +411,41 @@ class Downsample(Layer):
         return self.op.gemm(x)
 
 
+# FGDM_UP_PHASE=0: Upsample as nearest-2x kernel + 3x3 conv on the upsampled tensor (A/B switch). The sub-pixel form needs
+# enough rows per phase GEMM to fill the SMs (FGDM_UP_PHASE_MIN_ROWS input pixels; the UNet's 8x8 -> 16x16 level has 1024).
+UP_PHASE = os.environ.get("FGDM_UP_PHASE", "1") != "0"
+UP_PHASE_MIN_ROWS = int(os.environ.get("FGDM_UP_PHASE_MIN_ROWS", "4096"))
+
+
 class Upsample(Layer):
     """openaimodel.py:95-130; VAE model.py:42-57: nearest 2x then conv3x3."""
 
     def __init__(self, ch):
         super().__init__()
+        self.ch = ch
         self.conv = self.add("conv", Conv2d(ch, ch, 3))
 
+    def load(self, sd, prefix, dev):
+        super().load(sd, prefix, dev)
+        # Sub-pixel form: output pixel (2i+a, 2j+b) of conv3x3(nearest2x(x)) only sees input rows {i-1+a, i+a} and
+        # columns {j-1+b, j+b}; the 3x3 taps that land on the same input pixel are summed (in fp32, rounded once):
+        # four 4-tap convolutions on the LOW-resolution tensor = 4/9 of the flops, and no upsampled tensor in HBM.
+        w = self._get(sd, prefix + "conv.weight", (self.ch, self.ch, 3, 3)).to(dev, torch.float32)
+        sets = (((0,), (1, 2)), ((0, 1), (2,)))                  # a (or b) -> 3x3 taps behind 2x2 tap r (or s)
+        self.w_phase = []
+        for a in range(2):
+            for b in range(2):
+                taps = [sum(w[:, :, ky, kx] for ky in sets[a][r] for kx in sets[b][s]) for r in range(2) for s in range(2)]
+                self.w_phase.append(torch.stack(taps, 1).reshape(self.ch, 4 * self.ch).to(bf16).contiguous())   # [O][(r,s)][I]
+
     def forward(self, x):
+        nb, h, w, c = x.shape
+        if UP_PHASE and nb * h * w >= UP_PHASE_MIN_ROWS:
+            packed = torch.empty((nb, h, w, 4 * c), device=x.device, dtype=bf16)      # [.., phase, c]
+            for ph in range(4):
+                ops.conv_gemm(x, self.w_phase[ph], c, conv=CONV_UP2_P0 + ph, bias=self.conv.b, out=packed.view(-1, 4 * c),
+                              ldo=4 * c, col_off=ph * c)
+            return ops.resample(packed, 3)                        # -> [nb, 2h, 2w, c]
         return self.conv.gemm(ops.resample(x, 0))
 
 

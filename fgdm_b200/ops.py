@@ -11,7 +11,7 @@ import math
 import torch
 
 from . import _lib
-from ._lib import (ACT_NONE, ACT_QUICK_GELU, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, OUT_BF16, OUT_F32, OUT_GEGLU,
+from ._lib import (ACT_NONE, ACT_QUICK_GELU, ACT_RELU, ACT_SILU, CONV_1X1, CONV_3X3, CONV_3X3_S2, CONV_UP2_P0, OUT_BF16, OUT_F32, OUT_GEGLU,
                    OUT_NCHW_F32, OUT_QKV, GemmArgs)
 
 bf16 = torch.bfloat16
@@ -148,12 +148,13 @@ def conv_gemm(a0, weight, n, *, conv=CONV_1X1, a1=None, nb=None, h=None, w=None,
             raise RuntimeError("fgdm_gemm_stats_slots: " + _lib.last_error())
         stats = torch.empty((m, slots, 2), device=a0.device, dtype=torch.float32)
         args.row_stats = _p(stats)
-    kdim = (9 if conv != CONV_1X1 else 1) * (c0 + c1)
+    taps = 1 if conv == CONV_1X1 else (4 if conv >= CONV_UP2_P0 else 9)
+    kdim = taps * (c0 + c1)
     nres = (res0 is not None) + (res1 is not None)
     # profile key: shape + the epilogue variant (out mode, residuals, rowvec, LayerNorm fold consumer / producer)
     var = "".join(("" if out_mode == OUT_BF16 else " o%d" % out_mode, " r%d" % nres if nres else "", " rv" if rowvec is not None else "",
                    " ln" if ln is not None else "", " st" if want_stats else ""))
-    _call("fgdm_conv_gemm", ("gemm taps=%d m=%d k=%d n=%d%s" % (9 if conv != CONV_1X1 else 1, m, kdim, n, var), 2.0 * m * n * kdim,
+    _call("fgdm_conv_gemm", ("gemm taps=%d m=%d k=%d n=%d%s" % (taps, m, kdim, n, var), 2.0 * m * n * kdim,
                              2.0 * (m * (c0 + c1) + n * kdim + m * n * (1 + nres))), C.byref(args), _stream())
     return (out, stats) if want_stats else out
 
@@ -276,10 +277,13 @@ def skinny_linear(x, w, b, in_act=False, out_act=False):
 
 
 def resample(x, mode):
-    """mode 0: nearest 2x up; 1: 2x2 avg pool; 2: phase split -> [4, nb, h/2, w/2, c]."""
+    """mode 0: nearest 2x up; 1: 2x2 avg pool; 2: phase split -> [4, nb, h/2, w/2, c]; 3: pixel shuffle
+    [nb, h, w, 4*c'] -> [nb, 2h, 2w, c']."""
     nb, h, w, c = x.shape
     if mode == 0:
         out = torch.empty((nb, 2 * h, 2 * w, c), device=x.device, dtype=bf16)
+    elif mode == 3:
+        out = torch.empty((nb, 2 * h, 2 * w, c // 4), device=x.device, dtype=bf16)
     elif mode == 1:
         out = torch.empty((nb, h // 2, w // 2, c), device=x.device, dtype=bf16)
     else:

@@ -61,7 +61,14 @@ enum { FGDM_ACT_NONE = 0, FGDM_ACT_SILU = 1, FGDM_ACT_RELU = 2, FGDM_ACT_QUICK_G
 enum {
   FGDM_CONV_1X1 = 0,      /* Linear / 1x1 conv */
   FGDM_CONV_3X3 = 1,      /* 3x3, stride 1, pad 1 */
-  FGDM_CONV_3X3_S2 = 2    /* 3x3, stride 2, pad 1 on a phase-split input (fgdm_resample mode 2) */
+  FGDM_CONV_3X3_S2 = 2,   /* 3x3, stride 2, pad 1 on a phase-split input (fgdm_resample mode 2) */
+  /* Upsample = nearest 2x then 3x3 conv (openaimodel.py:95-130, model.py:42-57) WITHOUT the upsampled tensor: output
+   * pixel (2i+a, 2j+b) only sees the 2x2 input neighbourhood rows {i-1+a, i+a} x columns {j-1+b, j+b}, with the 3x3
+   * weights that land on the same input pixel summed by the host. FGDM_CONV_UP2_P0 + 2a + b is that 4-tap conv on the
+   * LOW-resolution input (nb, h, w = input geometry; weight [n][4*c0], K index = (r*2+s)*c0 + c): 4/9 of the flops. The
+   * four phases write column blocks of a [nb, h, w, 4n] tensor (ldo = 4n, col_off = (2a+b)*n) that fgdm_resample mode 3
+   * interleaves into [nb, 2h, 2w, n]. */
+  FGDM_CONV_UP2_P0 = 3, FGDM_CONV_UP2_P1 = 4, FGDM_CONV_UP2_P2 = 5, FGDM_CONV_UP2_P3 = 6
 };
 
 typedef struct {
@@ -195,7 +202,8 @@ int fgdm_skinny_linear(const float* x, const void* w, const float* b, float* y, 
                        int out_act, void* stream);
 
 /* NHWC bf16 resampling. mode 0: nearest 2x up (openaimodel.py:123, model.py:53); 1: 2x2 avg pool
- * (adapter.py:270-277); 2: phase split for stride-2 convs -> [4, nb, h/2, w/2, c]. */
+ * (adapter.py:270-277); 2: phase split for stride-2 convs -> [4, nb, h/2, w/2, c]; 3: pixel shuffle of the four
+ * FGDM_CONV_UP2_P* outputs, in [nb, h, w, 4, c'] (c = 4c' channels) -> out [nb, 2h, 2w, c'], phase = a*2 + b. */
 int fgdm_resample(const void* in, void* out, int nb, int h, int w, int c, int mode, void* stream);
 
 int fgdm_add_bf16(const void* a, const void* b, void* out, size_t n, void* stream);

@@ -401,6 +401,31 @@ def test_groupnorm(nb, h, w, c0, c1, silu, eps):
     assert relerr(nchw(y), ref) < 1e-2
 
 
+@pytest.mark.parametrize("nb,h,w,c", [(16, 16, 16, 1280), (16, 32, 32, 640), (2, 64, 64, 128), (3, 16, 32, 64), (1, 8, 8, 64)])
+def test_upsample_subpixel_phases(nb, h, w, c, monkeypatch):
+    """Upsample (openaimodel.py:95-130, model.py:42-57): nearest 2x + conv3x3 as four 4-tap sub-pixel convolutions on the
+    low-resolution tensor (FGDM_CONV_UP2_P*, pixel shuffle = fgdm_resample mode 3) against F.conv2d(F.interpolate(x)) and
+    against the kernel path that materialises the upsampled tensor."""
+    from fgdm_b200 import layers
+    torch.manual_seed(21)
+    up = layers.Upsample(c)
+    sd = {"conv.weight": torch.randn(c, c, 3, 3) * (9 * c) ** -0.5, "conv.bias": torch.randn(c) * 0.1}
+    up.load(sd, "", DEV)
+    x = torch.randn(nb, c, h, w, device=DEV)
+    xb = nhwc(x)
+    monkeypatch.setattr(layers, "UP_PHASE", True)
+    monkeypatch.setattr(layers, "UP_PHASE_MIN_ROWS", 1)
+    y = up.forward(xb)
+    monkeypatch.setattr(layers, "UP_PHASE", False)
+    y_old = up.forward(xb)
+    ref = F.conv2d(F.interpolate(nchw(xb), scale_factor=2, mode="nearest"), sd["conv.weight"].to(DEV), sd["conv.bias"].to(DEV),
+                   padding=1)
+    assert y.shape == y_old.shape == (nb, 2 * h, 2 * w, c)
+    e_new, e_old = relerr(nchw(y), ref), relerr(nchw(y_old), ref)
+    print(f"upsample {nb}x{h}x{w}x{c}: sub-pixel {e_new:.2e}, materialised {e_old:.2e}")
+    assert e_new < 1.5e-2 and e_old < 1.5e-2
+
+
 @pytest.mark.parametrize("rows,c", [(4096, 320), (1001, 320), (1024, 640), (256, 1280), (100, 64)])
 def test_layernorm(rows, c):
     x = (torch.randn(rows, c, device=DEV) * 3 + 1).to(torch.bfloat16)
