@@ -12,7 +12,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FGDM_B200_LIB") or os.path.join(_HERE, "libfgdm_b200.so")   # override: A/B builds of one kernel
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 OUT_BF16, OUT_GEGLU, OUT_QKV, OUT_F32, OUT_NCHW_F32 = 0, 1, 2, 3, 4
 ACT_NONE, ACT_SILU, ACT_RELU, ACT_QUICK_GELU = 0, 1, 2, 3

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define FGDM_ABI_VERSION 5
+#define FGDM_ABI_VERSION 6
 
 const char* fgdm_last_error(void);
 int fgdm_abi_version(void);
