@@ -260,3 +260,39 @@ def test_prompt_sharding_and_all_gather_gloo_world2():
         assert p.exitcode == 0
     assert res[0][1] == [0, 1, 2] and res[1][1] == [3, 4]
     assert res[0][2] == res[1][2] == [0, 1, 2, 3, 4, 255]
+
+
+def test_upsample_subpixel_weights_match_interpolate_then_conv():
+    """Host logic of the sub-pixel Upsample (layers.Upsample.load, include/fgdm_b200.h FGDM_CONV_UP2_P*): the four phase
+    weight sets, applied as 4-tap convolutions at the offsets api.cu programs (dh = a - 1 + r, dw = b - 1 + s), reproduce
+    F.conv2d(F.interpolate(x, scale_factor=2, mode="nearest"), w, b, padding=1) (openaimodel.py:118-130) up to the one
+    bf16 rounding of the summed weights."""
+    import torch.nn.functional as F
+    from fgdm_b200 import layers
+    torch.manual_seed(3)
+    c, nb, h, w = 8, 2, 5, 7
+    up = layers.Upsample(c)
+    sd = {"conv.weight": torch.randn(c, c, 3, 3), "conv.bias": torch.randn(c)}
+    up.load(sd, "", "cpu")
+    assert len(up.w_phase) == 4 and all(tuple(p.shape) == (c, 4 * c) and p.dtype == torch.bfloat16 for p in up.w_phase)
+    x = torch.randn(nb, c, h, w)
+    ref = F.conv2d(F.interpolate(x, scale_factor=2, mode="nearest"), sd["conv.weight"], sd["conv.bias"], padding=1)
+    xp = F.pad(x, (1, 1, 1, 1))
+    out = torch.empty_like(ref)
+    for ph in range(4):
+        a, b = ph >> 1, ph & 1
+        wp = up.w_phase[ph].float().reshape(c, 4, c)                       # [O][(r, s)][I]
+        acc = torch.zeros(nb, c, h, w)
+        for t in range(4):
+            dh, dw = a - 1 + (t >> 1), b - 1 + (t & 1)
+            acc += torch.einsum("oi,nihw->nohw", wp[:, t], xp[:, :, 1 + dh:1 + dh + h, 1 + dw:1 + dw + w])
+        out[:, :, a::2, b::2] = acc + sd["conv.bias"][None, :, None, None]
+    err = float((out - ref).abs().max() / ref.abs().max())
+    assert err < 1e-2, err                                               # bf16 weights: ~2^-9 relative
+    # and exactly, with the un-rounded sums
+    w32 = sd["conv.weight"]
+    sets = (((0,), (1, 2)), ((0, 1), (2,)))
+    for ph in range(4):
+        a, b = ph >> 1, ph & 1
+        exact = torch.stack([sum(w32[:, :, ky, kx] for ky in sets[a][r] for kx in sets[b][s]) for r in range(2) for s in range(2)], 1)
+        assert torch.allclose(up.w_phase[ph].float().reshape(c, 4, c), exact, rtol=1e-2, atol=1e-2)
