@@ -417,6 +417,18 @@ UP_PHASE = os.environ.get("FGDM_UP_PHASE", "1") != "0"
 UP_PHASE_MIN_ROWS = int(os.environ.get("FGDM_UP_PHASE_MIN_ROWS", "4096"))
 
 
+def _tile_geometry_ok(nb, h, w, bm=128):
+    """Mirror of gemm.cu tile_box: can [nb, h, w] images be cut into 128-row A tiles?"""
+    if nb == 1 and h == 1:
+        return True
+    if w >= bm:
+        return w % bm == 0
+    if bm % w != 0:
+        return False
+    rows = bm // w
+    return h % rows == 0 if rows <= h else rows % h == 0
+
+
 class Upsample(Layer):
     """openaimodel.py:95-130; VAE model.py:42-57: nearest 2x then conv3x3."""
 
@@ -440,7 +452,7 @@ class Upsample(Layer):
 
     def forward(self, x):
         nb, h, w, c = x.shape
-        if UP_PHASE and nb * h * w >= UP_PHASE_MIN_ROWS:
+        if UP_PHASE and nb * h * w >= UP_PHASE_MIN_ROWS and _tile_geometry_ok(nb, h, w):
             packed = torch.empty((nb, h, w, 4 * c), device=x.device, dtype=bf16)      # [.., phase, c]
             for ph in range(4):
                 ops.conv_gemm(x, self.w_phase[ph], c, conv=CONV_UP2_P0 + ph, bias=self.conv.b, out=packed.view(-1, 4 * c),
