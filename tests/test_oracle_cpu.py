@@ -296,3 +296,45 @@ def test_upsample_subpixel_weights_match_interpolate_then_conv():
         a, b = ph >> 1, ph & 1
         exact = torch.stack([sum(w32[:, :, ky, kx] for ky in sets[a][r] for kx in sets[b][s]) for r in range(2) for s in range(2)], 1)
         assert torch.allclose(up.w_phase[ph].float().reshape(c, 4, c), exact, rtol=1e-2, atol=1e-2)
+
+
+def test_upsample_path_selection_and_call_arguments(monkeypatch):
+    """Host logic of layers.Upsample.forward with the kernels stubbed: the sub-pixel form issues the four phase GEMMs
+    (conv = FGDM_CONV_UP2_P0 + phase, shared packed output with ldo = 4c and col_off = phase * c) and one pixel shuffle; small
+    launches, untileable low-resolution geometries and FGDM_UP_PHASE=0 take the nearest-2x + conv3x3 form."""
+    from fgdm_b200 import _lib, layers, ops
+    c = 64
+    up = layers.Upsample(c)
+    up.load({"conv.weight": torch.zeros(c, c, 3, 3), "conv.bias": torch.zeros(c)}, "", "cpu")
+    calls = []
+
+    def fake_gemm(a0, weight, n, **kw):
+        calls.append(("gemm", kw.get("conv", 0), tuple(a0.shape), tuple(weight.shape), kw.get("ldo"), kw.get("col_off", 0)))
+        out = kw.get("out")
+        return out if out is not None else torch.zeros(a0.shape[0] * a0.shape[1] * a0.shape[2], n, dtype=torch.bfloat16)
+
+    def fake_resample(x, mode):
+        calls.append(("resample", mode, tuple(x.shape)))
+        nb, h, w, ch = x.shape
+        return torch.zeros(nb, 2 * h, 2 * w, ch // 4 if mode == 3 else ch, dtype=torch.bfloat16)
+
+    monkeypatch.setattr(ops, "conv_gemm", fake_gemm)
+    monkeypatch.setattr(ops, "resample", fake_resample)
+    monkeypatch.setattr(layers, "UP_PHASE", True)
+    monkeypatch.setattr(layers, "UP_PHASE_MIN_ROWS", 4096)
+    x = torch.zeros(16, 16, 16, c, dtype=torch.bfloat16)                  # 4096 input pixels: sub-pixel form
+    y = up.forward(x)
+    assert tuple(y.shape) == (16, 32, 32, c)
+    assert [k[0] for k in calls] == ["gemm"] * 4 + ["resample"]
+    for ph in range(4):
+        kind, conv, ashape, wshape, ldo, col_off = calls[ph]
+        assert conv == _lib.CONV_UP2_P0 + ph and ashape == (16, 16, 16, c) and wshape == (c, 4 * c)
+        assert ldo == 4 * c and col_off == ph * c
+    assert calls[4] == ("resample", 3, (16, 16, 16, 4 * c))
+    for xs, flag in (((2, 16, 16, c), True), ((16, 24, 40, c), True), ((16, 16, 16, c), False)):   # small / untileable / off
+        calls.clear()
+        monkeypatch.setattr(layers, "UP_PHASE", flag)
+        y = up.forward(torch.zeros(*xs, dtype=torch.bfloat16))
+        assert [k[:2] for k in calls] == [("resample", 0), ("gemm", _lib.CONV_3X3)], calls
+        assert tuple(y.shape) == (xs[0], 2 * xs[1], 2 * xs[2], c)
+    assert layers._tile_geometry_ok(16, 32, 32) and layers._tile_geometry_ok(8, 256, 256) and not layers._tile_geometry_ok(1, 96, 192)
